@@ -1,0 +1,208 @@
+/* pathtracer_cuda.h — PathTracer_CUDA: the C ABI of the B200-native path-tracing hot path.
+ *
+ * Drop-in seam: these entry points replace the three calls PathTracer_Main makes into the
+ * reference's OpenCL layer (reference Controleur/PathTracer_OpenCL.h:17-19, called from
+ * Controleur/PathTracer.cpp:73-89):
+ *
+ *     OpenCL_SetupContext(globalVars, sampler)      ->  ptc_create
+ *     OpenCL_InitializeMemory(globalVars)           ->  ptc_upload_scene
+ *     OpenCL_RunKernel(globalVars, cb, n, &t,&t,&t) ->  { ptc_render; ptc_read_image; cb } x n,
+ *                                                       ptc_read_stats, ptc_destroy
+ *
+ * C++ shims with the reference's exact signatures (CUDA_SetupContext / CUDA_InitializeMemory /
+ * CUDA_RunKernel) live in opencl_pathtracer_b200/host/PathTracer_CUDA.h; INTEGRATION.md shows the
+ * three-line change in PathTracer.cpp.
+ *
+ * Conventions: every function returns a ptc_status (0 = success); no exceptions, no STL and no
+ * CUDA/torch types cross this boundary; host arrays are borrowed only for the duration of the call.
+ * A context is owned by one host thread at a time. There is NO CPU fallback: without a CUDA device
+ * ptc_create fails with PTC_ERR_NO_DEVICE.
+ */
+#ifndef PATHTRACER_CUDA_H
+#define PATHTRACER_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#include "pathtracer_structs.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define PTC_API __declspec(dllexport)
+#else
+#define PTC_API __attribute__((visibility("default")))
+#endif
+
+#define PTC_MAX_INTERSECTION_NUMBER 5000u /* reference Controleur/PathTracer_PreProc.h:17 */
+#define PTC_BVH_MAX_DEPTH 30u             /* reference Controleur/PathTracer_PreProc.h:18, kernel header.cl:16 */
+#define PTC_MAX_LIGHT_SIZE 30u            /* reference Controleur/PathTracer_PreProc.h:19 */
+
+typedef struct ptc_ctx ptc_ctx;
+
+typedef enum ptc_status
+{
+    PTC_OK = 0,
+    PTC_ERR_INVALID = 1,     /* bad argument / inconsistent scene (message says which) */
+    PTC_ERR_CUDA = 2,        /* a CUDA runtime call failed (message carries cudaGetErrorString) */
+    PTC_ERR_NO_DEVICE = 3,   /* no usable CUDA device: this library has no CPU path */
+    PTC_ERR_STATE = 4,       /* call order violated (e.g. render before upload) */
+    PTC_ERR_LIMIT = 5,       /* reference limits exceeded: BVH depth >= 30 or lights >= 30
+                                (reference Controleur/PathTracer.cpp:54-65 throws for the same) */
+    PTC_ERR_UNSUPPORTED = 6  /* input outside the documented contract (see DESIGN.md "w lanes") */
+} ptc_status;
+
+/* reference Controleur/PathTracer_Structs.h:130-135 (enum Sampler), same numbering */
+typedef enum ptc_sampler { PTC_SAMPLER_JITTERED = 0, PTC_SAMPLER_RANDOM = 1, PTC_SAMPLER_UNIFORM = 2 } ptc_sampler;
+
+/* PARITY: reference traversal order, culling quirks and IEEE arithmetic (bit-exact hits).
+ * FAST:   same estimator, free traversal order / correct culling / FMA (checked by image RMSE). */
+typedef enum ptc_mode { PTC_MODE_PARITY = 0, PTC_MODE_FAST = 1 } ptc_mode;
+
+enum
+{
+    PTC_FLAG_STAGE_TIMING = 1u << 0, /* bracket every stage launch with CUDA events (ptc_read_counters) */
+    PTC_FLAG_NO_VARIANCE = 1u << 1,  /* do not maintain imageV (only the dead supersampling path reads it) */
+    PTC_FLAG_NO_GRAPH = 1u << 2      /* launch stages directly instead of replaying a captured CUDA graph */
+};
+
+/* Replaces the `-D` build options of reference Controleur/PathTracer_OpenCL.cpp:292-314: all run-time here. */
+typedef struct ptc_config
+{
+    uint32_t struct_size;          /* = sizeof(ptc_config), for forward compatibility */
+    int32_t device;                /* CUDA device ordinal */
+    uint32_t image_width;          /* IMAGE_WIDTH */
+    uint32_t image_height;         /* IMAGE_HEIGHT */
+    uint32_t ray_max_depth;        /* MAX_REFLECTION_NUMBER */
+    uint32_t sampler;              /* ptc_sampler */
+    uint32_t mode;                 /* ptc_mode */
+    uint32_t iterations_per_batch; /* samples per pixel kept in flight per wavefront pass; 0 = auto */
+    uint32_t flags;                /* PTC_FLAG_* */
+    uint32_t reserved;
+    void *stream;                  /* cudaStream_t to launch on; NULL = the library creates its own */
+} ptc_config;
+
+/* What OpenCL_InitializeMemory reads out of GlobalVars (reference Controleur/PathTracer_OpenCL.cpp:165-183). */
+typedef struct ptc_scene_view
+{
+    uint32_t struct_size;
+    uint32_t bvh_size;
+    uint32_t triangulation_size;
+    uint32_t lights_size;
+    uint32_t materiaux_size;
+    uint32_t textures_size;
+    uint32_t textures_data_size;
+    uint32_t reserved;
+    const ptc_node *bvh;               /* bvh[0] is the root */
+    const ptc_triangle *triangulation; /* in BVH order (after BVH_Create permuted it) */
+    const ptc_light *lights;
+    const ptc_material *materiaux;
+    const ptc_texture *textures;
+    const ptc_uchar4 *textures_data;   /* sky faces and scene textures, one flat array */
+    const ptc_sky *sky;
+    ptc_float4 camera_position;
+    ptc_float4 camera_direction;
+    ptc_float4 camera_right;
+    ptc_float4 camera_up;
+} ptc_scene_view;
+
+/* Work and time counters, cumulative since ptc_create / ptc_reset_accumulation. */
+typedef struct ptc_counters
+{
+    uint64_t paths;             /* (pixel, iteration) samples finished */
+    uint64_t extension_rays;    /* closest-hit traversals  (BVH_IntersectRay calls) */
+    uint64_t shadow_rays;       /* any-hit traversals      (BVH_IntersectShadowRay calls) */
+    uint64_t box_tests;         /* BoundingBox_Intersects calls, all rays */
+    uint64_t triangle_tests;    /* Triangle_Intersects calls, all rays */
+    uint64_t kernel_launches;   /* kernels launched by this library */
+    double ms_generate;         /* per-stage device time, only with PTC_FLAG_STAGE_TIMING */
+    double ms_extend;
+    double ms_connect;
+    double ms_shade;
+    double ms_accumulate;
+    uint64_t launches_extend;
+    uint64_t launches_connect;
+    uint64_t scene_bytes_nodes;     /* device bytes of the flattened BVH */
+    uint64_t scene_bytes_triangles; /* device bytes of the intersection records */
+} ptc_counters;
+
+/* Device pointers of the accumulators, for zero-copy collectives (NCCL reduce of per-GPU images). */
+typedef struct ptc_device_buffers
+{
+    void *image_color;  /* float4[W*H]  running sum      (reference global__imageColor) */
+    void *image_ray_nb; /* float [W*H]  running count    (reference global__imageRayNb) */
+    void *image_v;      /* float4[W*H]  variance accumulator (reference global__imageV) or NULL */
+    void *ray_depths;   /* uint32[ray_max_depth+1] */
+    void *ray_bbx;      /* uint32[5000] */
+    void *ray_tri;      /* uint32[5000] */
+    void *stream;       /* cudaStream_t all of the above are written on */
+} ptc_device_buffers;
+
+/* OpenCL_SetupContext: pick the device, allocate image/statistics accumulators (zeroed — the reference
+ * never zeroes them) and the wavefront state. */
+PTC_API int ptc_create(const ptc_config *config, ptc_ctx **out_ctx);
+
+/* OpenCL_InitializeMemory: validate, flatten and upload the scene; set the camera. May be called again
+ * with a new scene (accumulators are kept; call ptc_reset_accumulation to start over). */
+PTC_API int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *scene);
+
+/* New (the reference bakes the camera once): position, direction, right, up. */
+PTC_API int ptc_set_camera(ptc_ctx *ctx, const float camera[16]);
+
+/* Zero imageColor / imageRayNb / imageV / the three histograms and the counters. */
+PTC_API int ptc_reset_accumulation(ptc_ctx *ctx);
+
+/* The body of OpenCL_RunKernel's loop for iterations [first, first+n): enqueue only, returns without
+ * waiting. Iteration numbers select the random streams (header.cl:255-264), so disjoint ranges rendered
+ * by different contexts / GPUs sum to exactly the paths a single run would trace. */
+PTC_API int ptc_render(ptc_ctx *ctx, uint32_t first_iteration, uint32_t n_iterations);
+
+PTC_API int ptc_synchronize(ptc_ctx *ctx);
+
+/* clEnqueueReadBuffer of imageColor / imageRayNb (reference PathTracer_OpenCL.cpp:97-98); waits for
+ * pending renders. Either pointer may be NULL. */
+PTC_API int ptc_read_image(ptc_ctx *ctx, float *image_color, float *image_ray_nb);
+PTC_API int ptc_read_variance(ptc_ctx *ctx, float *image_v);
+
+/* rayDepths[depth+1], rayIntersectedBBx[5000], rayIntersectedTri[5000] (reference :110-112). */
+PTC_API int ptc_read_stats(ptc_ctx *ctx, uint32_t *ray_depths, uint32_t *ray_bbx, uint32_t *ray_tri);
+
+/* Display epilogue on the device: sum/count -> clamp -> 8-bit, restating
+ * reference Alone/PathTracer_bitmap.cpp:259-279 (negative red marks the pixel pure red). 3 bytes per
+ * pixel, R,G,B, row-major, no padding. */
+PTC_API int ptc_read_rgb8(ptc_ctx *ctx, uint8_t *rgb);
+
+/* Resume / multi-GPU merge: add host accumulators into the device ones. */
+PTC_API int ptc_add_image(ptc_ctx *ctx, const float *image_color, const float *image_ray_nb);
+
+PTC_API int ptc_read_counters(ptc_ctx *ctx, ptc_counters *out);
+PTC_API int ptc_get_device_buffers(ptc_ctx *ctx, ptc_device_buffers *out);
+
+/* Parity probe: generate + one closest-hit traversal for every pixel of one iteration, without touching
+ * the accumulators. hit = triangle index in BVH order or -1; st = (s,t); dist2 = squared hit distance;
+ * dir = 4 floats per pixel; seed_after = RNG state after the sampler; counts = (boxes, triangles) tested.
+ * Any pointer may be NULL. */
+PTC_API int ptc_trace_primary(ptc_ctx *ctx, uint32_t iteration, int32_t *hit, float *st, float *dist2, float *dir,
+                              int32_t *seed_after, uint32_t *counts);
+
+/* Parity probe: per-pixel radiance of exactly one iteration (what Kernel_Main adds to imageColor). */
+PTC_API int ptc_render_single(ptc_ctx *ctx, uint32_t iteration, float *radiance);
+
+/* Pinned host memory for read-backs inside timed regions. */
+PTC_API void *ptc_host_alloc(size_t bytes);
+PTC_API void ptc_host_free(void *p);
+
+/* Message of the last failure on this context (or of the last failed ptc_create when ctx is NULL). */
+PTC_API const char *ptc_last_error(const ptc_ctx *ctx);
+PTC_API const char *ptc_version(void);
+PTC_API int ptc_device_count(void);
+
+/* Releases everything OpenCL_RunKernel releases at its end (reference PathTracer_OpenCL.cpp:120-139). */
+PTC_API void ptc_destroy(ptc_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PATHTRACER_CUDA_H */

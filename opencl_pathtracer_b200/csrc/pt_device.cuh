@@ -1,0 +1,145 @@
+// pt_device.cuh — device-side records and launch parameters of the wavefront path tracer.
+//
+// HBM layout (all arrays 256-byte aligned by cudaMalloc, every record a multiple of 16 bytes so that
+// each field group is one LDG.128):
+//   DevNode   64 B  one per INNER node of the reference BVH2: both children's boxes + both child
+//                   references, so one node visit = one 64-byte fetch (reference: 2 x 160-byte Node
+//                   records, Kernel/PathTracer_FullKernel.cl:660-672)
+//   DevTri    64 B  one per triangle, only what Triangle_Intersects needs (reference: a 336-byte copy,
+//                   kernel.cl:640)
+//   DevShade 128 B  one per triangle, what the shade stage needs once per hit (normals, UVs, materials)
+//   DevMaterial 32 B, DevLight 64 B (reference layout), DevTexture 16 B
+// Path state is SoA, indexed by path slot = localIteration * W*H + pixel.
+#pragma once
+
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace ptc
+{
+// child reference word: bit 31 = leaf. inner: index into DevNode[]. leaf: bits 30..4 = first triangle,
+// bits 3..0 = triangle count (1..15), 0 = "big leaf" whose count is bigLeafCount[first].
+constexpr uint32_t kLeafBit = 0x80000000u;
+constexpr uint32_t kMaxTriangles = 1u << 27;
+constexpr uint32_t kInvalidRef = 0xffffffffu;  // empty scene
+
+struct __align__(16) DevNode
+{
+    float4 a;  // L.min.x L.min.y L.min.z L.max.x
+    float4 b;  // L.max.y L.max.z R.min.x R.min.y
+    float4 c;  // R.min.z R.max.x R.max.y R.max.z
+    uint4 d;   // refL refR meta 0      meta: bits 1..0 cutAxis, bit 2 L empty, bit 3 R empty
+};
+static_assert(sizeof(DevNode) == 64, "DevNode");
+
+struct __align__(16) DevTri
+{
+    float4 n;   // N.xyzw (w lane kept: SURVEY.md F8)
+    float4 p;   // S1.xyz, d = dot4(N, S1)
+    float4 e1;  // u = S2 - S1 (xyz), denom = 1 / (uv*uv - uu*vv)
+    float4 e2;  // v = S3 - S1 (xyz), unused
+};
+static_assert(sizeof(DevTri) == 64, "DevTri");
+
+struct __align__(16) DevShade
+{
+    float4 n1, n2, n3;       // vertex normals
+    float4 uvp12;            // UVP1.xy UVP2.xy
+    float4 uvp3_uvn1;        // UVP3.xy UVN1.xy
+    float4 uvn23;            // UVN2.xy UVN3.xy
+    uint4 ids;               // materialWithPositiveNormalIndex, materialWithNegativeNormalIndex, id, 0
+    uint4 pad;
+};
+static_assert(sizeof(DevShade) == 128, "DevShade");
+
+struct __align__(16) DevMaterial
+{
+    float4 color;        // simpleColor
+    float opacity;
+    int textureId;
+    int type;
+    int isSimpleColor;
+};
+static_assert(sizeof(DevMaterial) == 32, "DevMaterial");
+
+struct __align__(16) DevLight
+{
+    float4 position, direction, color;
+    float power, cosInner, cosOuter;
+    int type;
+};
+static_assert(sizeof(DevLight) == 64, "DevLight");
+
+struct DevSky
+{
+    uint32_t w[6], h[6], off[6];
+    float cosRot, sinRot;
+};
+
+struct SceneDev
+{
+    const DevNode *nodes;
+    const DevTri *tris;
+    const DevShade *shade;
+    const DevMaterial *materials;
+    const DevLight *lights;
+    const uint4 *textures;  // width height offset 0
+    const uchar4 *texels;
+    const uint32_t *bigLeafCount;  // may be null
+    uint32_t rootRef;
+    uint32_t nLights;
+    uint32_t nTriangles;
+    DevSky sky;
+};
+
+struct Camera
+{
+    float4 position, direction, right, up;
+};
+
+struct PathState
+{
+    float4 *org;      // ray origin (4 lanes)
+    float4 *dir;      // ray direction (4 lanes, normalised)
+    float4 *thr;      // transferFunction
+    float4 *rad;      // radianceToCompute
+    float4 *hit;      // (bits: triangle index or -1, s, t, tpar)   q = org + dir * tpar
+    int *seed;        // RNG state
+    float2 *sample;   // pixel-plane sample, kept for accumulation (kernel.cl:1333)
+    uint32_t *meta;   // bits 7..0 reflectionId, bit 8 isInWater, bit 9 finished
+    uint32_t *nbbx;   // numIntersectedBBx (camera ray + its shadow rays)
+    uint32_t *ntri;   // numIntersectedTri
+    uint32_t *occl;   // bit i = light i occluded at the current hit
+};
+
+// queue / cursor block, one set per bounce so nothing has to be reset inside a batch
+constexpr int kMaxBounces = 64;
+struct Counters
+{
+    uint32_t qcount[kMaxBounces + 1];     // live paths entering bounce b
+    uint32_t curExtend[kMaxBounces + 1];  // work cursors of the persistent kernels
+    uint32_t curConnect[kMaxBounces + 1];
+    unsigned long long extensionRays, shadowRays, boxTests, triTests, paths;
+};
+
+struct FrameParams
+{
+    uint32_t width, height;
+    uint32_t maxDepth;
+    uint32_t sampler;
+    uint32_t firstIteration;  // of this batch
+    uint32_t nIterations;     // in this batch
+    uint32_t flags;
+};
+
+struct ImageDev
+{
+    float4 *color;
+    float *rayNb;
+    float4 *variance;  // may be null
+    uint32_t *rayDepths;
+    uint32_t *rayBbx;
+    uint32_t *rayTri;
+};
+
+}  // namespace ptc

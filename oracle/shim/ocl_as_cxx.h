@@ -1,0 +1,62 @@
+// TEST INFRASTRUCTURE ONLY — part of the parity oracle, never linked into the product.
+//
+// ocl_as_cxx.h — gives the OpenCL C constructs used by the reference kernel
+// (/root/reference/Kernel/PathTracer_FullKernel.cl + _header.cl) a defined C++17
+// meaning, so that g++ can compile the reference kernel source itself (a generated,
+// mechanically rewritten copy under oracle/_ref/, see oracle/rewrite_cl.py).
+//
+// This header is included INSIDE a namespace by oracle/ref_glue.cpp, once per sampler
+// variant, so that the functions declared here hide the global <cmath> overloads for
+// unqualified calls made by the kernel source.
+//
+// Canonical arithmetic (this file is the spec the CUDA PARITY kernels follow):
+//   dot(float4,float4)   = ((x1*x2 + y1*y2) + z1*z2) + w1*w2          (4 lanes)
+//   length(v)            = sqrtf(dot(v,v))
+//   normalize(v)         = v / length(v)                                (4 IEEE divides)
+//   cross(a,b)           = 3-lane, w = 0
+//   sqrt/cos/sin/exp     = sqrtf / cosf / sinf / expf of the host libm
+//   fmax/fmin/max/min    = IEEE compare-select on floats
+// Build flags that go with it: -O2 -ffp-contract=off -fno-fast-math -fwrapv.
+
+#ifndef OCL_SHIM_TYPES_DEFINED
+#error "include ocl_shim_types.h at global scope first"
+#endif
+
+// ---- scalar helpers -------------------------------------------------------------------
+static inline float sqrt(float x) { return ::sqrtf(x); }
+static inline float cos(float x) { return ::cosf(x); }
+static inline float sin(float x) { return ::sinf(x); }
+static inline float exp(float x) { return ::expf(x); }
+static inline float fabs(float x) { return ::fabsf(x); }
+static inline float fmax(float a, float b) { return ::fmaxf(a, b); }
+static inline float fmin(float a, float b) { return ::fminf(a, b); }
+static inline float max(float a, float b) { return a < b ? b : a; }
+static inline float min(float a, float b) { return b < a ? b : a; }
+
+// ---- vector helpers -------------------------------------------------------------------
+static inline float4 make_float4(float x, float y, float z, float w) { return float4{x, y, z, w}; }
+static inline float4 make_float4(float4 v) { return v; }
+static inline float2 make_float2(float x, float y) { return float2{x, y}; }
+static inline int4 make_int4(int x, int y, int z, int w) { return int4{x, y, z, w}; }
+static inline RGBAColor_t make_RGBAColor(float x, float y, float z, float w) { return float4{x, y, z, w}; }
+
+static inline float dot(float4 a, float4 b) { return ((a.x * b.x + a.y * b.y) + a.z * b.z) + a.w * b.w; }
+static inline float length(float4 a) { return ::sqrtf(dot(a, a)); }
+static inline float4 normalize(float4 a) { float l = length(a); return float4{a.x / l, a.y / l, a.z / l, a.w / l}; }
+static inline float distance(float4 a, float4 b) { return length(a - b); }
+static inline float4 cross(float4 a, float4 b)
+{
+    return float4{a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x, 0.f};
+}
+static inline float4 min(float4 a, float4 b) { return float4{min(a.x, b.x), min(a.y, b.y), min(a.z, b.z), min(a.w, b.w)}; }
+static inline float4 max(float4 a, float4 b) { return float4{max(a.x, b.x), max(a.y, b.y), max(a.z, b.z), max(a.w, b.w)}; }
+static inline int2 min(int2 a, int2 b) { return int2{a.x < b.x ? a.x : b.x, a.y < b.y ? a.y : b.y}; }
+static inline float4 exp(float4 a) { return float4{::expf(a.x), ::expf(a.y), ::expf(a.z), ::expf(a.w)}; }
+static inline float4 convert_float4(uchar4 c) { return float4{(float)c.x, (float)c.y, (float)c.z, (float)c.w}; }
+
+// ---- work-item functions / atomics ----------------------------------------------------
+static inline size_t get_global_id(uint d) { return ocl_shim::gid[d]; }
+static inline size_t get_local_id(uint) { return 0; }
+static inline size_t get_local_size(uint) { return 1; }
+static inline void barrier(int) {}
+static inline uint atomic_inc(uint *p) { return __atomic_fetch_add(p, 1u, __ATOMIC_RELAXED); }
