@@ -1,0 +1,72 @@
+#!/usr/bin/env python3
+"""Builds the native libraries IN-TREE (opencl_pathtracer_b200/_lib/):
+
+  libpathtracer_cuda.so   the product: sm_100a kernels + the C ABI of include/pathtracer_cuda.h
+  libpathtracer_host.so   host-side mirror of the reference interface (importer, BVH builder, controller,
+                          CUDA_* shims) + the pth_* C entry points used by Python
+  pathtracer_alone        headless stand-alone front-end (counterpart of the reference's Alone/main.cpp)
+
+nvcc cross-compiles for sm_100a without a GPU. Bit-exact arithmetic: -fmad=false on the device,
+-ffp-contract=off on the host.
+"""
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+LIB = os.path.join(HERE, "_lib")
+CSRC = os.path.join(HERE, "csrc")
+HOST = os.path.join(HERE, "host")
+INC = os.path.join(ROOT, "include")
+
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-fmad=false", "-std=c++17",
+              "-Xcompiler", "-fPIC,-fopenmp,-ffp-contract=off,-fvisibility=hidden", "-I", INC, "-I", CSRC]
+CXX_FLAGS = ["-std=c++17", "-O2", "-fPIC", "-fopenmp", "-ffp-contract=off", "-fno-fast-math", "-Wall", "-Wno-unknown-pragmas",
+             "-I", INC, "-I", HOST]
+
+
+def _newer(target, sources):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(s) > t for s in sources)
+
+
+def _run(cmd, verbose):
+    if verbose:
+        print(" ".join(cmd), flush=True)
+    subprocess.check_call(cmd)
+
+
+def build(verbose=False, force=False):
+    os.makedirs(LIB, exist_ok=True)
+    cuda_so = os.path.join(LIB, "libpathtracer_cuda.so")
+    headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))] + \
+              [os.path.join(INC, f) for f in os.listdir(INC)]
+    cu = [os.path.join(CSRC, "pt_kernels.cu"), os.path.join(CSRC, "pathtracer_cuda.cu")]
+    if force or _newer(cuda_so, cu + headers + [__file__]):
+        objs = []
+        for src in cu:
+            obj = os.path.join(LIB, os.path.basename(src) + ".o")
+            _run(["nvcc"] + NVCC_FLAGS + ["-c", src, "-o", obj], verbose)
+            objs.append(obj)
+        _run(["nvcc", "-shared", "-o", cuda_so] + objs + ["-Xcompiler", "-fopenmp", "-lgomp"], verbose)
+        for o in objs:
+            os.remove(o)
+    host_so = os.path.join(LIB, "libpathtracer_host.so")
+    host_src = [os.path.join(HOST, f) for f in ("PathTracer_BVH.cpp", "PathTracer_ProceduralImporter.cpp", "PathTracer_CUDA.cpp",
+                                                "PathTracer_Dialog.cpp", "PathTracer.cpp", "pth_capi.cpp")]
+    host_hdr = [os.path.join(HOST, f) for f in os.listdir(HOST) if f.endswith(".h")] + headers
+    if force or _newer(host_so, host_src + host_hdr + [cuda_so, __file__]):
+        _run(["g++"] + CXX_FLAGS + ["-shared", "-o", host_so] + host_src +
+             ["-L", LIB, "-lpathtracer_cuda", "-Wl,-rpath,$ORIGIN"], verbose)
+    exe = os.path.join(LIB, "pathtracer_alone")
+    if force or _newer(exe, [os.path.join(HOST, "main.cpp"), host_so]):
+        _run(["g++"] + CXX_FLAGS + ["-o", exe, os.path.join(HOST, "main.cpp"), "-L", LIB, "-lpathtracer_host", "-lpathtracer_cuda",
+                                    "-Wl,-rpath,$ORIGIN"], verbose)
+    return cuda_so, host_so
+
+
+if __name__ == "__main__":
+    print(build(verbose=True, force="--force" in sys.argv))

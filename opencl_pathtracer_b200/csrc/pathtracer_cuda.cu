@@ -1,0 +1,749 @@
+// pathtracer_cuda.cu — PathTracer_CUDA: implementation of the C ABI declared in include/pathtracer_cuda.h.
+//
+// Replaces the OpenCL context / buffer / launch-loop code of the reference
+// (Controleur/PathTracer_OpenCL.cpp:56-198, :316-402). Host side only: the kernels are in pt_kernels.cu.
+// There is no CPU path in this library: without a CUDA device ptc_create fails.
+#include "pathtracer_cuda.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "pt_launch.h"
+
+using namespace ptc;
+
+namespace
+{
+thread_local std::string g_createError;
+
+struct StageEvent
+{
+    int stage;  // 0 generate, 1 extend, 2 connect, 3 shade, 4 accumulate
+    cudaEvent_t a, b;
+};
+
+template <typename T>
+struct DevBuf
+{
+    T *p = nullptr;
+    size_t n = 0;
+    cudaError_t alloc(size_t count)
+    {
+        release();
+        n = count;
+        if (count == 0) count = 1;  // the reference clamps empty buffers to 1 byte (PathTracer_OpenCL.cpp:165-171)
+        return cudaMalloc((void **)&p, count * sizeof(T));
+    }
+    void release()
+    {
+        if (p) cudaFree(p);
+        p = nullptr;
+        n = 0;
+    }
+};
+}  // namespace
+
+struct ptc_ctx
+{
+    ptc_config cfg{};
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool ownStream = false;
+    bool fast = false;
+    bool sceneLoaded = false;
+    std::string err;
+
+    uint32_t nPix = 0, batchIters = 1;
+    size_t capacity = 0;  // path slots
+    LaunchCfg lc{};
+    int smCount = 0;
+
+    // scene
+    DevBuf<DevNode> nodes;
+    DevBuf<DevTri> tris;
+    DevBuf<DevShade> shade;
+    DevBuf<DevMaterial> materials;
+    DevBuf<DevLight> lights;
+    DevBuf<uint4> textures;
+    DevBuf<uchar4> texels;
+    DevBuf<uint32_t> bigLeaf;
+    SceneDev sc{};
+    Camera cam{};
+
+    // path state + queues
+    DevBuf<float4> org, dir, thr, rad, hit;
+    DevBuf<int> seed;
+    DevBuf<float2> sample;
+    DevBuf<uint32_t> meta, nbbx, ntri, occl, queue[2];
+    PathState st{};
+    DevBuf<Counters> counters;
+
+    // accumulators
+    DevBuf<float4> imgColor, imgV;
+    DevBuf<float> imgRayNb;
+    DevBuf<uint32_t> rayDepths, rayBbx, rayTri;
+    ImageDev img{};
+    DevBuf<uint8_t> rgb8;
+
+    // host-side counters
+    uint64_t launches = 0, launchesExtend = 0, launchesConnect = 0;
+    double msStage[5] = {0, 0, 0, 0, 0};
+    std::vector<StageEvent> pending;
+    std::vector<cudaEvent_t> eventPool;
+};
+
+namespace
+{
+int fail(ptc_ctx *c, int code, const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    if (c) c->err = buf;
+    else g_createError = buf;
+    return code;
+}
+
+#define CK(call)                                                                                              \
+    do                                                                                                        \
+    {                                                                                                         \
+        cudaError_t e__ = (call);                                                                             \
+        if (e__ != cudaSuccess) return fail(ctx, PTC_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e__)); \
+    } while (0)
+
+inline float4 to4(const ptc_float4 &v) { return make_float4(v.x, v.y, v.z, v.w); }
+inline float hdot4(const ptc_float4 &a, const ptc_float4 &b) { return ((a.x * b.x + a.y * b.y) + a.z * b.z) + a.w * b.w; }
+
+cudaEvent_t getEvent(ptc_ctx *c)
+{
+    if (!c->eventPool.empty())
+    {
+        cudaEvent_t e = c->eventPool.back();
+        c->eventPool.pop_back();
+        return e;
+    }
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    return e;
+}
+
+struct StageTimer
+{
+    ptc_ctx *c;
+    StageEvent ev{};
+    bool on;
+    StageTimer(ptc_ctx *ctx, int stage) : c(ctx), on((ctx->cfg.flags & PTC_FLAG_STAGE_TIMING) != 0)
+    {
+        if (!on) return;
+        ev.stage = stage;
+        ev.a = getEvent(c);
+        ev.b = getEvent(c);
+        cudaEventRecord(ev.a, c->stream);
+    }
+    ~StageTimer()
+    {
+        if (!on) return;
+        cudaEventRecord(ev.b, c->stream);
+        c->pending.push_back(ev);
+    }
+};
+
+void drainTimers(ptc_ctx *c)
+{
+    for (auto &e : c->pending)
+    {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, e.a, e.b) == cudaSuccess) c->msStage[e.stage] += ms;
+        c->eventPool.push_back(e.a);
+        c->eventPool.push_back(e.b);
+    }
+    c->pending.clear();
+}
+}  // namespace
+
+// ================================================================================================ create
+extern "C" {
+
+const char *ptc_version(void) { return "PathTracer_CUDA 0.1 (sm_100a)"; }
+
+int ptc_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+
+const char *ptc_last_error(const ptc_ctx *ctx) { return ctx ? ctx->err.c_str() : g_createError.c_str(); }
+
+void *ptc_host_alloc(size_t bytes)
+{
+    void *p = nullptr;
+    if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) return nullptr;
+    return p;
+}
+void ptc_host_free(void *p)
+{
+    if (p) cudaFreeHost(p);
+}
+
+void ptc_destroy(ptc_ctx *ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    drainTimers(ctx);
+    for (auto e : ctx->eventPool) cudaEventDestroy(e);
+    ctx->nodes.release(); ctx->tris.release(); ctx->shade.release(); ctx->materials.release(); ctx->lights.release();
+    ctx->textures.release(); ctx->texels.release(); ctx->bigLeaf.release();
+    ctx->org.release(); ctx->dir.release(); ctx->thr.release(); ctx->rad.release(); ctx->hit.release();
+    ctx->seed.release(); ctx->sample.release(); ctx->meta.release(); ctx->nbbx.release(); ctx->ntri.release();
+    ctx->occl.release(); ctx->queue[0].release(); ctx->queue[1].release(); ctx->counters.release();
+    ctx->imgColor.release(); ctx->imgV.release(); ctx->imgRayNb.release(); ctx->rayDepths.release();
+    ctx->rayBbx.release(); ctx->rayTri.release(); ctx->rgb8.release();
+    if (ctx->ownStream && ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+int ptc_reset_accumulation(ptc_ctx *ctx)
+{
+    if (!ctx) return PTC_ERR_INVALID;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaMemsetAsync(ctx->imgColor.p, 0, sizeof(float4) * ctx->nPix, ctx->stream));
+    CK(cudaMemsetAsync(ctx->imgRayNb.p, 0, sizeof(float) * ctx->nPix, ctx->stream));
+    if (ctx->imgV.p) CK(cudaMemsetAsync(ctx->imgV.p, 0, sizeof(float4) * ctx->nPix, ctx->stream));
+    CK(cudaMemsetAsync(ctx->rayDepths.p, 0, sizeof(uint32_t) * (kMaxBounces + 1), ctx->stream));
+    CK(cudaMemsetAsync(ctx->rayBbx.p, 0, sizeof(uint32_t) * PTC_MAX_INTERSECTION_NUMBER, ctx->stream));
+    CK(cudaMemsetAsync(ctx->rayTri.p, 0, sizeof(uint32_t) * PTC_MAX_INTERSECTION_NUMBER, ctx->stream));
+    CK(cudaMemsetAsync(ctx->counters.p, 0, sizeof(Counters), ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    drainTimers(ctx);
+    ctx->launches = ctx->launchesExtend = ctx->launchesConnect = 0;
+    for (double &m : ctx->msStage) m = 0;
+    return PTC_OK;
+}
+
+int ptc_create(const ptc_config *config, ptc_ctx **out_ctx)
+{
+    ptc_ctx *ctx = nullptr;  // CK() reports into g_createError while ctx is null
+    if (!config || !out_ctx) return fail(nullptr, PTC_ERR_INVALID, "ptc_create: null argument");
+    *out_ctx = nullptr;
+    if (config->struct_size != sizeof(ptc_config)) return fail(nullptr, PTC_ERR_INVALID, "ptc_create: struct_size %u != %zu", config->struct_size, sizeof(ptc_config));
+    if (config->image_width == 0 || config->image_height == 0)
+        return fail(nullptr, PTC_ERR_INVALID, "Image dimensions must be positive");  // reference PathTracer.cpp:147-153
+    if ((uint64_t)config->image_width * config->image_height > (1ull << 28)) return fail(nullptr, PTC_ERR_INVALID, "image too large");
+    if (config->ray_max_depth > (uint32_t)kMaxBounces) return fail(nullptr, PTC_ERR_LIMIT, "ray_max_depth %u exceeds %d", config->ray_max_depth, kMaxBounces);
+    if (config->sampler > 2u || config->mode > 1u) return fail(nullptr, PTC_ERR_INVALID, "unknown sampler or mode");
+    int nDev = 0;
+    if (cudaGetDeviceCount(&nDev) != cudaSuccess || nDev == 0)
+        return fail(nullptr, PTC_ERR_NO_DEVICE, "no CUDA device: PathTracer_CUDA has no CPU path");
+    if (config->device < 0 || config->device >= nDev) return fail(nullptr, PTC_ERR_INVALID, "device %d out of range (%d devices)", config->device, nDev);
+    CK(cudaSetDevice(config->device));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, config->device));
+    if (prop.major < 10) return fail(nullptr, PTC_ERR_NO_DEVICE, "device %d is sm_%d%d; this library is built for sm_100a only", config->device, prop.major, prop.minor);
+
+    ptc_ctx *c = new ptc_ctx();
+    c->cfg = *config;
+    c->device = config->device;
+    c->fast = config->mode == PTC_MODE_FAST;
+    c->nPix = config->image_width * config->image_height;
+    c->smCount = prop.multiProcessorCount;
+    if (config->stream) c->stream = (cudaStream_t)config->stream;
+    else
+    {
+        if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess)
+        {
+            delete c;
+            return fail(nullptr, PTC_ERR_CUDA, "cudaStreamCreate failed");
+        }
+        c->ownStream = true;
+    }
+    // iterations kept in flight per wavefront pass: auto = enough for >= 2M paths
+    uint32_t b = config->iterations_per_batch;
+    if (b == 0) b = ((1u << 21) + c->nPix - 1) / c->nPix;
+    if (b > 64) b = 64;
+    while ((uint64_t)b * c->nPix > (1ull << 30) && b > 1) b--;
+    c->batchIters = b;
+    c->capacity = (size_t)b * c->nPix;
+    c->lc.traverseGrid = c->smCount * traverse_ctas_per_sm(c->fast);
+    c->lc.streamGrid = c->smCount * 8;
+
+    cudaError_t e = cudaSuccess;
+    auto A = [&](cudaError_t r) { if (e == cudaSuccess) e = r; };
+    const size_t n = c->capacity;
+    A(c->org.alloc(n)); A(c->dir.alloc(n)); A(c->thr.alloc(n)); A(c->rad.alloc(n)); A(c->hit.alloc(n));
+    A(c->seed.alloc(n)); A(c->sample.alloc(n)); A(c->meta.alloc(n)); A(c->nbbx.alloc(n)); A(c->ntri.alloc(n));
+    A(c->occl.alloc(n)); A(c->queue[0].alloc(n)); A(c->queue[1].alloc(n)); A(c->counters.alloc(1));
+    A(c->imgColor.alloc(c->nPix)); A(c->imgRayNb.alloc(c->nPix));
+    if (!(config->flags & PTC_FLAG_NO_VARIANCE)) A(c->imgV.alloc(c->nPix));
+    A(c->rayDepths.alloc(kMaxBounces + 1)); A(c->rayBbx.alloc(PTC_MAX_INTERSECTION_NUMBER)); A(c->rayTri.alloc(PTC_MAX_INTERSECTION_NUMBER));
+    if (e != cudaSuccess)
+    {
+        std::string msg = std::string("device allocation failed: ") + cudaGetErrorString(e);
+        ptc_destroy(c);
+        return fail(nullptr, PTC_ERR_CUDA, "%s", msg.c_str());
+    }
+    c->st = PathState{c->org.p, c->dir.p, c->thr.p, c->rad.p, c->hit.p, c->seed.p, c->sample.p, c->meta.p, c->nbbx.p, c->ntri.p, c->occl.p};
+    c->img = ImageDev{c->imgColor.p, c->imgRayNb.p, c->imgV.p, c->rayDepths.p, c->rayBbx.p, c->rayTri.p};
+    // the reference never zeroes its accumulators; this library always does
+    int rc = ptc_reset_accumulation(c);
+    if (rc != PTC_OK)
+    {
+        g_createError = c->err;
+        ptc_destroy(c);
+        return rc;
+    }
+    *out_ctx = c;
+    return PTC_OK;
+}
+
+// ================================================================================================ scene upload
+// Flattening: reference AoS records (include/pathtracer_structs.h) -> packed device records (pt_device.cuh).
+//   * one 64-byte DevNode per INNER node: both children's pMin/pMax + both child references + cutAxis
+//   * one 64-byte DevTri per triangle: N (4 lanes), S1 + d = dot4(N,S1), u + denom, v   (Triangle_Intersects :528-556)
+//   * one 128-byte DevShade per triangle: vertex normals, UVs, material ids
+// d and denom are ray independent; they are computed here with the same IEEE single-precision operations
+// and association order the kernel of the reference uses (this file is compiled without FMA contraction
+// on the host), so the device sees the values the reference would recompute per test.
+int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
+{
+    if (!ctx || !s) return PTC_ERR_INVALID;
+    if (s->struct_size != sizeof(ptc_scene_view)) return fail(ctx, PTC_ERR_INVALID, "ptc_upload_scene: struct_size mismatch");
+    const uint32_t nT = s->triangulation_size, nN = s->bvh_size, nL = s->lights_size, nM = s->materiaux_size, nX = s->textures_size;
+    const uint32_t nTexel = s->textures_data_size;
+    if ((nT && !s->triangulation) || (nN && !s->bvh) || (nL && !s->lights) || (nM && !s->materiaux) || (nX && !s->textures) ||
+        (nTexel && !s->textures_data) || !s->sky)
+        return fail(ctx, PTC_ERR_INVALID, "ptc_upload_scene: null array with non-zero size");
+    if (nL >= PTC_MAX_LIGHT_SIZE)  // reference PathTracer.cpp:60-65
+        return fail(ctx, PTC_ERR_LIMIT, "The scene has too many lights : it has %u and should be under %u", nL, PTC_MAX_LIGHT_SIZE);
+    if (nT >= kMaxTriangles) return fail(ctx, PTC_ERR_LIMIT, "too many triangles (%u, limit %u)", nT, kMaxTriangles);
+    if (nT && nN == 0) return fail(ctx, PTC_ERR_INVALID, "triangles without a BVH");
+    CK(cudaSetDevice(ctx->device));
+
+    // ---- BVH: validate, measure depth, number the inner nodes in array (= depth-first) order
+    std::vector<uint32_t> innerIndex(nN, 0xffffffffu);
+    uint32_t nInner = 0, maxDepth = 0;
+    std::vector<uint32_t> bigLeaf;
+    if (nT)
+    {
+        std::vector<uint8_t> seen(nN, 0);
+        std::vector<std::pair<uint32_t, uint32_t>> stack;  // node, depth
+        stack.push_back({0u, 0u});
+        while (!stack.empty())
+        {
+            auto [id, depth] = stack.back();
+            stack.pop_back();
+            if (id >= nN) return fail(ctx, PTC_ERR_INVALID, "BVH child index %u out of range (%u nodes)", id, nN);
+            if (seen[id]) return fail(ctx, PTC_ERR_INVALID, "BVH node %u reachable twice", id);
+            seen[id] = 1;
+            const ptc_node &n = s->bvh[id];
+            if (n.isLeaf)
+            {
+                if ((uint64_t)n.triangleStartIndex + n.nbTriangles > nT) return fail(ctx, PTC_ERR_INVALID, "BVH leaf %u range out of bounds", id);
+                if (depth > maxDepth) maxDepth = depth;
+            }
+            else
+            {
+                stack.push_back({n.son2Id, depth + 1});
+                stack.push_back({n.son1Id, depth + 1});
+            }
+        }
+        if (maxDepth >= PTC_BVH_MAX_DEPTH)  // reference PathTracer.cpp:54-59
+            return fail(ctx, PTC_ERR_LIMIT, "BVH is too deep : it has a size of %u and should be under %u", maxDepth, PTC_BVH_MAX_DEPTH);
+        for (uint32_t i = 0; i < nN; i++)
+            if (seen[i] && !s->bvh[i].isLeaf) innerIndex[i] = nInner++;
+    }
+    auto childRef = [&](uint32_t id) -> uint32_t {
+        const ptc_node &n = s->bvh[id];
+        if (!n.isLeaf) return innerIndex[id];
+        uint32_t cnt = n.nbTriangles;
+        if (cnt == 0 || cnt > 15)
+        {
+            if (bigLeaf.empty()) bigLeaf.assign(nT + 1, 0u);
+            bigLeaf[n.triangleStartIndex] = cnt;  // a zero-triangle leaf shares its start with another leaf at most when cnt == 0
+            cnt = 0;
+        }
+        return kLeafBit | (n.triangleStartIndex << 4) | cnt;
+    };
+    std::vector<DevNode> hNodes(nInner);
+    uint32_t rootRef = kInvalidRef;
+    if (nT)
+    {
+        // zero-triangle leaves: give them an empty range that cannot alias a real big leaf
+        for (uint32_t i = 0; i < nN; i++)
+        {
+            if (innerIndex[i] == 0xffffffffu) continue;
+            const ptc_node &n = s->bvh[i];
+            const ptc_node &L = s->bvh[n.son1Id], &R = s->bvh[n.son2Id];
+            DevNode d;
+            d.a = make_float4(L.trianglesAABB.pMin.x, L.trianglesAABB.pMin.y, L.trianglesAABB.pMin.z, L.trianglesAABB.pMax.x);
+            d.b = make_float4(L.trianglesAABB.pMax.y, L.trianglesAABB.pMax.z, R.trianglesAABB.pMin.x, R.trianglesAABB.pMin.y);
+            d.c = make_float4(R.trianglesAABB.pMin.z, R.trianglesAABB.pMax.x, R.trianglesAABB.pMax.y, R.trianglesAABB.pMax.z);
+            uint32_t meta = n.cutAxis & 3u;
+            // an empty child box fails BoundingBox_Intersects (:68); a zero-triangle leaf has nothing to test either
+            if (L.trianglesAABB.isEmpty || (L.isLeaf && L.nbTriangles == 0)) meta |= 4u;
+            if (R.trianglesAABB.isEmpty || (R.isLeaf && R.nbTriangles == 0)) meta |= 8u;
+            if (n.cutAxis > 2u) return fail(ctx, PTC_ERR_INVALID, "BVH node %u has cutAxis %u", i, n.cutAxis);
+            d.d = make_uint4((meta & 4u) ? (kLeafBit | 1u) : childRef(n.son1Id), (meta & 8u) ? (kLeafBit | 1u) : childRef(n.son2Id), meta, 0u);
+            hNodes[innerIndex[i]] = d;
+        }
+        const ptc_node &root = s->bvh[0];
+        if (root.isLeaf && root.nbTriangles == 0) rootRef = kInvalidRef;
+        else rootRef = childRef(0);
+    }
+
+    // ---- triangles
+    std::vector<DevTri> hTris(nT);
+    std::vector<DevShade> hShade(nT);
+    int badW = -1, badMat = -1;
+#pragma omp parallel for schedule(static)
+    for (long long i = 0; i < (long long)nT; i++)
+    {
+        const ptc_triangle &t = s->triangulation[i];
+        if (!(t.S1.w == t.S2.w && t.S1.w == t.S3.w)) badW = (int)i;
+        if (t.materialWithPositiveNormalIndex >= nM || t.materialWithNegativeNormalIndex >= nM) badMat = (int)i;
+        const ptc_float4 u = {t.S2.x - t.S1.x, t.S2.y - t.S1.y, t.S2.z - t.S1.z, t.S2.w - t.S1.w};
+        const ptc_float4 v = {t.S3.x - t.S1.x, t.S3.y - t.S1.y, t.S3.z - t.S1.z, t.S3.w - t.S1.w};
+        const float uv = hdot4(u, v), uu = hdot4(u, u), vv = hdot4(v, v);
+        const float denom = 1 / (uv * uv - uu * vv);
+        DevTri d;
+        d.n = to4(t.N);
+        d.p = make_float4(t.S1.x, t.S1.y, t.S1.z, hdot4(t.N, t.S1));
+        d.e1 = make_float4(u.x, u.y, u.z, denom);
+        d.e2 = make_float4(v.x, v.y, v.z, 0.f);
+        hTris[i] = d;
+        DevShade h;
+        h.n1 = to4(t.N1); h.n2 = to4(t.N2); h.n3 = to4(t.N3);
+        h.uvp12 = make_float4(t.UVP1.x, t.UVP1.y, t.UVP2.x, t.UVP2.y);
+        h.uvp3_uvn1 = make_float4(t.UVP3.x, t.UVP3.y, t.UVN1.x, t.UVN1.y);
+        h.uvn23 = make_float4(t.UVN2.x, t.UVN2.y, t.UVN3.x, t.UVN3.y);
+        h.ids = make_uint4(t.materialWithPositiveNormalIndex, t.materialWithNegativeNormalIndex, t.id, 0u);
+        h.pad = make_uint4(0, 0, 0, 0);
+        hShade[i] = h;
+    }
+    if (badW >= 0) return fail(ctx, PTC_ERR_UNSUPPORTED, "triangle %d: S1.w, S2.w, S3.w differ (vertices must share one w lane)", badW);
+    if (badMat >= 0) return fail(ctx, PTC_ERR_INVALID, "triangle %d: material index out of range", badMat);
+
+    // ---- materials, textures, lights, sky
+    std::vector<DevMaterial> hMat(nM);
+    for (uint32_t i = 0; i < nM; i++)
+    {
+        const ptc_material &m = s->materiaux[i];
+        hMat[i].color = to4(m.simpleColor);
+        hMat[i].opacity = m.opacity;
+        hMat[i].textureId = m.textureId;
+        hMat[i].type = m.type;
+        hMat[i].isSimpleColor = m.isSimpleColor ? 1 : 0;
+        if (!m.isSimpleColor && (m.textureId < 0 || (uint32_t)m.textureId >= nX))
+            return fail(ctx, PTC_ERR_INVALID, "material %u: texture index %d out of range", i, m.textureId);
+    }
+    auto texOk = [&](const ptc_texture &t) { return t.width && t.height && (uint64_t)t.offset + (uint64_t)t.width * t.height <= nTexel; };
+    std::vector<uint4> hTex(nX);
+    for (uint32_t i = 0; i < nX; i++)
+    {
+        if (!texOk(s->textures[i])) return fail(ctx, PTC_ERR_INVALID, "texture %u exceeds texturesData", i);
+        hTex[i] = make_uint4(s->textures[i].width, s->textures[i].height, s->textures[i].offset, 0u);
+    }
+    DevSky sky{};
+    for (int f = 0; f < 6; f++)
+    {
+        if (!texOk(s->sky->skyTextures[f])) return fail(ctx, PTC_ERR_INVALID, "sky face %d exceeds texturesData", f);
+        sky.w[f] = s->sky->skyTextures[f].width;
+        sky.h[f] = s->sky->skyTextures[f].height;
+        sky.off[f] = s->sky->skyTextures[f].offset;
+    }
+    sky.cosRot = s->sky->cosRotationAngle;
+    sky.sinRot = s->sky->sinRotationAngle;
+    static_assert(sizeof(DevLight) == sizeof(ptc_light), "Light is uploaded as is");
+
+    // ---- upload (pending renders use the old buffers: wait for them first)
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(ctx->nodes.alloc(nInner)); CK(ctx->tris.alloc(nT)); CK(ctx->shade.alloc(nT)); CK(ctx->materials.alloc(nM));
+    CK(ctx->lights.alloc(nL)); CK(ctx->textures.alloc(nX)); CK(ctx->texels.alloc(nTexel)); CK(ctx->bigLeaf.alloc(bigLeaf.size()));
+    auto up = [&](void *dst, const void *src, size_t bytes) { return bytes ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream) : cudaSuccess; };
+    CK(up(ctx->nodes.p, hNodes.data(), sizeof(DevNode) * nInner));
+    CK(up(ctx->tris.p, hTris.data(), sizeof(DevTri) * nT));
+    CK(up(ctx->shade.p, hShade.data(), sizeof(DevShade) * nT));
+    CK(up(ctx->materials.p, hMat.data(), sizeof(DevMaterial) * nM));
+    CK(up(ctx->lights.p, s->lights, sizeof(DevLight) * nL));
+    CK(up(ctx->textures.p, hTex.data(), sizeof(uint4) * nX));
+    CK(up(ctx->texels.p, s->textures_data, sizeof(uchar4) * nTexel));
+    CK(up(ctx->bigLeaf.p, bigLeaf.data(), sizeof(uint32_t) * bigLeaf.size()));
+    CK(cudaStreamSynchronize(ctx->stream));  // host staging vectors die at return
+
+    SceneDev &sc = ctx->sc;
+    sc.nodes = ctx->nodes.p; sc.tris = ctx->tris.p; sc.shade = ctx->shade.p; sc.materials = ctx->materials.p;
+    sc.lights = ctx->lights.p; sc.textures = ctx->textures.p; sc.texels = ctx->texels.p;
+    sc.bigLeafCount = bigLeaf.empty() ? nullptr : ctx->bigLeaf.p;
+    sc.rootRef = rootRef; sc.nLights = nL; sc.nTriangles = nT; sc.sky = sky;
+    ctx->cam = Camera{to4(s->camera_position), to4(s->camera_direction), to4(s->camera_right), to4(s->camera_up)};
+    ctx->sceneLoaded = true;
+    return PTC_OK;
+}
+
+int ptc_set_camera(ptc_ctx *ctx, const float camera[16])
+{
+    if (!ctx || !camera) return PTC_ERR_INVALID;
+    std::memcpy(&ctx->cam, camera, sizeof(Camera));
+    return PTC_OK;
+}
+
+// ================================================================================================ render
+namespace
+{
+// One wavefront pass over `nIter` iterations starting at `first` (state must hold nIter * nPix slots).
+// accumulate = false leaves the per-path radiance in st.rad (parity probes). maxBounces < 0 = config depth.
+int runBatch(ptc_ctx *ctx, uint32_t first, uint32_t nIter, bool accumulate, int maxBounces)
+{
+    FrameParams fp{};
+    fp.width = ctx->cfg.image_width;
+    fp.height = ctx->cfg.image_height;
+    fp.maxDepth = ctx->cfg.ray_max_depth;
+    fp.sampler = ctx->cfg.sampler;
+    fp.firstIteration = first;
+    fp.nIterations = nIter;
+    fp.flags = ctx->cfg.flags;
+    const uint32_t nPaths = nIter * ctx->nPix;
+    Counters *cn = ctx->counters.p;
+    cudaStream_t s = ctx->stream;
+    launch_reset(s, cn, nPaths);
+    {
+        StageTimer t(ctx, 0);
+        launch_generate(s, ctx->lc, fp, ctx->cam, ctx->st);
+    }
+    ctx->launches += 2;
+    const int depth = maxBounces >= 0 ? maxBounces : (int)fp.maxDepth;
+    for (int b = 0; b < depth; b++)
+    {
+        const uint32_t *qin = b == 0 ? nullptr : ctx->queue[b & 1].p;
+        uint32_t *qout = ctx->queue[(b + 1) & 1].p;
+        {
+            StageTimer t(ctx, 1);
+            launch_extend(s, ctx->lc, ctx->fast, ctx->sc, ctx->st, qin, cn, b);
+        }
+        if (ctx->sc.nLights)
+        {
+            StageTimer t(ctx, 2);
+            launch_connect(s, ctx->lc, ctx->fast, ctx->sc, ctx->st, qin, cn, b);
+            ctx->launches++;
+            ctx->launchesConnect++;
+        }
+        {
+            StageTimer t(ctx, 3);
+            launch_shade(s, ctx->lc, ctx->fast, ctx->sc, fp, ctx->st, qin, qout, cn, b);
+        }
+        ctx->launches += 2;
+        ctx->launchesExtend++;
+    }
+    if (accumulate)
+    {
+        StageTimer t(ctx, 4);
+        launch_accumulate(s, ctx->lc, fp, ctx->st, ctx->img, cn);
+        ctx->launches++;
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(ctx, PTC_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(e));
+    return PTC_OK;
+}
+}  // namespace
+
+int ptc_render(ptc_ctx *ctx, uint32_t first_iteration, uint32_t n_iterations)
+{
+    if (!ctx) return PTC_ERR_INVALID;
+    if (!ctx->sceneLoaded) return fail(ctx, PTC_ERR_STATE, "ptc_render before ptc_upload_scene");
+    CK(cudaSetDevice(ctx->device));
+    uint32_t done = 0;
+    while (done < n_iterations)
+    {
+        const uint32_t n = std::min(ctx->batchIters, n_iterations - done);
+        int rc = runBatch(ctx, first_iteration + done, n, true, -1);
+        if (rc != PTC_OK) return rc;
+        done += n;
+    }
+    return PTC_OK;
+}
+
+int ptc_synchronize(ptc_ctx *ctx)
+{
+    if (!ctx) return PTC_ERR_INVALID;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    drainTimers(ctx);
+    return PTC_OK;
+}
+
+static int readBack(ptc_ctx *ctx, void *dst, const void *src, size_t bytes)
+{
+    if (!dst) return PTC_OK;
+    CK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    return PTC_OK;
+}
+
+int ptc_read_image(ptc_ctx *ctx, float *image_color, float *image_ray_nb)
+{
+    if (!ctx) return PTC_ERR_INVALID;
+    CK(cudaSetDevice(ctx->device));
+    int rc = readBack(ctx, image_color, ctx->imgColor.p, sizeof(float4) * ctx->nPix);
+    if (rc == PTC_OK) rc = readBack(ctx, image_ray_nb, ctx->imgRayNb.p, sizeof(float) * ctx->nPix);
+    if (rc != PTC_OK) return rc;
+    return ptc_synchronize(ctx);
+}
+
+int ptc_read_variance(ptc_ctx *ctx, float *image_v)
+{
+    if (!ctx) return PTC_ERR_INVALID;
+    if (!ctx->imgV.p) return fail(ctx, PTC_ERR_STATE, "context created with PTC_FLAG_NO_VARIANCE");
+    CK(cudaSetDevice(ctx->device));
+    int rc = readBack(ctx, image_v, ctx->imgV.p, sizeof(float4) * ctx->nPix);
+    if (rc != PTC_OK) return rc;
+    return ptc_synchronize(ctx);
+}
+
+int ptc_read_stats(ptc_ctx *ctx, uint32_t *ray_depths, uint32_t *ray_bbx, uint32_t *ray_tri)
+{
+    if (!ctx) return PTC_ERR_INVALID;
+    CK(cudaSetDevice(ctx->device));
+    int rc = readBack(ctx, ray_depths, ctx->rayDepths.p, sizeof(uint32_t) * (ctx->cfg.ray_max_depth + 1));
+    if (rc == PTC_OK) rc = readBack(ctx, ray_bbx, ctx->rayBbx.p, sizeof(uint32_t) * PTC_MAX_INTERSECTION_NUMBER);
+    if (rc == PTC_OK) rc = readBack(ctx, ray_tri, ctx->rayTri.p, sizeof(uint32_t) * PTC_MAX_INTERSECTION_NUMBER);
+    if (rc != PTC_OK) return rc;
+    return ptc_synchronize(ctx);
+}
+
+int ptc_read_rgb8(ptc_ctx *ctx, uint8_t *rgb)
+{
+    if (!ctx || !rgb) return PTC_ERR_INVALID;
+    CK(cudaSetDevice(ctx->device));
+    if (!ctx->rgb8.p) CK(ctx->rgb8.alloc((size_t)3 * ctx->nPix));
+    launch_rgb8(ctx->stream, ctx->img, ctx->nPix, ctx->rgb8.p);
+    ctx->launches++;
+    int rc = readBack(ctx, rgb, ctx->rgb8.p, (size_t)3 * ctx->nPix);
+    if (rc != PTC_OK) return rc;
+    return ptc_synchronize(ctx);
+}
+
+int ptc_add_image(ptc_ctx *ctx, const float *image_color, const float *image_ray_nb)
+{
+    if (!ctx) return PTC_ERR_INVALID;
+    CK(cudaSetDevice(ctx->device));
+    DevBuf<float4> c;
+    DevBuf<float> n;
+    if (image_color)
+    {
+        CK(c.alloc(ctx->nPix));
+        CK(cudaMemcpyAsync(c.p, image_color, sizeof(float4) * ctx->nPix, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    if (image_ray_nb)
+    {
+        CK(n.alloc(ctx->nPix));
+        CK(cudaMemcpyAsync(n.p, image_ray_nb, sizeof(float) * ctx->nPix, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    launch_add_image(ctx->stream, ctx->img, ctx->nPix, c.p, n.p);
+    ctx->launches++;
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    c.release();
+    n.release();
+    if (e != cudaSuccess) return fail(ctx, PTC_ERR_CUDA, "ptc_add_image: %s", cudaGetErrorString(e));
+    return PTC_OK;
+}
+
+int ptc_read_counters(ptc_ctx *ctx, ptc_counters *out)
+{
+    if (!ctx || !out) return PTC_ERR_INVALID;
+    int rc = ptc_synchronize(ctx);
+    if (rc != PTC_OK) return rc;
+    Counters h;
+    CK(cudaMemcpy(&h, ctx->counters.p, sizeof(Counters), cudaMemcpyDeviceToHost));
+    std::memset(out, 0, sizeof(*out));
+    out->paths = h.paths;
+    out->extension_rays = h.extensionRays;
+    out->shadow_rays = h.shadowRays;
+    out->box_tests = h.boxTests;
+    out->triangle_tests = h.triTests;
+    out->kernel_launches = ctx->launches;
+    out->ms_generate = ctx->msStage[0];
+    out->ms_extend = ctx->msStage[1];
+    out->ms_connect = ctx->msStage[2];
+    out->ms_shade = ctx->msStage[3];
+    out->ms_accumulate = ctx->msStage[4];
+    out->launches_extend = ctx->launchesExtend;
+    out->launches_connect = ctx->launchesConnect;
+    out->scene_bytes_nodes = ctx->nodes.n * sizeof(DevNode);
+    out->scene_bytes_triangles = ctx->tris.n * sizeof(DevTri);
+    return PTC_OK;
+}
+
+int ptc_get_device_buffers(ptc_ctx *ctx, ptc_device_buffers *out)
+{
+    if (!ctx || !out) return PTC_ERR_INVALID;
+    out->image_color = ctx->imgColor.p;
+    out->image_ray_nb = ctx->imgRayNb.p;
+    out->image_v = ctx->imgV.p;
+    out->ray_depths = ctx->rayDepths.p;
+    out->ray_bbx = ctx->rayBbx.p;
+    out->ray_tri = ctx->rayTri.p;
+    out->stream = ctx->stream;
+    return PTC_OK;
+}
+
+// ================================================================================================ parity probes
+int ptc_trace_primary(ptc_ctx *ctx, uint32_t iteration, int32_t *hit, float *st, float *dist2, float *dir, int32_t *seed_after,
+                      uint32_t *counts)
+{
+    if (!ctx) return PTC_ERR_INVALID;
+    if (!ctx->sceneLoaded) return fail(ctx, PTC_ERR_STATE, "ptc_trace_primary before ptc_upload_scene");
+    CK(cudaSetDevice(ctx->device));
+    FrameParams fp{};
+    fp.width = ctx->cfg.image_width; fp.height = ctx->cfg.image_height; fp.maxDepth = ctx->cfg.ray_max_depth;
+    fp.sampler = ctx->cfg.sampler; fp.firstIteration = iteration; fp.nIterations = 1; fp.flags = ctx->cfg.flags;
+    const uint32_t n = ctx->nPix;
+    launch_reset(ctx->stream, ctx->counters.p, n);
+    launch_generate(ctx->stream, ctx->lc, fp, ctx->cam, ctx->st);
+    launch_extend(ctx->stream, ctx->lc, ctx->fast, ctx->sc, ctx->st, nullptr, ctx->counters.p, 0);
+    DevBuf<int32_t> dHit, dSeed;
+    DevBuf<float2> dSt;
+    DevBuf<float> dD2;
+    DevBuf<float4> dDir;
+    DevBuf<uint2> dCnt;
+    if (hit) CK(dHit.alloc(n));
+    if (st) CK(dSt.alloc(n));
+    if (dist2) CK(dD2.alloc(n));
+    if (dir) CK(dDir.alloc(n));
+    if (seed_after) CK(dSeed.alloc(n));
+    if (counts) CK(dCnt.alloc(n));
+    launch_probe_primary(ctx->stream, fp, ctx->st, dHit.p, dSt.p, dD2.p, dDir.p, dSeed.p, dCnt.p);
+    ctx->launches += 4;
+    int rc = PTC_OK;
+    if (rc == PTC_OK && hit) rc = readBack(ctx, hit, dHit.p, sizeof(int32_t) * n);
+    if (rc == PTC_OK && st) rc = readBack(ctx, st, dSt.p, sizeof(float2) * n);
+    if (rc == PTC_OK && dist2) rc = readBack(ctx, dist2, dD2.p, sizeof(float) * n);
+    if (rc == PTC_OK && dir) rc = readBack(ctx, dir, dDir.p, sizeof(float4) * n);
+    if (rc == PTC_OK && seed_after) rc = readBack(ctx, seed_after, dSeed.p, sizeof(int32_t) * n);
+    if (rc == PTC_OK && counts) rc = readBack(ctx, counts, dCnt.p, sizeof(uint2) * n);
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    dHit.release(); dSeed.release(); dSt.release(); dD2.release(); dDir.release(); dCnt.release();
+    if (rc != PTC_OK) return rc;
+    if (e != cudaSuccess) return fail(ctx, PTC_ERR_CUDA, "ptc_trace_primary: %s", cudaGetErrorString(e));
+    return PTC_OK;
+}
+
+int ptc_render_single(ptc_ctx *ctx, uint32_t iteration, float *radiance)
+{
+    if (!ctx || !radiance) return PTC_ERR_INVALID;
+    if (!ctx->sceneLoaded) return fail(ctx, PTC_ERR_STATE, "ptc_render_single before ptc_upload_scene");
+    CK(cudaSetDevice(ctx->device));
+    int rc = runBatch(ctx, iteration, 1, false, -1);
+    if (rc != PTC_OK) return rc;
+    rc = readBack(ctx, radiance, ctx->rad.p, sizeof(float4) * ctx->nPix);
+    if (rc != PTC_OK) return rc;
+    return ptc_synchronize(ctx);
+}
+
+}  // extern "C"

@@ -1,0 +1,533 @@
+// pt_kernels.cu — the wavefront stages that replace the reference megakernel Kernel_Main
+// (Kernel/PathTracer_FullKernel.cl:1180-1350). Compiled for sm_100a with -fmad=false (see pt_math.cuh).
+//
+//   k_reset       per-batch queue counters
+//   k_generate    InitializeRandomSeed header.cl:255-264, sampler :1119-1150, camera ray :1208-1215
+//   k_extend      BVH_IntersectRay :620-702          (persistent CTAs, warps pull 32-ray chunks)
+//   k_connect     BVH_IntersectShadowRay :705-783 for every light of Scene_ComputeDirectIllumination :930-948
+//   k_shade       hit setup :1254-1275, direct light sum :901-954, Scene_ComputeRadiance :791-891,
+//                 sky :1281-1288, termination :1248, :1294-1304; ballot-compacts survivors into the next queue
+//   k_accumulate  statistics :1319-1331 and per-pixel accumulation :1333-1349
+#include "pt_launch.h"
+#include "pt_shade.cuh"
+#include "pt_traverse.cuh"
+
+namespace ptc
+{
+constexpr int kTraverseThreads = 128;
+constexpr int kStreamThreads = 256;
+
+// ------------------------------------------------------------------------------------------------ reset
+__global__ void k_reset(Counters *cn, uint32_t nPaths)
+{
+    const int i = threadIdx.x;
+    if (i <= kMaxBounces)
+    {
+        cn->qcount[i] = i == 0 ? nPaths : 0u;
+        cn->curExtend[i] = 0;
+        cn->curConnect[i] = 0;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ generate
+// slot k = localIteration * W*H + pixel; bounce 0 uses the identity queue (queue == nullptr).
+__global__ void __launch_bounds__(kStreamThreads) k_generate(FrameParams fp, Camera cam, PathState st)
+{
+    const uint32_t nPix = fp.width * fp.height;
+    const uint32_t total = nPix * fp.nIterations;
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < total; k += gridDim.x * blockDim.x)
+    {
+        const uint32_t li = k / nPix, pix = k - li * nPix;
+        const uint32_t y = pix / fp.width, x = pix - y * fp.width;
+        const uint32_t iter = fp.firstIteration + li;
+        int seed = rng_init(x, y, iter, fp.width, fp.height);
+        float sx, sy;
+        if (fp.sampler == 2)
+        {
+            // SAMPLE_UNIFORM :1124-1135
+            const int sampleId = (int)(iter % 9u);
+            float ox = (float)(sampleId % 3), oy = (float)(sampleId / 3);
+            ox += 0.5f; oy += 0.5f;
+            ox /= 3.f; oy /= 3.f;
+            sx = (float)x + ox; sy = (float)y + oy;
+            sx /= (float)fp.width; sy /= (float)fp.height;
+            sx -= 0.5f; sy -= 0.5f;
+        }
+        else if (fp.sampler == 1)
+        {
+            // SAMPLE_RANDOM :1138-1141
+            sx = rng_next(seed); sy = rng_next(seed);
+            sx *= 0.9f; sy *= 0.9f;
+            sx += 0.05f; sy += 0.05f;
+            sx -= 0.5f; sy -= 0.5f;
+        }
+        else
+        {
+            // SAMPLE_JITTERED :1145-1146
+            sx = ((float)x + 0.9f * rng_next(seed) + 0.05f) / ((float)fp.width) - 0.5f;
+            sy = ((float)y + 0.9f * rng_next(seed) + 0.05f) / ((float)fp.height) - 0.5f;
+        }
+        const float4 shot = cam.direction + (cam.right * sx) + (cam.up * sy);  // :1213
+        st.org[k] = cam.position;
+        st.dir[k] = normalize4(shot);
+        st.thr[k] = f4(1, 1, 1, 1);
+        st.rad[k] = f4(0, 0, 0, 0);
+        st.seed[k] = seed;
+        st.sample[k] = make_float2(sx, sy);
+        st.meta[k] = 0;
+        st.nbbx[k] = 0;
+        st.ntri[k] = 0;
+        st.occl[k] = 0;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ traversal
+// Persistent kernels: each warp pulls chunks of 32 queue entries from a global cursor until the queue of
+// this bounce is exhausted; per-thread traversal stacks live in shared memory, laid out [level][thread].
+__device__ __forceinline__ bool fetch_chunk(uint32_t *cursor, uint32_t count, uint32_t &base)
+{
+    const unsigned lane = threadIdx.x & 31u;
+    uint32_t b = 0;
+    if (lane == 0) b = atomicAdd(cursor, 32u);
+    base = __shfl_sync(0xffffffffu, b, 0);
+    return base < count;
+}
+
+__device__ __forceinline__ void flush_work(Counters *cn, unsigned long long *rayCounter, uint32_t nRays, uint32_t nb, uint32_t nt)
+{
+    for (int o = 16; o; o >>= 1)
+    {
+        nb += __shfl_xor_sync(0xffffffffu, nb, o);
+        nt += __shfl_xor_sync(0xffffffffu, nt, o);
+        nRays += __shfl_xor_sync(0xffffffffu, nRays, o);
+    }
+    if ((threadIdx.x & 31u) == 0 && nRays)
+    {
+        atomicAdd(rayCounter, (unsigned long long)nRays);
+        atomicAdd(&cn->boxTests, (unsigned long long)nb);
+        atomicAdd(&cn->triTests, (unsigned long long)nt);
+    }
+}
+
+template <bool FAST>
+__global__ void __launch_bounds__(kTraverseThreads) k_extend(SceneDev sc, PathState st, const uint32_t *__restrict__ queue,
+                                                            Counters *__restrict__ cn, int bounce)
+{
+    extern __shared__ uint32_t smemStack[];
+    uint32_t *stk = smemStack + threadIdx.x;
+    const uint32_t count = cn->qcount[bounce];
+    uint32_t nbSum = 0, ntSum = 0, nRays = 0;
+    uint32_t base;
+    while (fetch_chunk(&cn->curExtend[bounce], count, base))
+    {
+        const uint32_t k = base + (threadIdx.x & 31u);
+        if (k < count)
+        {
+            const uint32_t p = queue ? queue[k] : k;
+            const Ray r = make_ray(st.org[p], st.dir[p]);
+            int tri = -1;
+            float hs = 0.f, ht = 0.f, htp = 0.f;
+            uint32_t nb = 0, nt = 0;
+            traverse<false, FAST>(sc, r, INFINITY, tri, hs, ht, htp, nb, nt, stk, kTraverseThreads);
+            st.hit[p] = f4(__int_as_float(tri), hs, ht, htp);
+            st.nbbx[p] += nb;
+            st.ntri[p] += nt;
+            nbSum += nb; ntSum += nt; nRays++;
+        }
+    }
+    flush_work(cn, &cn->extensionRays, nRays, nbSum, ntSum);
+}
+
+template <bool FAST>
+__global__ void __launch_bounds__(kTraverseThreads) k_connect(SceneDev sc, PathState st, const uint32_t *__restrict__ queue,
+                                                             Counters *__restrict__ cn, int bounce)
+{
+    extern __shared__ uint32_t smemStack[];
+    uint32_t *stk = smemStack + threadIdx.x;
+    const uint32_t count = cn->qcount[bounce];
+    uint32_t nbSum = 0, ntSum = 0, nRays = 0;
+    uint32_t base;
+    while (fetch_chunk(&cn->curConnect[bounce], count, base))
+    {
+        const uint32_t k = base + (threadIdx.x & 31u);
+        if (k >= count) continue;
+        const uint32_t p = queue ? queue[k] : k;
+        const float4 h = st.hit[p];
+        const int htri = __float_as_int(h.x);
+        if (htri < 0) continue;  // miss: no direct lighting
+        const float4 o = st.org[p], d = st.dir[p];
+        const float4 q = f4(o.x + d.x * h.w, o.y + d.y * h.w, o.z + d.z * h.w, o.w + d.w * h.w);  // :538
+        uint32_t occl = 0, nb = 0, nt = 0;
+        bool lit = true;
+        if (FAST)
+        {
+            // GLASS / WATER / METAL / UNKNOWN never read the direct light (:805-843): their shadow rays
+            // cannot change the image and are not traced
+            const float4 n = __ldg(&sc.tris[htri].n);
+            const uint4 ids = __ldg(&sc.shade[htri].ids);
+            const int mtype = sc.materials[dot4(n, d) < 0 ? ids.x : ids.y].type;
+            lit = (mtype == 0 || mtype == 3);
+        }
+        if (lit)
+            for (uint32_t li = 0; li < sc.nLights; li++)
+            {
+                float4 ldir;
+                float bound;
+                shadow_setup(sc.lights[li], q, ldir, bound);
+                const Ray r = make_ray(q, ldir);
+                int tri;
+                float hs, ht, htp;
+                if (traverse<true, FAST>(sc, r, bound, tri, hs, ht, htp, nb, nt, stk, kTraverseThreads)) occl |= 1u << li;
+                nRays++;
+            }
+        st.occl[p] = occl;
+        st.nbbx[p] += nb;  // :946-947 the camera ray inherits its shadow rays' counters
+        st.ntri[p] += nt;
+        nbSum += nb; ntSum += nt;
+    }
+    flush_work(cn, &cn->shadowRays, nRays, nbSum, ntSum);
+}
+
+// ------------------------------------------------------------------------------------------------ shade
+template <bool FAST>
+__global__ void __launch_bounds__(kStreamThreads) k_shade(SceneDev sc, FrameParams fp, PathState st, const uint32_t *__restrict__ qin,
+                                                         uint32_t *__restrict__ qout, Counters *__restrict__ cn, int bounce)
+{
+    const uint32_t count = cn->qcount[bounce];
+    const uint32_t stride = blockDim.x * gridDim.x;
+    const uint32_t rounds = (count + stride - 1) / stride;
+    for (uint32_t it = 0; it < rounds; it++)
+    {
+        const uint32_t k = it * stride + blockIdx.x * blockDim.x + threadIdx.x;
+        bool alive = false;
+        uint32_t p = 0;
+        if (k < count)
+        {
+            p = qin ? qin[k] : k;
+            const float4 o = st.org[p], d = st.dir[p], h = st.hit[p];
+            float4 T = st.thr[p], rad = st.rad[p];
+            uint32_t meta = st.meta[p];
+            const int tri = __float_as_int(h.x);
+            if (tri < 0)
+            {
+                // :1281-1288 sky
+                rad = rad + sky_color(sc, d) * T;
+                st.rad[p] = rad;
+            }
+            else
+            {
+                int seed = st.seed[p];
+                const float s = h.y, t = h.z;
+                const float4 q = f4(o.x + d.x * h.w, o.y + d.y * h.w, o.z + d.z * h.w, o.w + d.w * h.w);
+                const float4 N = __ldg(&sc.tris[tri].n);
+                const DevShade *sh = &sc.shade[tri];
+                const float nd = dot4(N, d);
+                const bool positive = nd < 0;  // :568
+                const uint4 ids = __ldg(&sh->ids);
+                const DevMaterial mat = sc.materials[positive ? ids.x : ids.y];
+                // :591-602 surface colour of the final hit
+                float4 color;
+                if (mat.isSimpleColor) color = mat.color;
+                else
+                {
+                    const float4 a = __ldg(&sh->uvp12), b = __ldg(&sh->uvp3_uvn1), c = __ldg(&sh->uvn23);
+                    const float w0 = 1 - s - t;
+                    float tu, tv;
+                    if (positive) { tu = (a.x * w0 + a.z * s) + b.x * t; tv = (a.y * w0 + a.w * s) + b.y * t; }
+                    else { tu = (b.z * w0 + c.x * s) + c.z * t; tv = (b.w * w0 + c.y * s) + c.w * t; }
+                    const uint4 tx = __ldg(&sc.textures[mat.textureId]);
+                    color = texture_lookup(sc, tx.x, tx.y, tx.z, tu, tv);
+                }
+                // :1267-1274 normals
+                const bool same = dot4(d, N) > 0;
+                const float4 Ng = same ? -N : N;
+                const float4 n1 = __ldg(&sh->n1), n2 = __ldg(&sh->n2), n3 = __ldg(&sh->n3);
+                float4 Ns = normalize4((n2 * s) + (n3 * t) + (n1 * (1 - s - t)));
+                if (same) Ns = -Ns;
+                put_in_same_hemisphere(Ns, -d);
+                Ns = normalize4(Ns);
+                // :901-954 direct illumination from the occlusion bits the connect stage left
+                float4 L = f4(0, 0, 0, 0);
+                const uint32_t occl = st.occl[p];
+                if (!FAST || mat.type == 0 || mat.type == 3)
+                    for (uint32_t li = 0; li < sc.nLights; li++)
+                    {
+                        const DevLight l = sc.lights[li];
+                        const float4 full = (l.type == 0) ? -l.direction : (l.position - q);
+                        const float4 ldir = normalize4(full);
+                        const float brdf = material_brdf(mat.type, -ldir, Ns, d);
+                        if (!((occl >> li) & 1u)) L = L + (light_power_toward(l, q, Ns) * brdf) * l.color;
+                    }
+                // :791-891
+                float4 Nref = d, out = d;
+                float4 add = f4(0, 0, 0, 0);
+                bool inWater = (meta >> 8) & 1u;
+                if (mat.type == 0)
+                {
+                    T = T * color;
+                    add = L * T;
+                    out = cosine_sample_hemisphere(seed, Ns);
+                    Nref = Ns;
+                }
+                else if (mat.type == 2)
+                {
+                    float cos2;
+                    const float cos1 = -dot4(d, Ns);
+                    const float rF = fresnel(1, 1.55f, cos1, cos2);
+                    if (rng_next(seed) < rF) { out = d - (Ns * (2 * dot4(d, Ns))); Nref = Ng; }
+                    else { T = T * (color * (1 - mat.opacity)); Nref = d; }
+                }
+                else if (mat.type == 1)
+                {
+                    const float n1w = inWater ? 1.333f : 1.f, n2w = inWater ? 1.f : 1.333f;
+                    float cos2;
+                    const float cos1 = -dot4(d, Ns);
+                    const float rF = fresnel(n1w, n2w, cos1, cos2);
+                    // on total reflection the reference leaves refractedDirection unset and never reads it
+                    const float4 refr = d * (n1w / n2w) + Ns * (n1w / n2w * cos1 - cos2);
+                    const float coeff = (n2w * n2w) / (n1w * n1w);
+                    if (rng_next(seed) < rF) { out = d - (Ns * (2 * dot4(d, Ns))); Nref = Ng; }
+                    else { inWater = !inWater; out = refr; Nref = -Ng; T = T * coeff; }
+                }
+                else if (mat.type == 3)
+                {
+                    add = add + L * color * T;
+                    const float rF = fresnel_varnish(d, Ns);
+                    if (rng_next(seed) < rF) out = d - (Ns * (2 * dot4(d, Ns)));
+                    else { out = cosine_sample_hemisphere(seed, Ns); T = T * color; }
+                }
+                put_in_same_hemisphere(out, Nref);
+                rad = rad + add;
+                const uint32_t refl = (meta & 0xffu) + 1u;
+                meta = refl | (inWater ? 0x100u : 0u);
+                st.org[p] = q + 0.001f * out;  // :880
+                st.dir[p] = normalize4(out);
+                st.thr[p] = T;
+                st.rad[p] = rad;
+                st.seed[p] = seed;
+                st.meta[p] = meta;
+                // :1294-1304 and the loop condition :1248
+                alive = !(clmax(T.x, clmax(T.y, T.z)) <= 0.001f) && refl < fp.maxDepth;
+            }
+        }
+        // warp-aggregated append of the survivors to the next bounce's queue
+        const unsigned m = __ballot_sync(0xffffffffu, alive);
+        if (m)
+        {
+            const unsigned lane = threadIdx.x & 31u;
+            const int leader = __ffs(m) - 1;
+            uint32_t base = 0;
+            if ((int)lane == leader) base = atomicAdd(&cn->qcount[bounce + 1], (uint32_t)__popc(m));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (alive) qout[base + __popc(m & ((1u << lane) - 1u))] = p;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ accumulate
+// :1333-1336 — the double-precision literal 0.5 makes this a double computation in the reference
+__device__ __forceinline__ uint32_t target_pixel(float2 sample, uint32_t W, uint32_t H)
+{
+    int px = (int)(((double)sample.x + 0.5) * (double)(int)W);
+    int py = (int)(((double)sample.y + 0.5) * (double)(int)H);
+    px = px < (int)W - 1 ? px : (int)W - 1;
+    py = py < (int)H - 1 ? py : (int)H - 1;
+    return (uint32_t)(py * (int)W + px);
+}
+
+// :1339-1349 on one pixel (plain read-modify-write: the caller owns the pixel)
+__device__ __forceinline__ void add_sample(const ImageDev &img, uint32_t pix, float4 x, uint32_t iteration)
+{
+    const float4 sumBefore = img.color[pix];
+    const float4 sumAfter = sumBefore + x;
+    const float nBefore = img.rayNb[pix];
+    const float nAfter = nBefore + 1.f;
+    img.rayNb[pix] = nAfter;
+    img.color[pix] = sumAfter;
+    if (img.variance)
+    {
+        if (iteration == 0) img.variance[pix] = f4(0, 0, 0, 0);
+        else img.variance[pix] = img.variance[pix] + (x - sumBefore / nBefore) * (x - sumAfter / nAfter);
+    }
+}
+
+__device__ __forceinline__ void add_sample_atomic(const ImageDev &img, uint32_t pix, float4 x)
+{
+    float *c = reinterpret_cast<float *>(img.color + pix);
+    atomicAdd(c + 0, x.x); atomicAdd(c + 1, x.y); atomicAdd(c + 2, x.z); atomicAdd(c + 3, x.w);
+    atomicAdd(img.rayNb + pix, 1.f);
+}
+
+// :1319-1331; the depth histogram (<= 65 bins) is privatised in shared memory
+__device__ __forceinline__ void count_path(const ImageDev &img, uint32_t *sDepth, uint32_t meta, uint32_t nb, uint32_t nt)
+{
+    atomicAdd(&sDepth[meta & 0xffu], 1u);
+    if (nb < 5000u) atomicAdd(&img.rayBbx[nb], 1u);
+    if (nt < 5000u) atomicAdd(&img.rayTri[nt], 1u);
+}
+
+// ORDERED (jittered / uniform samplers: a path lands in its own pixel): one thread per pixel adds the
+// iterations of the batch in iteration order, so sums are bit-identical to the reference's sequential loop.
+// Otherwise (SAMPLE_RANDOM scatters to arbitrary pixels; the reference races there): atomics.
+template <bool ORDERED>
+__global__ void __launch_bounds__(kStreamThreads) k_accumulate(FrameParams fp, PathState st, ImageDev img, Counters *cn)
+{
+    __shared__ uint32_t sDepth[kMaxBounces + 1];
+    for (int i = threadIdx.x; i <= kMaxBounces; i += blockDim.x) sDepth[i] = 0;
+    __syncthreads();
+    const uint32_t nPix = fp.width * fp.height;
+    uint32_t nPaths = 0;
+    if (ORDERED)
+    {
+        for (uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x; pix < nPix; pix += gridDim.x * blockDim.x)
+            for (uint32_t li = 0; li < fp.nIterations; li++)
+            {
+                const uint32_t k = li * nPix + pix;
+                const float4 x = st.rad[k];
+                const uint32_t tp = target_pixel(st.sample[k], fp.width, fp.height);
+                count_path(img, sDepth, st.meta[k], st.nbbx[k], st.ntri[k]);
+                if (tp == pix) add_sample(img, pix, x, fp.firstIteration + li);
+                else add_sample_atomic(img, tp, x);
+                nPaths++;
+            }
+    }
+    else
+    {
+        const uint32_t total = nPix * fp.nIterations;
+        for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < total; k += gridDim.x * blockDim.x)
+        {
+            count_path(img, sDepth, st.meta[k], st.nbbx[k], st.ntri[k]);
+            add_sample_atomic(img, target_pixel(st.sample[k], fp.width, fp.height), st.rad[k]);
+            nPaths++;
+        }
+    }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i <= fp.maxDepth && i <= (uint32_t)kMaxBounces; i += blockDim.x)
+        if (sDepth[i]) atomicAdd(&img.rayDepths[i], sDepth[i]);
+    for (int o = 16; o; o >>= 1) nPaths += __shfl_xor_sync(0xffffffffu, nPaths, o);
+    if ((threadIdx.x & 31u) == 0 && nPaths) atomicAdd(&cn->paths, (unsigned long long)nPaths);
+}
+
+// ------------------------------------------------------------------------------------------------ probes / epilogues
+__global__ void k_probe_primary(FrameParams fp, PathState st, int32_t *hit, float2 *stOut, float *dist2, float4 *dir,
+                                int32_t *seedAfter, uint2 *counts)
+{
+    const uint32_t nPix = fp.width * fp.height;
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < nPix; k += gridDim.x * blockDim.x)
+    {
+        const float4 h = st.hit[k], o = st.org[k], d = st.dir[k];
+        const int tri = __float_as_int(h.x);
+        if (hit) hit[k] = tri;
+        if (stOut) stOut[k] = tri < 0 ? make_float2(0.f, 0.f) : make_float2(h.y, h.z);
+        if (dist2)
+        {
+            // |q - origin|^2 exactly as Triangle_Intersects forms it (:538-541)
+            const float4 q = f4(o.x + d.x * h.w, o.y + d.y * h.w, o.z + d.z * h.w, o.w + d.w * h.w);
+            const float4 f = q - o;
+            dist2[k] = tri < 0 ? INFINITY : dot4(f, f);
+        }
+        if (dir) dir[k] = d;
+        if (seedAfter) seedAfter[k] = st.seed[k];
+        if (counts) counts[k] = make_uint2(st.nbbx[k], st.ntri[k]);
+    }
+}
+
+// reference Alone/PathTracer_bitmap.cpp:259-279 (its test reads .x three times; a negative red marks the pixel)
+__global__ void k_rgb8(ImageDev img, uint32_t nPixels, uint8_t *rgb)
+{
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < nPixels; p += gridDim.x * blockDim.x)
+    {
+        const float4 c = img.color[p];
+        const float n = img.rayNb[p];
+        int r, g, b;
+        if (c.x < 0) { r = 255; g = 0; b = 0; }
+        else
+        {
+            r = (int)fminf(c.x * 255.f / n, 255.f);
+            g = (int)fminf(c.y * 255.f / n, 255.f);
+            b = (int)fminf(c.z * 255.f / n, 255.f);
+        }
+        rgb[3 * p + 0] = (uint8_t)r;
+        rgb[3 * p + 1] = (uint8_t)g;
+        rgb[3 * p + 2] = (uint8_t)b;
+    }
+}
+
+__global__ void k_add_image(ImageDev img, uint32_t nPixels, const float4 *color, const float *rayNb)
+{
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < nPixels; p += gridDim.x * blockDim.x)
+    {
+        if (color) img.color[p] = img.color[p] + color[p];
+        if (rayNb) img.rayNb[p] = img.rayNb[p] + rayNb[p];
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ launchers
+static const size_t kStackBytes = (size_t)kStackDepth * kTraverseThreads * sizeof(uint32_t);
+
+int traverse_ctas_per_sm(bool fast)
+{
+    int n = 0, m = 0;
+    if (fast)
+    {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_extend<true>, kTraverseThreads, kStackBytes);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&m, k_connect<true>, kTraverseThreads, kStackBytes);
+    }
+    else
+    {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_extend<false>, kTraverseThreads, kStackBytes);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&m, k_connect<false>, kTraverseThreads, kStackBytes);
+    }
+    n = n < m ? n : m;
+    return n < 1 ? 1 : n;
+}
+
+void launch_reset(cudaStream_t s, Counters *cn, uint32_t nPaths) { k_reset<<<1, 128, 0, s>>>(cn, nPaths); }
+
+void launch_generate(cudaStream_t s, const LaunchCfg &lc, const FrameParams &fp, const Camera &cam, const PathState &st)
+{
+    k_generate<<<lc.streamGrid, kStreamThreads, 0, s>>>(fp, cam, st);
+}
+
+void launch_extend(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const PathState &st, const uint32_t *queue,
+                   Counters *cn, int bounce)
+{
+    if (fast) k_extend<true><<<lc.traverseGrid, kTraverseThreads, kStackBytes, s>>>(sc, st, queue, cn, bounce);
+    else k_extend<false><<<lc.traverseGrid, kTraverseThreads, kStackBytes, s>>>(sc, st, queue, cn, bounce);
+}
+
+void launch_connect(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const PathState &st, const uint32_t *queue,
+                    Counters *cn, int bounce)
+{
+    if (fast) k_connect<true><<<lc.traverseGrid, kTraverseThreads, kStackBytes, s>>>(sc, st, queue, cn, bounce);
+    else k_connect<false><<<lc.traverseGrid, kTraverseThreads, kStackBytes, s>>>(sc, st, queue, cn, bounce);
+}
+
+void launch_shade(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const FrameParams &fp, const PathState &st,
+                  const uint32_t *qin, uint32_t *qout, Counters *cn, int bounce)
+{
+    if (fast) k_shade<true><<<lc.streamGrid, kStreamThreads, 0, s>>>(sc, fp, st, qin, qout, cn, bounce);
+    else k_shade<false><<<lc.streamGrid, kStreamThreads, 0, s>>>(sc, fp, st, qin, qout, cn, bounce);
+}
+
+void launch_accumulate(cudaStream_t s, const LaunchCfg &lc, const FrameParams &fp, const PathState &st, const ImageDev &img,
+                       Counters *cn)
+{
+    if (fp.sampler == 1) k_accumulate<false><<<lc.streamGrid, kStreamThreads, 0, s>>>(fp, st, img, cn);
+    else k_accumulate<true><<<lc.streamGrid, kStreamThreads, 0, s>>>(fp, st, img, cn);
+}
+
+void launch_probe_primary(cudaStream_t s, const FrameParams &fp, const PathState &st, int32_t *hit, float2 *stOut, float *dist2,
+                          float4 *dir, int32_t *seedAfter, uint2 *counts)
+{
+    k_probe_primary<<<1024, 256, 0, s>>>(fp, st, hit, stOut, dist2, dir, seedAfter, counts);
+}
+
+void launch_rgb8(cudaStream_t s, const ImageDev &img, uint32_t nPixels, uint8_t *rgb) { k_rgb8<<<1024, 256, 0, s>>>(img, nPixels, rgb); }
+
+void launch_add_image(cudaStream_t s, const ImageDev &img, uint32_t nPixels, const float4 *color, const float *rayNb)
+{
+    k_add_image<<<1024, 256, 0, s>>>(img, nPixels, color, rayNb);
+}
+
+}  // namespace ptc

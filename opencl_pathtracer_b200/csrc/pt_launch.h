@@ -1,0 +1,33 @@
+// pt_launch.h — host-callable launchers of the wavefront stages (defined in pt_kernels.cu).
+#pragma once
+
+#include "pt_device.cuh"
+
+namespace ptc
+{
+struct LaunchCfg
+{
+    int traverseGrid;  // persistent extend / connect CTAs (multiple of the SM count)
+    int streamGrid;    // grid of the streaming stages (generate / shade / accumulate)
+};
+
+int traverse_ctas_per_sm(bool fast);
+
+void launch_reset(cudaStream_t s, Counters *cn, uint32_t nPaths);
+void launch_generate(cudaStream_t s, const LaunchCfg &lc, const FrameParams &fp, const Camera &cam, const PathState &st);
+void launch_extend(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const PathState &st, const uint32_t *queue,
+                   Counters *cn, int bounce);
+void launch_connect(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const PathState &st, const uint32_t *queue,
+                    Counters *cn, int bounce);
+void launch_shade(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const FrameParams &fp, const PathState &st,
+                  const uint32_t *qin, uint32_t *qout, Counters *cn, int bounce);
+void launch_accumulate(cudaStream_t s, const LaunchCfg &lc, const FrameParams &fp, const PathState &st, const ImageDev &img,
+                       Counters *cn);
+// parity probes
+void launch_probe_primary(cudaStream_t s, const FrameParams &fp, const PathState &st, int32_t *hit, float2 *stOut, float *dist2,
+                          float4 *dir, int32_t *seedAfter, uint2 *counts);
+// display epilogue: sum / count -> clamp -> 8 bit (reference Alone/PathTracer_bitmap.cpp:259-279)
+void launch_rgb8(cudaStream_t s, const ImageDev &img, uint32_t nPixels, uint8_t *rgb);
+void launch_add_image(cudaStream_t s, const ImageDev &img, uint32_t nPixels, const float4 *color, const float *rayNb);
+
+}  // namespace ptc

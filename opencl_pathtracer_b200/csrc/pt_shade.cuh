@@ -1,0 +1,166 @@
+// pt_shade.cuh — per-hit shading arithmetic of the shade stage (compiled with -fmad=false).
+//
+// Reference functions restated here (Kernel/PathTracer_FullKernel.cl unless noted):
+//   texture_lookup            Texture_GetPixelColorValue  header.cl:430-459
+//   sky_color                 Sky_GetColorValue / Sky_GetFaceColorValue :438-512
+//   fresnel, fresnel_varnish  Material_Fresnel*ReflectionFraction :192-292
+//   material_brdf             Material_BRDF :166-190
+//   light_power_toward        Light_PowerToward header.cl:403-421
+//   concentric_sample_disk    Material_ConcentricSampleDisk :339-416
+//   cosine_sample_hemisphere  Material_CosineSampleHemisphere :303-336
+#pragma once
+
+#include "pt_device.cuh"
+#include "pt_math.cuh"
+
+namespace ptc
+{
+constexpr float kPi = 3.14159265f;  // PATH_PI
+constexpr float kPiInv = 0.31830988618f;
+
+// nearest texel, wrap by truncation, alpha inverted
+__device__ __forceinline__ float4 texture_lookup(const SceneDev &sc, uint32_t w, uint32_t h, uint32_t off, float u, float v)
+{
+    u = u - ((int)u) + (u < 0 ? 1 : 0);
+    v = v - ((int)v) + (v < 0 ? 1 : 0);
+    const uint32_t x = (uint32_t)(u * (w - 1));
+    const uint32_t y = (uint32_t)(v * (h - 1));
+    const uchar4 c = __ldg(&sc.texels[off + y * w + x]);
+    float4 bgra = f4((float)c.x, (float)c.y, (float)c.z, (float)c.w) / 255.f;
+    bgra.w = 1.f - bgra.w;
+    return bgra;
+}
+
+__device__ __forceinline__ float4 sky_color(const SceneDev &sc, float4 dir)
+{
+    const float x = sc.sky.cosRot * dir.x - sc.sky.sinRot * dir.y;
+    const float y = sc.sky.sinRot * dir.x + sc.sky.cosRot * dir.y;
+    const float z = dir.z;
+    int face = 0;
+    float u = 0, v = 0;
+    if (fabsf(z) > fabsf(x) && fabsf(z) > fabsf(y))
+    {
+        if (z > 0) { face = 5; u = (1 - x / z) / 2; v = (1 + y / z) / 2; }
+        else { face = 0; u = (1 + x / z) / 2; v = (1 + y / z) / 2; }
+    }
+    else if (fabsf(x) > fabsf(y) && fabsf(x) > fabsf(z))
+    {
+        if (x > 0) { face = 1; u = (1 - y / x) / 2; v = (1 + z / x) / 2; }
+        else { face = 3; u = (1 - y / x) / 2; v = (1 - z / x) / 2; }
+    }
+    else if (fabsf(y) > fabsf(x) && fabsf(y) > fabsf(z))
+    {
+        if (y > 0) { face = 4; u = (1 + x / y) / 2; v = (1 + z / y) / 2; }
+        else { face = 2; u = (1 + x / y) / 2; v = (1 - z / y) / 2; }
+    }
+    return texture_lookup(sc, sc.sky.w[face], sc.sky.h[face], sc.sky.off[face], u, v);
+}
+
+// The three Fresnel fractions share one body; n1/n2 differ. Returns 1 on total reflection.
+__device__ __forceinline__ float fresnel(float n1, float n2, float cos1, float &cos2)
+{
+    const float sin1 = sqrtf(1 - cos1 * cos1);
+    const float sin2 = n1 * sin1 / n2;
+    cos2 = 0.f;
+    if (sin2 >= 1) return 1;
+    cos2 = sqrtf(1 - sin2 * sin2);
+    const float rPara = (n2 * cos1 - n1 * cos2) / (n2 * cos1 + n1 * cos2);
+    const float rPerp = (n1 * cos1 - n2 * cos2) / (n1 * cos1 + n2 * cos2);
+    return (rPara * rPara + rPerp * rPerp) / 2.0f;
+}
+
+// :256-292 with isInVarnish = false
+__device__ __forceinline__ float fresnel_varnish(float4 incident, float4 N)
+{
+    const float cos1 = fmaxf(0.f, fminf(1.f, -dot4(incident, N)));
+    float cos2;
+    return fresnel(1.0f, 3.f, cos1, cos2);
+}
+
+__device__ __forceinline__ float material_brdf(int type, float4 incident, float4 N, float4 reflected)
+{
+    if (type == 0) return kPiInv;
+    if (type == 2) return 1;
+    if (type == 1)
+    {
+        const float denom = 1 + 0.8f * dot4(incident, reflected);
+        return (1 - 0.8f * 0.8f) / (4 * kPi * denom * denom);
+    }
+    if (type == 3) return (1 - fresnel_varnish(incident, N)) * kPiInv;
+    return 1;
+}
+
+__device__ __forceinline__ float light_power_toward(const DevLight &l, float4 p, float4 N)
+{
+    if (l.type == 0) return l.power * fmaxf(dot4(-l.direction, N), 0.f);
+    if (l.type == 1)
+    {
+        const float4 t = p - l.position;
+        return l.power / dot4(t, t) * fmaxf(dot4(normalize4(l.position - p), N), 0.f);
+    }
+    if (l.type == 2)
+    {
+        const float4 ld = normalize4(p - l.position);
+        const float cosAngle = dot4(ld, l.direction);
+        if (cosAngle > l.cosInner) return l.power * fmaxf(-dot4(ld, N), 0.f);
+        if (cosAngle < l.cosOuter) return 0.0f;
+        return l.power * (cosAngle - l.cosOuter) / (l.cosInner - l.cosOuter) * fmaxf(-dot4(ld, N), 0);
+    }
+    return 0.f;
+}
+
+// cos/sin: the reference calls OpenCL's cos/sin (implementation-defined accuracy); the oracle build uses
+// glibc cosf/sinf (< 1 ulp). They are evaluated in double here and rounded once, which yields the
+// correctly rounded float and therefore agrees with the oracle in all but a ~1e-7 fraction of calls.
+__device__ __forceinline__ void concentric_sample_disk(int &seed, float &dx, float &dy)
+{
+    const float u1 = rng_next(seed);
+    const float u2 = rng_next(seed);
+    float r, theta;
+    const float sx = 2 * u1 - 1;
+    const float sy = 2 * u2 - 1;
+    if (fabsf(sx) < 0.0001f) { r = sy; theta = 0; }
+    else if (fabsf(sy) < 0.0001f) { r = sx; theta = 2; }
+    else if (sx > -sy)
+    {
+        if (sx > sy) { r = sx; if (sy > 0) theta = sy / sx; else theta = 8.f + sy / sx; }
+        else { r = sy; theta = 2.f - sx / sy; }
+    }
+    else
+    {
+        if (sx < sy) { r = -sx; theta = 4.f + sy / sx; }
+        else { r = -sy; theta = 6.f - sy / sx; }
+    }
+    theta *= kPi / 4.f;
+    r = (float)((double)r * 0.999);  // `r *= 0.999;` with a double literal (:408)
+    double sn, cs;
+    sincos((double)theta, &sn, &cs);
+    dx = r * (float)cs;
+    dy = r * (float)sn;
+}
+
+__device__ __forceinline__ float4 cosine_sample_hemisphere(int &seed, float4 N)
+{
+    float x, y, z;
+    concentric_sample_disk(seed, x, y);
+    z = 1 - x * x - y * y;
+    z = (z < 0) ? 0 : sqrtf(z);
+    const float4 v = f4(x, y, z, 0);
+    if (N.z > 0.9999f) return v;
+    if (N.z < -0.9999f) return -v;
+    const float4 sn = normalize4(f4(-N.y, N.x, 0, 0));
+    const float4 tn = normalize4(cross3(N, sn));
+    return normalize4(f4(dot4(f4(sn.x, tn.x, N.x, 0), v), dot4(f4(sn.y, tn.y, N.y, 0), v), dot4(f4(sn.z, tn.z, N.z, 0), v), 0));
+}
+
+// Shadow ray of one light from the hit point q (:932-938): direction = normalize(full), bound =
+// length(full) (INFINITY for a directional light) — a LENGTH handed to a parameter that the triangle
+// test compares with squared distances (F9b), reproduced as is in both modes.
+__device__ __forceinline__ void shadow_setup(const DevLight &l, float4 q, float4 &dir, float &bound)
+{
+    const float4 full = (l.type == 0) ? -l.direction : (l.position - q);
+    dir = normalize4(full);
+    bound = (l.type == 0) ? INFINITY : length4(full);
+}
+
+}  // namespace ptc

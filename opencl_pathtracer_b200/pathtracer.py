@@ -1,0 +1,154 @@
+"""Python face of the PathTracer_CUDA boundary: every call goes through the C ABI (include/pathtracer_cuda.h).
+
+PathTracerCUDA mirrors the life cycle of the reference's device layer
+(OpenCL_SetupContext -> OpenCL_InitializeMemory -> OpenCL_RunKernel, Controleur/PathTracer_OpenCL.h:17-19):
+construct (= setup), upload(scene) (= initialize memory), render(first, n) + read_image() (= the body of the
+run loop), read_stats(), close() (= the release at the end of OpenCL_RunKernel).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _native as N
+
+
+class PathTracerError(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__("PathTracer_CUDA error %d: %s" % (code, message))
+        self.code = code
+
+
+class PathTracerCUDA:
+    def __init__(self, width, height, ray_max_depth=10, sampler=N.SAMPLER_JITTERED, mode=N.MODE_PARITY, device=0,
+                 iterations_per_batch=0, flags=0, stream=None):
+        self._lib = N.cuda_lib()
+        cfg = N.Config()
+        cfg.struct_size = C.sizeof(N.Config)
+        cfg.device, cfg.image_width, cfg.image_height = device, width, height
+        cfg.ray_max_depth, cfg.sampler, cfg.mode = ray_max_depth, sampler, mode
+        cfg.iterations_per_batch, cfg.flags = iterations_per_batch, flags
+        cfg.stream = stream
+        h = C.c_void_p()
+        rc = self._lib.ptc_create(C.byref(cfg), C.byref(h))
+        if rc != N.PTC_OK:
+            raise PathTracerError(rc, self._lib.ptc_last_error(None).decode())
+        self._h = h
+        self.width, self.height, self.ray_max_depth = width, height, ray_max_depth
+        self.n_pixels = width * height
+
+    def _ck(self, rc):
+        if rc != N.PTC_OK:
+            raise PathTracerError(rc, self._lib.ptc_last_error(self._h).decode())
+
+    def upload(self, scene):
+        v = scene.view() if hasattr(scene, "view") else scene
+        self._ck(self._lib.ptc_upload_scene(self._h, C.byref(v)))
+
+    def set_camera(self, camera16):
+        a = np.ascontiguousarray(camera16, dtype=np.float32)
+        assert a.size == 16
+        self._ck(self._lib.ptc_set_camera(self._h, a.ctypes.data_as(C.POINTER(C.c_float))))
+
+    def reset(self):
+        self._ck(self._lib.ptc_reset_accumulation(self._h))
+
+    def render(self, first_iteration, n_iterations, sync=False):
+        self._ck(self._lib.ptc_render(self._h, first_iteration, n_iterations))
+        if sync:
+            self.synchronize()
+
+    def synchronize(self):
+        self._ck(self._lib.ptc_synchronize(self._h))
+
+    def read_image(self, color=None, ray_nb=None):
+        """imageColor (running sum, float32 [H, W, 4]) and imageRayNb (running count, [H, W])."""
+        if color is None:
+            color = np.empty((self.height, self.width, 4), dtype=np.float32)
+        if ray_nb is None:
+            ray_nb = np.empty((self.height, self.width), dtype=np.float32)
+        self._ck(self._lib.ptc_read_image(self._h, color.ctypes.data, ray_nb.ctypes.data))
+        return color, ray_nb
+
+    def read_image_into(self, color_ptr, ray_nb_ptr):
+        self._ck(self._lib.ptc_read_image(self._h, color_ptr, ray_nb_ptr))
+
+    def read_variance(self):
+        v = np.empty((self.height, self.width, 4), dtype=np.float32)
+        self._ck(self._lib.ptc_read_variance(self._h, v.ctypes.data))
+        return v
+
+    def read_stats(self):
+        d = np.zeros(self.ray_max_depth + 1, dtype=np.uint32)
+        b = np.zeros(N.MAX_INTERSECTION_NUMBER, dtype=np.uint32)
+        t = np.zeros(N.MAX_INTERSECTION_NUMBER, dtype=np.uint32)
+        self._ck(self._lib.ptc_read_stats(self._h, d.ctypes.data, b.ctypes.data, t.ctypes.data))
+        return d, b, t
+
+    def read_rgb8(self):
+        rgb = np.empty((self.height, self.width, 3), dtype=np.uint8)
+        self._ck(self._lib.ptc_read_rgb8(self._h, rgb.ctypes.data))
+        return rgb
+
+    def add_image(self, color, ray_nb):
+        color = np.ascontiguousarray(color, dtype=np.float32)
+        ray_nb = np.ascontiguousarray(ray_nb, dtype=np.float32)
+        self._ck(self._lib.ptc_add_image(self._h, color.ctypes.data, ray_nb.ctypes.data))
+
+    def counters(self):
+        c = N.Counters()
+        self._ck(self._lib.ptc_read_counters(self._h, C.byref(c)))
+        return {f[0]: getattr(c, f[0]) for f in N.Counters._fields_}
+
+    def device_buffers(self):
+        b = N.DeviceBuffers()
+        self._ck(self._lib.ptc_get_device_buffers(self._h, C.byref(b)))
+        return b
+
+    def trace_primary(self, iteration=0):
+        n = self.n_pixels
+        out = {"hit": np.empty(n, np.int32), "st": np.empty((n, 2), np.float32), "dist2": np.empty(n, np.float32),
+               "dir": np.empty((n, 4), np.float32), "seed_after": np.empty(n, np.int32), "counts": np.empty((n, 2), np.uint32)}
+        self._ck(self._lib.ptc_trace_primary(self._h, iteration, out["hit"].ctypes.data, out["st"].ctypes.data, out["dist2"].ctypes.data,
+                                             out["dir"].ctypes.data, out["seed_after"].ctypes.data, out["counts"].ctypes.data))
+        return out
+
+    def render_single(self, iteration):
+        r = np.empty((self.height, self.width, 4), dtype=np.float32)
+        self._ck(self._lib.ptc_render_single(self._h, iteration, r.ctypes.data))
+        return r
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.ptc_destroy(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def PathTracer_Main(scene, image_width, image_height, numImagesToRender, saveRenderedImages=False, loadSky=False, sampler=0, rayDepth=10,
+                    mode=N.MODE_PARITY, readBackEvery=0, device=0, exportFolder=None, seed=20261104):
+    """The reference's whole host pipeline (Controleur/PathTracer.cpp:25-110) through the C++ controller of
+    host/PathTracer.cpp: importer -> BVH_Create -> CUDA_SetupContext / CUDA_InitializeMemory / CUDA_RunKernel.
+    Returns dict(imageColor, imageRayNb, rayDepths, rayIntersectedBBx, rayIntersectedTri)."""
+    L = N.host_lib()
+    color = np.zeros((image_height, image_width, 4), np.float32)
+    nb = np.zeros((image_height, image_width), np.float32)
+    d = np.zeros(rayDepth + 1, np.uint32)
+    b = np.zeros(N.MAX_INTERSECTION_NUMBER, np.uint32)
+    t = np.zeros(N.MAX_INTERSECTION_NUMBER, np.uint32)
+    rc = L.pth_main(scene.encode(), seed, image_width, image_height, numImagesToRender, int(saveRenderedImages), int(loadSky), sampler,
+                    rayDepth, mode, readBackEvery or numImagesToRender, device, exportFolder.encode() if exportFolder else None,
+                    color.ctypes.data, nb.ctypes.data, d.ctypes.data, b.ctypes.data, t.ctypes.data)
+    if rc != 0:
+        raise RuntimeError("PathTracer_Main failed (see stderr)")
+    return {"imageColor": color, "imageRayNb": nb, "rayDepths": d, "rayIntersectedBBx": b, "rayIntersectedTri": t}
