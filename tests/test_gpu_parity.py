@@ -1,0 +1,194 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the oracle = the reference kernel itself compiled
+for the CPU (oracle/_ref). Bars (BASELINE.json north_star):
+  * random streams, primary ray directions, primary-hit triangle index, (s,t), dist2, work counters: BIT-EXACT
+  * single-sample radiance: |a-b| <= 1e-3 * max(|a|,|b|) + 1e-6 per channel on all pixels whose path is not
+    affected by a floating-point tie (fraction of affected pixels reported and bounded)
+  * accumulated images: RMSE bound stated in each test
+"""
+import numpy as np
+import pytest
+
+import opencl_pathtracer_b200 as pt
+
+pytestmark = pytest.mark.gpu
+
+REL_TOL = 1e-3  # north_star: single-sample radiance within 1e-3 relative error
+ABS_TOL = 1e-6
+
+
+def _rel_mismatch(a, b):
+    a = a.reshape(-1, 4).astype(np.float64)
+    b = b.reshape(-1, 4).astype(np.float64)
+    bad = np.abs(a - b) > REL_TOL * np.maximum(np.abs(a), np.abs(b)) + ABS_TOL
+    return bad.any(axis=1)
+
+
+@pytest.mark.parametrize("name,w,h,sky", [("cornell", 128, 96, False), ("cornell_specular", 96, 96, False),
+                                           ("gallery", 160, 120, True), ("atrium:4", 160, 96, False)])
+@pytest.mark.parametrize("sampler", [0, 2])
+def test_primary_hits_bit_exact(ptref, scene_factory, name, w, h, sky, sampler):
+    sc = scene_factory(name, w, h, sky)
+    ref = ptref.primary(sc, w, h, sampler=sampler, iteration=3)
+    with pt.PathTracerCUDA(w, h, sampler=sampler, mode=pt.MODE_PARITY) as r:
+        r.upload(sc)
+        got = r.trace_primary(3)
+    assert np.array_equal(got["seed_after"], ref["seed_after"])
+    assert np.array_equal(got["dir"].view(np.uint32), ref["dir"].view(np.uint32)), "primary ray directions differ"
+    assert np.array_equal(got["hit"], ref["hit"]), "primary hit triangle ids differ: %d px" % (got["hit"] != ref["hit"]).sum()
+    assert (ref["hit"] >= 0).any()
+    assert np.array_equal(got["st"].view(np.uint32), ref["st"].view(np.uint32))
+    assert np.array_equal(got["dist2"].view(np.uint32), ref["dist2"].view(np.uint32))
+    assert np.array_equal(got["counts"], ref["counts"]), "per-ray box / triangle test counters differ"
+
+
+def test_primary_hits_random_sampler(ptref, scene_factory):
+    w, h = 96, 64
+    sc = scene_factory("gallery", w, h, True)
+    ref = ptref.primary(sc, w, h, sampler=1, iteration=5)
+    with pt.PathTracerCUDA(w, h, sampler=1) as r:
+        r.upload(sc)
+        got = r.trace_primary(5)
+    for k in ("seed_after", "hit", "counts"):
+        assert np.array_equal(got[k], ref[k]), k
+    assert np.array_equal(got["dir"].view(np.uint32), ref["dir"].view(np.uint32))
+
+
+@pytest.mark.parametrize("name,w,h,sky,depth", [("cornell", 128, 96, False, 10), ("cornell_specular", 96, 96, False, 10),
+                                                 ("gallery", 160, 120, True, 10), ("gallery", 64, 48, True, 3),
+                                                 ("atrium:4", 128, 80, False, 6)])
+def test_single_sample_radiance(ptref, scene_factory, name, w, h, sky, depth):
+    sc = scene_factory(name, w, h, sky)
+    for it in (0, 7):
+        ref = ptref.render(sc, w, h, depth, 0, it, it + 1)["imageColor"]
+        with pt.PathTracerCUDA(w, h, ray_max_depth=depth, mode=pt.MODE_PARITY) as r:
+            r.upload(sc)
+            got = r.render_single(it)
+        bad = _rel_mismatch(got, ref)
+        frac = bad.mean()
+        print("%s it=%d depth=%d: %d / %d pixels outside 1e-3 (%.4f %%), exact-equal %.2f %%" %
+              (name, it, depth, bad.sum(), bad.size, 100 * frac, 100 * (got.view(np.uint32) == ref.view(np.uint32)).all(axis=-1).mean()))
+        assert np.isfinite(got).all()
+        assert frac <= 2e-3, "fraction of pixels whose path diverged (fp ties / libm ulps) too large: %g" % frac
+
+
+def test_accumulated_image_and_statistics(ptref, scene_factory):
+    """C1-shaped: Cornell, 16 spp, full pipeline incl. histograms; batching must not change sums."""
+    w, h, depth, spp = 96, 96, 10, 16
+    sc = scene_factory("cornell", w, h, False)
+    ref = ptref.render(sc, w, h, depth, 0, 0, spp)
+    for batch in (1, 5):
+        with pt.PathTracerCUDA(w, h, ray_max_depth=depth, iterations_per_batch=batch) as r:
+            r.upload(sc)
+            r.render(0, spp)
+            color, nb = r.read_image()
+            d, b, t = r.read_stats()
+            v = r.read_variance()
+            c = r.counters()
+        assert np.array_equal(nb, ref["imageRayNb"])
+        assert c["paths"] == w * h * spp
+        mean = ref["imageColor"][..., :3].mean()
+        rmse = np.sqrt(((color[..., :3] - ref["imageColor"][..., :3]) ** 2).mean())
+        print("batch", batch, "rmse/mean", rmse / mean, "depth hist", d.tolist(), ref["rayDepths"].tolist())
+        assert rmse / mean < 2e-3
+        # histograms: equal up to the handful of paths that diverged on a tie
+        assert d.sum() == ref["rayDepths"].sum() == w * h * spp
+        assert np.abs(d.astype(np.int64) - ref["rayDepths"].astype(np.int64)).sum() <= 2e-3 * w * h * spp
+        assert b.sum() == ref["rayIntersectedBBx"].sum() and t.sum() == ref["rayIntersectedTri"].sum()
+        assert np.abs(b.astype(np.int64) - ref["rayIntersectedBBx"].astype(np.int64)).sum() <= 4e-3 * w * h * spp
+        assert np.isfinite(v).all()
+
+
+def test_iteration_ranges_compose(scene_factory):
+    """render(0,8) == render(0,3) + render(3,5) bit for bit (random streams depend on the iteration number only)."""
+    w, h = 64, 64
+    sc = scene_factory("cornell_specular", w, h, False)
+    with pt.PathTracerCUDA(w, h, iterations_per_batch=3) as r:
+        r.upload(sc)
+        r.render(0, 8)
+        a, na = r.read_image()
+        r.reset()
+        r.render(0, 3)
+        r.render(3, 5)
+        b, nb = r.read_image()
+    assert np.array_equal(a.view(np.uint32), b.view(np.uint32)) and np.array_equal(na, nb)
+
+
+def test_fast_mode_matches_parity(ptref, scene_factory):
+    """FAST = same arithmetic, correct distance culling, unlit shadow rays skipped: identical hits, same image."""
+    w, h = 160, 120
+    sc = scene_factory("gallery", w, h, True)
+    with pt.PathTracerCUDA(w, h, mode=pt.MODE_PARITY) as p, pt.PathTracerCUDA(w, h, mode=pt.MODE_FAST) as f:
+        p.upload(sc)
+        f.upload(sc)
+        hp, hf = p.trace_primary(1), f.trace_primary(1)
+        mism = (hp["hit"] != hf["hit"]).mean()
+        print("primary hit mismatch fraction FAST vs PARITY: %g" % mism)
+        assert mism <= 1e-4
+        assert (hf["counts"][:, 0] <= hp["counts"][:, 0]).all(), "FAST must never test more boxes than PARITY"
+        assert hf["counts"][:, 0].sum() < hp["counts"][:, 0].sum()
+        rp, rf = p.render_single(2), f.render_single(2)
+        bad = _rel_mismatch(rf, rp).mean()
+        print("1-spp radiance mismatch fraction FAST vs PARITY: %g" % bad)
+        assert bad <= 2e-3
+
+
+def test_rgb8_epilogue_and_add_image(scene_factory):
+    w, h = 64, 48
+    sc = scene_factory("cornell", w, h, False)
+    with pt.PathTracerCUDA(w, h) as r:
+        r.upload(sc)
+        r.render(0, 4)
+        color, nb = r.read_image()
+        rgb = r.read_rgb8()
+        exp = np.minimum(color[..., :3] * np.float32(255.0) / nb[..., None], np.float32(255.0)).astype(np.int32)
+        assert np.abs(rgb.astype(np.int32) - exp).max() <= 1
+        r.add_image(color, nb)
+        c2, n2 = r.read_image()
+        assert np.array_equal(c2, color + color) and np.array_equal(n2, nb + nb)
+
+
+def test_moving_camera_reset(scene_factory):
+    w, h = 64, 48
+    sc = scene_factory("cornell", w, h, False)
+    cam = sc.camera().copy()
+    with pt.PathTracerCUDA(w, h) as r:
+        r.upload(sc)
+        r.render(0, 1)
+        a, _ = r.read_image()
+        cam2 = cam.copy()
+        cam2[0:3] += np.float32(25.0)
+        r.set_camera(cam2)
+        r.reset()
+        r.render(0, 1)
+        b, nb = r.read_image()
+        assert (nb == 1).all() and not np.array_equal(a, b)
+        r.set_camera(cam)
+        r.reset()
+        r.render(0, 1)
+        c, _ = r.read_image()
+        assert np.array_equal(a.view(np.uint32), c.view(np.uint32))
+
+
+def test_error_paths(scene_factory):
+    with pytest.raises(pt.PathTracerError) as e:
+        pt.PathTracerCUDA(0, 10)
+    assert e.value.code == 1
+    with pt.PathTracerCUDA(32, 32) as r:
+        with pytest.raises(pt.PathTracerError) as e:
+            r.render(0, 1)
+        assert e.value.code == 4  # PTC_ERR_STATE: render before upload
+    with pytest.raises(pt.PathTracerError) as e:
+        pt.PathTracerCUDA(32, 32, ray_max_depth=1000)
+    assert e.value.code == 5
+
+
+def test_controller_drop_in(ptref, scene_factory):
+    """PathTracer_Main (C++ controller, reference call sequence) end to end vs the oracle's launch loop."""
+    w, h, spp = 80, 60, 4
+    out = pt.PathTracer_Main("cornell", w, h, spp, rayDepth=10)
+    sc = scene_factory("cornell", w, h, False)
+    ref = ptref.render(sc, w, h, 10, 0, 0, spp)
+    assert np.array_equal(out["imageRayNb"], ref["imageRayNb"])
+    bad = _rel_mismatch(out["imageColor"], ref["imageColor"]).mean()
+    assert bad <= 5e-3
+    assert out["rayDepths"].sum() == w * h * spp
