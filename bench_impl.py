@@ -1,0 +1,213 @@
+"""Second half of bench.py: the CUDA arm (see bench.py's docstring for the contract)."""
+import json
+import os
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+
+
+class _DevArray:
+    """__cuda_array_interface__ view of a device pointer owned by the PathTracer_CUDA context (zero-copy for NCCL)."""
+
+    def __init__(self, ptr, n_floats):
+        self.__cuda_array_interface__ = {"shape": (n_floats,), "typestr": "<f4", "data": (int(ptr), False), "version": 2}
+
+
+def run_ours(args, rank, local_rank, world):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import opencl_pathtracer_b200 as pt
+    from bench import DEPTH, H, W, WORKLOADS, ClockSampler, load_peaks
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — this benchmark has no CPU fallback (use --impl reference for the CPU reference)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    wl = WORKLOADS[args.workload]
+    S, K, WU = args.spp_per_step, args.steps, args.warmup
+    mode = pt.MODE_FAST if args.mode == "fast" else pt.MODE_PARITY
+    n_pix = W * H
+    scene = pt.Scene(wl["scene"], W, H)
+    info = scene.info
+    stream = torch.cuda.Stream(device=dev)
+
+    def first_iter(step):
+        return (step * world + rank) * S  # disjoint iteration ranges per rank
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    with torch.cuda.stream(stream):
+        r = pt.PathTracerCUDA(W, H, ray_max_depth=DEPTH, mode=mode, device=local_rank, flags=pt.FLAG_NO_VARIANCE, stream=stream.cuda_stream)
+        r.upload(scene)
+        bufs = r.device_buffers()
+        color = torch.as_tensor(_DevArray(bufs.image_color, n_pix * 4), device=dev)
+        count = torch.as_tensor(_DevArray(bufs.image_ray_nb, n_pix), device=dev)
+
+        # ---------------- device-timed region: K steps + one NCCL reduce of the accumulators
+        for i in range(WU):
+            r.render(first_iter(i), S)
+        r.synchronize()
+        r.reset()
+        c0 = r.counters()
+        clocks = ClockSampler(local_rank)
+        barrier()
+        if rank == 0:
+            clocks.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for i in range(K):
+            r.render(first_iter(WU + i), S)
+        if world > 1:
+            dist.reduce(color, dst=0, op=dist.ReduceOp.SUM)
+            dist.reduce(count, dst=0, op=dist.ReduceOp.SUM)
+        e1.record(stream)
+        barrier()
+        ms = max_over_ranks(e0.elapsed_time(e1))
+        clk = clocks.stop() if rank == 0 else None
+        c1 = r.counters()
+        launches = c1["kernel_launches"] - c0["kernel_launches"]
+        rays = sum_over_ranks((c1["extension_rays"] - c0["extension_rays"]) + (c1["shadow_rays"] - c0["shadow_rays"]))
+        paths = sum_over_ranks(c1["paths"] - c0["paths"])
+        assert paths == float(K) * S * n_pix * world, (paths, K, S, n_pix, world)
+        if rank == 0:
+            mean_rgb = float((color.view(-1, 4)[:, :3].sum(0) / count.sum()).mean().item())
+        value = paths / (ms * 1e-3)
+
+        # ---------------- e2e: reference-facing call sequence with host buffers, host wall clock
+        r.reset()
+        host_c = torch.empty(n_pix * 4, dtype=torch.float32, pin_memory=True)
+        host_n = torch.empty(n_pix, dtype=torch.float32, pin_memory=True)
+        cam = scene.camera()
+        if world > 1:
+            tmp_c, tmp_n = torch.empty_like(color), torch.empty_like(count)
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(K):
+            r.set_camera(cam)  # the step's input: 64 bytes host -> device (kernel parameter block)
+            r.render(first_iter(i), S)
+            if world == 1:
+                r.read_image_into(host_c.data_ptr(), host_n.data_ptr())  # device -> pinned host, synchronises
+            else:
+                tmp_c.copy_(color)
+                tmp_n.copy_(count)
+                dist.reduce(tmp_c, dst=0, op=dist.ReduceOp.SUM)
+                dist.reduce(tmp_n, dst=0, op=dist.ReduceOp.SUM)
+                if rank == 0:
+                    host_c.copy_(tmp_c, non_blocking=True)
+                    host_n.copy_(tmp_n, non_blocking=True)
+                stream.synchronize()
+        barrier()
+        e2e_s = max_over_ranks(time.perf_counter() - t0)
+        e2e_value = K * S * n_pix * world / e2e_s
+        r.close()
+
+        # ---------------- roofline of the dominant traversal kernel (rank 0; separate context with per-stage CUDA events)
+        roof = None
+        extra = {}
+        if rank == 0:
+            peaks, peak_kind = load_peaks()
+            rp = pt.PathTracerCUDA(W, H, ray_max_depth=DEPTH, mode=mode, device=local_rank, flags=pt.FLAG_NO_VARIANCE | pt.FLAG_STAGE_TIMING,
+                                   stream=stream.cuda_stream)
+            rp.upload(scene)
+            rp.render(0, S, sync=True)
+            rp.reset()
+            rp.render(S, S, sync=True)
+            c = rp.counters()
+            rp.close()
+            ext_bytes = 64.0 * (c["ext_box_tests"] / 2 + c["ext_triangle_tests"])
+            con_bytes = 64.0 * ((c["box_tests"] - c["ext_box_tests"]) / 2 + (c["triangle_tests"] - c["ext_triangle_tests"]))
+            kern = {"k_extend": (ext_bytes, c["ms_extend"], c["launches_extend"], c["extension_rays"]),
+                    "k_connect": (con_bytes, c["ms_connect"], c["launches_connect"], c["shadow_rays"])}
+            dom = max(kern, key=lambda k: kern[k][1])
+            traffic = None
+            tp = os.path.join(ROOT, "profiles", "traffic.json")
+            if os.path.exists(tp):
+                with open(tp) as f:
+                    traffic = json.load(f).get(dom)
+
+            def roofline(name):
+                b, t_ms, n, nrays = kern[name]
+                ach = b / (t_ms * 1e-3) / 1e9 if t_ms > 0 else 0.0
+                return {"kernel": name, "bound": "hbm", "achieved": ach, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": ach / peaks["hbm_gbs"],
+                        "peak_kind": peak_kind + " HBM copy bandwidth (working set is L2-resident: see DESIGN.md)",
+                        "algorithmic_bytes_per_launch": b / max(n, 1), "avg_launch_ms": t_ms / max(n, 1), "launches": n,
+                        "mrays_per_s": nrays / (t_ms * 1e-3) / 1e6 if t_ms > 0 else 0.0}
+
+            roof = roofline(dom)
+            roof["traffic"] = traffic
+            other = "k_connect" if dom == "k_extend" else "k_extend"
+            extra["roofline_other"] = roofline(other)
+            tot = c["ms_generate"] + c["ms_extend"] + c["ms_connect"] + c["ms_shade"] + c["ms_accumulate"]
+            extra["stage_ms_per_step"] = {k: c["ms_" + k] for k in ("generate", "extend", "connect", "shade", "accumulate")}
+            extra["stage_share"] = {k: (c["ms_" + k] / tot if tot else 0.0) for k in ("generate", "extend", "connect", "shade", "accumulate")}
+            extra["work_per_path"] = {"box_tests": c["box_tests"] / c["paths"], "triangle_tests": c["triangle_tests"] / c["paths"],
+                                      "rays": (c["extension_rays"] + c["shadow_rays"]) / c["paths"]}
+
+            # PARITY mode beside it (bit-exact arithmetic + the reference's culling quirks), 2 steps
+            if world == 1 and args.mode == "fast":
+                rq = pt.PathTracerCUDA(W, H, ray_max_depth=DEPTH, mode=pt.MODE_PARITY, device=local_rank, flags=pt.FLAG_NO_VARIANCE,
+                                       stream=stream.cuda_stream)
+                rq.upload(scene)
+                rq.render(0, S, sync=True)
+                q0, q1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                q0.record(stream)
+                rq.render(S, 2 * S)
+                q1.record(stream)
+                rq.synchronize()
+                cq = rq.counters()
+                rq.close()
+                qms = q0.elapsed_time(q1)
+                extra["parity_mode"] = {"value": 2 * S * n_pix / (qms * 1e-3), "unit": "samples/s", "ms_per_step": qms / 2,
+                                        "box_tests_per_path": cq["box_tests"] / cq["paths"]}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            from oracle import ptref
+            rows = (508, 572)
+            t0 = time.perf_counter()
+            ptref.render(scene, W, H, DEPTH, 0, 0, 1, rows=rows)
+            dt = time.perf_counter() - t0
+            cpu = {"value": (rows[1] - rows[0]) * W / dt, "unit": "samples/s", "cores": ptref.max_threads(), "kind": "reference",
+                   "sample": "rows %d..%d of the %dx%d frame, 1 spp (%d paths), %.1f s; oracle/_ref = the reference kernel source compiled with g++ -O2 + OpenMP"
+                             % (rows[0], rows[1], W, H, (rows[1] - rows[0]) * W, dt)}
+        except Exception as e:  # the oracle is test infrastructure: its absence must not hide the GPU number
+            cpu = {"value": None, "unit": "samples/s", "cores": 0, "kind": "reference", "sample": "unavailable: %s" % e}
+
+    if world > 1:
+        dist.barrier()
+    if rank == 0:
+        line = {"metric": "samples/s", "value": value, "unit": "samples/s", "n_gpus": world, "steps": K, "warmup": WU,
+                "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "mrays_per_s": rays / (ms * 1e-3) / 1e6,
+                "config": {"workload": wl["desc"], "image": [W, H], "ray_max_depth": DEPTH, "sampler": "jittered", "mode": args.mode,
+                           "spp_per_step_per_gpu": S, "triangles": int(info.triangulationSize), "bvh_nodes": int(info.bvhSize),
+                           "parallelism": "iteration-range sharding x%d, one NCCL reduce of the accumulators per run" % world,
+                           "l2": "not flushed: each step streams ~%.1f GB of path state (> L2); the %.0f MB scene is L2-resident by design"
+                                 % (S * n_pix * 112 / 1e9, (info.triangulationSize * 64 + info.bvhSize * 32) / 1e6)},
+                "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": 64, "d2h_bytes_per_step": n_pix * 20,
+                        "ms_per_step": 1000.0 * e2e_s / K},
+                "gpu_launches": int(launches), "clocks": clk, "roofline": roof, "cpu_baseline": cpu, "mean_rgb": mean_rgb}
+        line.update(extra)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()

@@ -126,6 +126,8 @@ typedef struct ptc_counters
     uint64_t launches_connect;
     uint64_t scene_bytes_nodes;     /* device bytes of the flattened BVH */
     uint64_t scene_bytes_triangles; /* device bytes of the intersection records */
+    uint64_t ext_box_tests;         /* share of box_tests / triangle_tests spent by closest-hit traversals */
+    uint64_t ext_triangle_tests;
 } ptc_counters;
 
 /* Device pointers of the accumulators, for zero-copy collectives (NCCL reduce of per-GPU images). */

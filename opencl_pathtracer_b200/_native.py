@@ -42,7 +42,8 @@ class Counters(C.Structure):
     _fields_ = [("paths", C.c_uint64), ("extension_rays", C.c_uint64), ("shadow_rays", C.c_uint64), ("box_tests", C.c_uint64),
                 ("triangle_tests", C.c_uint64), ("kernel_launches", C.c_uint64), ("ms_generate", C.c_double), ("ms_extend", C.c_double),
                 ("ms_connect", C.c_double), ("ms_shade", C.c_double), ("ms_accumulate", C.c_double), ("launches_extend", C.c_uint64),
-                ("launches_connect", C.c_uint64), ("scene_bytes_nodes", C.c_uint64), ("scene_bytes_triangles", C.c_uint64)]
+                ("launches_connect", C.c_uint64), ("scene_bytes_nodes", C.c_uint64), ("scene_bytes_triangles", C.c_uint64),
+                ("ext_box_tests", C.c_uint64), ("ext_triangle_tests", C.c_uint64)]
 
 
 class DeviceBuffers(C.Structure):

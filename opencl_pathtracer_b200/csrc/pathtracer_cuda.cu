@@ -677,6 +677,8 @@ int ptc_read_counters(ptc_ctx *ctx, ptc_counters *out)
     out->launches_connect = ctx->launchesConnect;
     out->scene_bytes_nodes = ctx->nodes.n * sizeof(DevNode);
     out->scene_bytes_triangles = ctx->tris.n * sizeof(DevTri);
+    out->ext_box_tests = h.extBoxTests;
+    out->ext_triangle_tests = h.extTriTests;
     return PTC_OK;
 }
 

@@ -120,6 +120,7 @@ struct Counters
     uint32_t curExtend[kMaxBounces + 1];  // work cursors of the persistent kernels
     uint32_t curConnect[kMaxBounces + 1];
     unsigned long long extensionRays, shadowRays, boxTests, triTests, paths;
+    unsigned long long extBoxTests, extTriTests;  // share of boxTests / triTests spent by closest-hit rays
 };
 
 struct FrameParams

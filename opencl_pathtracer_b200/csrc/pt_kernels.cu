@@ -106,6 +106,11 @@ __device__ __forceinline__ void flush_work(Counters *cn, unsigned long long *ray
         atomicAdd(rayCounter, (unsigned long long)nRays);
         atomicAdd(&cn->boxTests, (unsigned long long)nb);
         atomicAdd(&cn->triTests, (unsigned long long)nt);
+        if (rayCounter == &cn->extensionRays)
+        {
+            atomicAdd(&cn->extBoxTests, (unsigned long long)nb);
+            atomicAdd(&cn->extTriTests, (unsigned long long)nt);
+        }
     }
 }
 

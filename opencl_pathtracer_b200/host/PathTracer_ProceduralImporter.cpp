@@ -129,8 +129,16 @@ struct SceneBuilder
                      const Float4 &nc, Float2 ua, Float2 ub, Float2 uc, uint mp, uint mn)
     {
         if (!Triangle_isValid(a, b, c)) return;
+        // A degenerate vertex normal (pole of a sphere, centre of a disc) would be replaced inside Triangle_Create by the
+        // face normal N, whose w lane is 1 (host cross()). The kernel's 4-lane normalize then yields a
+        // shading normal with w != 0 and, for axis-aligned faces, a NaN tangent frame (kernel.cl:323) whose NaN ray sweeps
+        // the whole BVH in the reference. Scenes are generated without that artefact: such vertices get the face
+        // normal as a VECTOR (w = 0), as a modelling package would export it.
+        Float4 fn = normalize(cross(b - a, c - a));
+        fn.w = 0;
+        const Float4 na2 = length(na) < 0.5f ? fn : na, nb2 = length(nb) < 0.5f ? fn : nb, nc2 = length(nc) < 0.5f ? fn : nc;
         Triangle t;
-        Triangle_Create(&t, a, b, c, ua, ub, uc, ua, ub, uc, na, nb, nc, mp, mn, (uint)tris.size());
+        Triangle_Create(&t, a, b, c, ua, ub, uc, ua, ub, uc, na2, nb2, nc2, mp, mn, (uint)tris.size());
         if (!(t.N.x == t.N.x) || !(t.N.y == t.N.y) || !(t.N.z == t.N.z)) return;  // zero-area sliver
         tris.push_back(t);
     }

@@ -38,6 +38,7 @@ def lib():
         L.ptref_sizes.argtypes = [vp]
         L.ptref_bvh_create.argtypes = [vp, u32, vp, vp, vp]
         L.ptref_render.argtypes = [C.POINTER(RefScene), u32, u32, u32, C.c_int, u32, u32, vp, vp, vp, vp, vp, vp, C.c_int]
+        L.ptref_render_rows.argtypes = [C.POINTER(RefScene), u32, u32, u32, C.c_int, u32, u32, u32, u32, vp, vp, vp, vp, vp, vp, C.c_int]
         L.ptref_primary.argtypes = [C.POINTER(RefScene), u32, u32, C.c_int, u32, vp, vp, vp, vp, vp, vp]
         L.ptref_rng.argtypes = [u32, u32, u32, u32, u32, C.c_int, vp, vp, vp]
         L.ptref_cosine_sample.argtypes = [C.c_int32, vp, vp, vp]
@@ -75,16 +76,17 @@ def ref_scene(scene):
     return r
 
 
-def render(scene, W, H, max_depth, sampler, it_begin, it_end, nthreads=0, acc=None):
+def render(scene, W, H, max_depth, sampler, it_begin, it_end, nthreads=0, acc=None, rows=None):
     """Reference launch loop. Returns dict of accumulators (new zeroed ones unless `acc` is passed back in)."""
     if acc is None:
         acc = {"imageColor": np.zeros((H, W, 4), np.float32), "imageRayNb": np.zeros((H, W), np.float32),
                "imageV": np.zeros((H, W, 4), np.float32), "rayDepths": np.zeros(max_depth + 1, np.uint32),
                "rayIntersectedBBx": np.zeros(5000, np.uint32), "rayIntersectedTri": np.zeros(5000, np.uint32)}
     rs = ref_scene(scene)
-    rc = lib().ptref_render(C.byref(rs), W, H, max_depth, sampler, it_begin, it_end, acc["imageColor"].ctypes.data,
-                            acc["imageRayNb"].ctypes.data, acc["imageV"].ctypes.data, acc["rayDepths"].ctypes.data,
-                            acc["rayIntersectedBBx"].ctypes.data, acc["rayIntersectedTri"].ctypes.data, nthreads)
+    r0, r1 = rows if rows is not None else (0, H)
+    rc = lib().ptref_render_rows(C.byref(rs), W, H, max_depth, sampler, it_begin, it_end, r0, r1, acc["imageColor"].ctypes.data,
+                                 acc["imageRayNb"].ctypes.data, acc["imageV"].ctypes.data, acc["rayDepths"].ctypes.data,
+                                 acc["rayIntersectedBBx"].ctypes.data, acc["rayIntersectedTri"].ctypes.data, nthreads)
     assert rc == 0
     return acc
 

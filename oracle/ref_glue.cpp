@@ -163,9 +163,23 @@ static void set_options(uint32_t W, uint32_t H, uint32_t maxDepth, uint32_t ligh
 // zeroes them before the first call), so consecutive iteration ranges can be rendered by consecutive calls.
 // sampler: 0 JITTERED, 1 RANDOM, 2 UNIFORM (Controleur/PathTracer_Structs.h:130-135). RANDOM scatters to
 // arbitrary pixels without atomics in the reference, so it is run on one thread here.
+int ptref_render_rows(const ptref_scene *s, uint32_t W, uint32_t H, uint32_t maxDepth, int sampler, uint32_t iterBegin,
+                      uint32_t iterEnd, uint32_t rowBegin, uint32_t rowEnd, float *imageColor, float *imageRayNb, float *imageV,
+                      uint32_t *rayDepths, uint32_t *bbx, uint32_t *tri, int nthreads);
+
 int ptref_render(const ptref_scene *s, uint32_t W, uint32_t H, uint32_t maxDepth, int sampler, uint32_t iterBegin,
                  uint32_t iterEnd, float *imageColor, float *imageRayNb, float *imageV, uint32_t *rayDepths,
                  uint32_t *bbx, uint32_t *tri, int nthreads)
+{
+    return ptref_render_rows(s, W, H, maxDepth, sampler, iterBegin, iterEnd, 0, H, imageColor, imageRayNb, imageV, rayDepths, bbx, tri,
+                             nthreads);
+}
+
+// Same loop restricted to image rows [rowBegin, rowEnd): a bounded sample of a large frame for the timed CPU
+// baseline (work-items of other rows are simply not launched; every launched work-item is unchanged).
+int ptref_render_rows(const ptref_scene *s, uint32_t W, uint32_t H, uint32_t maxDepth, int sampler, uint32_t iterBegin,
+                      uint32_t iterEnd, uint32_t rowBegin, uint32_t rowEnd, float *imageColor, float *imageRayNb, float *imageV,
+                      uint32_t *rayDepths, uint32_t *bbx, uint32_t *tri, int nthreads)
 {
     set_options(W, H, maxDepth, s->lightsSize);
     float4 cam[4];
@@ -175,7 +189,7 @@ int ptref_render(const ptref_scene *s, uint32_t W, uint32_t H, uint32_t maxDepth
     for (uint32_t it = iterBegin; it < iterEnd; it++)
     {
 #pragma omp parallel for schedule(dynamic, 1) num_threads(nthreads)
-        for (int64_t y = 0; y < (int64_t)H; y++)
+        for (int64_t y = (int64_t)rowBegin; y < (int64_t)(rowEnd < H ? rowEnd : H); y++)
         {
             ocl_shim::gid[1] = (size_t)y;
             for (uint32_t x = 0; x < W; x++)
@@ -266,6 +280,74 @@ int ptref_cosine_sample(int32_t seed, const float *N, float *out, int32_t *seedA
     memcpy(out, &v, 16);
     *seedAfter = sd;
     return 0;
+}
+
+// Debug probe: Kernel_Main's path loop (kernel.cl:1248-1315) for ONE work-item, made with the reference's own functions,
+// logging per bounce: origin(4) direction(4) | hit tri, material type | boxes, triangles tested by the closest-hit
+// traversal, boxes, triangles by the shadow rays | s, t. Returns the number of bounces logged.
+int ptref_path_debug(const ptref_scene *s, uint32_t W, uint32_t H, uint32_t maxDepth, uint32_t x, uint32_t y, uint32_t it,
+                     float *rays /*[maxDepth][8]*/, int32_t *ids /*[maxDepth][2]*/, uint32_t *work /*[maxDepth][4]*/, float *st)
+{
+    namespace K = refk_jittered;
+    set_options(W, H, maxDepth, s->lightsSize);
+    float4 cam[4];
+    memcpy(cam, s->camera, sizeof(cam));
+    ocl_shim::gid[0] = x;
+    ocl_shim::gid[1] = y;
+    K::Ray3D r;
+    int seedValue = K::InitializeRandomSeed(it);
+    int *seed = &seedValue;
+    float2 sample = K::sampler(&r, seed, it);
+    float4 shot = cam[1] + (cam[2] * sample.x) + (cam[3] * sample.y);
+    K::Ray3D_Create(&r, &cam[0], &shot, false);
+    r.sample = sample;
+    const K::Node *bvh = (const K::Node *)s->bvh;
+    const K::Triangle *tris = (const K::Triangle *)s->triangulation;
+    const K::Light *lights = (const K::Light *)s->lights;
+    const K::Material *mats = (const K::Material *)s->materiaux;
+    const K::Texture *tex = (const K::Texture *)s->textures;
+    const uchar4 *texd = (const uchar4 *)s->texturesData;
+    const K::Sky *sky = (const K::Sky *)s->sky;
+    float4 T{1, 1, 1, 1};
+    int n = 0;
+    bool active = true;
+    while (active && r.reflectionId < maxDepth)
+    {
+        memcpy(rays + 8 * n, &r.origin, 16);
+        memcpy(rays + 8 * n + 4, &r.direction, 16);
+        uint32_t b0 = r.numIntersectedBBx, t0 = r.numIntersectedTri;
+        bool h = K::BVH_IntersectRay(seed, bvh, tris, lights, mats, tex, texd, sky, &r);
+        work[4 * n] = r.numIntersectedBBx - b0;
+        work[4 * n + 1] = r.numIntersectedTri - t0;
+        work[4 * n + 2] = work[4 * n + 3] = 0;
+        ids[2 * n] = h ? (int32_t)r.intersectedTriangleId : -1;
+        ids[2 * n + 1] = -1;
+        st[2 * n] = h ? r.s : 0;
+        st[2 * n + 1] = h ? r.t : 0;
+        if (h)
+        {
+            K::Triangle tri = tris[r.intersectedTriangleId];
+            K::Material mat = mats[r.intersectedMaterialId];
+            ids[2 * n + 1] = mat.type;
+            bool same = (K::dot(r.direction, tri.N) > 0);
+            float4 Ng = K::Triangle_GetNormal(&tri, !same);
+            float4 Ns = K::Triangle_GetSmoothNormal(&tri, !same, r.s, r.t);
+            float4 ro = -r.direction;
+            K::Vector_PutInSameHemisphereAs(&Ns, &ro);
+            Ns = K::normalize(Ns);
+            uint32_t b1 = r.numIntersectedBBx, t1 = r.numIntersectedTri;
+            float4 L = K::Scene_ComputeDirectIllumination(seed, bvh, tris, lights, mats, tex, texd, sky, &r, &mat, &Ns);
+            work[4 * n + 2] = r.numIntersectedBBx - b1;
+            work[4 * n + 3] = r.numIntersectedTri - t1;
+            K::Scene_ComputeRadiance(seed, bvh, tris, lights, mats, tex, texd, sky, &r, &tri, &mat, &L, &T, &Ng, &Ns);
+            r.reflectionId++;
+        }
+        else
+            active = false;
+        n++;
+        if (active && K::Vector_Max(&T) <= 0.001f) active = false;
+    }
+    return n;
 }
 
 int ptref_max_threads() { return omp_get_max_threads(); }
