@@ -1,0 +1,101 @@
+"""CPU: the C-ABI library loads and exports every symbol include/pathtracer_cuda.h declares; host-side mirror of the
+reference interface (importer conventions, controller error behaviour, BMP writer, sharding arithmetic)."""
+import ctypes as C
+import os
+import re
+import struct
+import subprocess
+
+import numpy as np
+import pytest
+
+import opencl_pathtracer_b200 as pt
+from opencl_pathtracer_b200 import _native as N
+from opencl_pathtracer_b200.sharding import iteration_range
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "pathtracer_cuda.h")).read()
+    declared = re.findall(r"PTC_API\s+[\w\s\*]+?\b(ptc_\w+)\s*\(", hdr)
+    assert len(declared) >= 20 and sorted(declared) == sorted(N.PTC_SYMBOLS)
+    lib = N.cuda_lib()
+    for name in declared:
+        assert getattr(lib, name) is not None
+    out = subprocess.run(["nm", "-D", "--defined-only", os.path.join(N.LIB_DIR, "libpathtracer_cuda.so")], capture_output=True, text=True).stdout
+    exported = set(re.findall(r" T (ptc_\w+)", out))
+    assert set(declared) <= exported
+    assert lib.ptc_version().decode().startswith("PathTracer_CUDA")
+
+
+def test_abi_struct_sizes():
+    assert C.sizeof(N.Config) == 48 and C.sizeof(N.SceneView) == 32 + 7 * 8 + 64
+    assert C.sizeof(N.Counters) == 17 * 8
+
+
+def test_no_cpu_fallback():
+    lib = N.cuda_lib()
+    if lib.ptc_device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    with pytest.raises(pt.PathTracerError) as e:
+        pt.PathTracerCUDA(16, 16)
+    assert e.value.code == N.PTC_ERR_NO_DEVICE and "no CPU path" in str(e.value)
+    with pytest.raises(RuntimeError):
+        pt.PathTracer_Main("cornell", 16, 16, 1)  # the controller returns false, as the reference's does on any device error
+
+
+def test_importer_conventions():
+    """Maya importer conventions restated by the procedural importer (Maya/PathTracer_MayaImporter.cpp:934-1047)."""
+    sc = pt.Scene("gallery", 32, 32, load_sky=True)
+    t = sc.triangles()
+    for v in ("S1", "S2", "S3"):
+        assert (t[v]["w"] == 1).all()  # points
+    for v in ("N1", "N2", "N3"):
+        assert (t[v]["w"] == 0).all()  # vectors
+        ln = np.sqrt(t[v]["x"] ** 2 + t[v]["y"] ** 2 + t[v]["z"] ** 2)
+        assert np.allclose(ln, 1, atol=1e-5)
+    assert (t["N"]["w"] == 1).all()  # host cross() returns w = 1 and normalize() keeps it
+
+    def lex_le(a, b):
+        return (a["x"] < b["x"]) | ((a["x"] == b["x"]) & (a["y"] < b["y"])) | ((a["x"] == b["x"]) & (a["y"] == b["y"]) & (a["z"] <= b["z"]))
+    assert lex_le(t["S1"], t["S2"]).all() and lex_le(t["S2"], t["S3"]).all()  # vertices stored in lexicographic order
+    m = sc.materials()
+    assert set(m["type"].tolist()) >= {0, 1, 2, 3, 4}
+    lt = sc.lights()
+    assert sorted(lt["type"].tolist()) == [0, 1, 2]
+    # deterministic
+    sc2 = pt.Scene("gallery", 32, 32, load_sky=True)
+    assert np.array_equal(sc2.triangles().view(np.uint8), t.view(np.uint8))
+    # black sky when loadSky = false: six 1x1 faces over one zero texel (MayaImporter.cpp:703-719)
+    assert pt.Scene("cornell", 8, 8).info.texturesDataSize == 1
+
+
+def test_unknown_scene_and_scene_sizes():
+    with pytest.raises(RuntimeError):
+        pt.Scene("no_such_scene", 8, 8)
+    assert pt.Scene("cornell", 8, 8).info.triangulationSize == 30
+    n = pt.Scene("atrium", 8, 8, build_bvh=False).info.triangulationSize
+    assert abs(n - 262144) / 262144 < 0.01  # BASELINE.json configs[2]: ~262k triangles
+
+
+def test_iteration_range_partition():
+    for total in (0, 1, 7, 256, 1024):
+        for world in (1, 2, 3, 8):
+            seen = []
+            for r in range(world):
+                b, n = iteration_range(r, world, 5, total)
+                seen += list(range(b, b + n))
+            assert seen == list(range(5, 5 + total))
+    with pytest.raises(ValueError):
+        iteration_range(2, 2, 0, 4)
+
+
+def test_bmp_writer(tmp_path):
+    """PathTracerDialog::PaintWindow writes NNN.bmp with the reference's conversion (Alone/PathTracer_bitmap.cpp:237-286)."""
+    exe = os.path.join(N.LIB_DIR, "pathtracer_alone")
+    assert os.path.exists(exe)
+    # without a GPU the stand-alone front-end must fail loudly (exit code 1), never render on the CPU
+    if N.cuda_lib().ptc_device_count() == 0:
+        r = subprocess.run([exe, "cornell", "16", "16", "1", "2", "0", "0", "1", str(tmp_path) + "/"], capture_output=True, text=True)
+        assert r.returncode == 1 and "ERROR" in r.stderr

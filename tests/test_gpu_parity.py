@@ -192,3 +192,28 @@ def test_controller_drop_in(ptref, scene_factory):
     bad = _rel_mismatch(out["imageColor"], ref["imageColor"]).mean()
     assert bad <= 5e-3
     assert out["rayDepths"].sum() == w * h * spp
+
+
+def test_gpu_against_committed_golden_vectors():
+    """Same checks against tests/golden/reference_vectors.npz (generated from the reference by tests/golden/make_golden.py),
+    so the parity claim does not depend on oracle/_ref being present on the GPU box."""
+    from golden_cases import CASES, key, load
+    g = load()
+    for name, w, h, sky, depth in CASES:
+        k = key(name)
+        sc = pt.Scene(name, w, h, load_sky=sky)
+        with pt.PathTracerCUDA(w, h, ray_max_depth=depth) as r:
+            r.upload(sc)
+            p = r.trace_primary(0)
+            rad = r.render_single(0)
+            r.render(0, 4)
+            color, nb = r.read_image()
+            d, b, t = r.read_stats()
+        for f in ("hit", "seed_after", "counts"):
+            assert np.array_equal(p[f], g[k + "_primary_" + f]), (name, f)
+        for f in ("st", "dist2", "dir"):
+            assert np.array_equal(p[f].view(np.uint32), g[k + "_primary_" + f].view(np.uint32)), (name, f)
+        assert _rel_mismatch(rad, g[k + "_radiance_it0"]).mean() <= 2e-3
+        assert np.array_equal(nb, g[k + "_acc4_imageRayNb"])
+        assert _rel_mismatch(color, g[k + "_acc4_imageColor"]).mean() <= 5e-3
+        assert np.abs(d.astype(np.int64) - g[k + "_acc4_rayDepths"].astype(np.int64)).sum() <= 4e-3 * w * h * 4 + 2
