@@ -9,6 +9,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -274,6 +275,9 @@ int ptc_create(const ptc_config *config, ptc_ctx **out_ctx)
     c->capacity = (size_t)b * c->nPix;
     c->lc.traverseGrid = c->smCount * traverse_ctas_per_sm(c->fast);
     c->lc.streamGrid = c->smCount * 8;
+    c->lc.refillMin = 8;
+    if (const char *e = std::getenv("PTC_REFILL_MIN")) c->lc.refillMin = (uint32_t)std::max(1, std::min(32, std::atoi(e)));
+    if (const char *e = std::getenv("PTC_CTAS_PER_SM")) c->lc.traverseGrid = c->smCount * std::max(1, std::atoi(e));
 
     cudaError_t e = cudaSuccess;
     auto A = [&](cudaError_t r) { if (e == cudaSuccess) e = r; };
@@ -325,6 +329,8 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
         return fail(ctx, PTC_ERR_LIMIT, "The scene has too many lights : it has %u and should be under %u", nL, PTC_MAX_LIGHT_SIZE);
     if (nT >= kMaxTriangles) return fail(ctx, PTC_ERR_LIMIT, "too many triangles (%u, limit %u)", nT, kMaxTriangles);
     if (nT && nN == 0) return fail(ctx, PTC_ERR_INVALID, "triangles without a BVH");
+    if ((uint64_t)ctx->capacity * (nL ? nL : 1) >= (1ull << 32))
+        return fail(ctx, PTC_ERR_LIMIT, "paths in flight (%zu) x lights (%u) exceeds 2^32: lower iterations_per_batch", ctx->capacity, nL);
     CK(cudaSetDevice(ctx->device));
 
     // ---- BVH: validate, measure depth, number the inner nodes in array (= depth-first) order
@@ -417,7 +423,13 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
         d.n = to4(t.N);
         d.p = make_float4(t.S1.x, t.S1.y, t.S1.z, hdot4(t.N, t.S1));
         d.e1 = make_float4(u.x, u.y, u.z, denom);
-        d.e2 = make_float4(v.x, v.y, v.z, 0.f);
+        uint32_t types = 0x55u;  // MAT_UNKNOWN on both sides if the indices are bad (reported below)
+        if (t.materialWithPositiveNormalIndex < nM && t.materialWithNegativeNormalIndex < nM)
+            types = ((uint32_t)s->materiaux[t.materialWithPositiveNormalIndex].type & 15u) |
+                    (((uint32_t)s->materiaux[t.materialWithNegativeNormalIndex].type & 15u) << 4);
+        float typesAsFloat;
+        std::memcpy(&typesAsFloat, &types, 4);
+        d.e2 = make_float4(v.x, v.y, v.z, typesAsFloat);
         hTris[i] = d;
         DevShade h;
         h.n1 = to4(t.N1); h.n2 = to4(t.N2); h.n3 = to4(t.N3);

@@ -37,7 +37,7 @@ struct __align__(16) DevTri
     float4 n;   // N.xyzw (w lane kept: SURVEY.md F8)
     float4 p;   // S1.xyz, d = dot4(N, S1)
     float4 e1;  // u = S2 - S1 (xyz), denom = 1 / (uv*uv - uu*vv)
-    float4 e2;  // v = S3 - S1 (xyz), unused
+    float4 e2;  // v = S3 - S1 (xyz), w = bits: MaterialType of the positive side (3..0) and of the negative side (7..4)
 };
 static_assert(sizeof(DevTri) == 64, "DevTri");
 

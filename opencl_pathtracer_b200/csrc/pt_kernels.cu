@@ -114,83 +114,119 @@ __device__ __forceinline__ void flush_work(Counters *cn, unsigned long long *ray
     }
 }
 
-template <bool FAST>
-__global__ void __launch_bounds__(kTraverseThreads) k_extend(SceneDev sc, PathState st, const uint32_t *__restrict__ queue,
-                                                            Counters *__restrict__ cn, int bounce)
-{
-    extern __shared__ uint32_t smemStack[];
-    uint32_t *stk = smemStack + threadIdx.x;
-    const uint32_t count = cn->qcount[bounce];
-    uint32_t nbSum = 0, ntSum = 0, nRays = 0;
-    uint32_t base;
-    while (fetch_chunk(&cn->curExtend[bounce], count, base))
-    {
-        const uint32_t k = base + (threadIdx.x & 31u);
-        if (k < count)
-        {
-            const uint32_t p = queue ? queue[k] : k;
-            const Ray r = make_ray(st.org[p], st.dir[p]);
-            int tri = -1;
-            float hs = 0.f, ht = 0.f, htp = 0.f;
-            uint32_t nb = 0, nt = 0;
-            traverse<false, FAST>(sc, r, INFINITY, tri, hs, ht, htp, nb, nt, stk, kTraverseThreads);
-            st.hit[p] = f4(__int_as_float(tri), hs, ht, htp);
-            st.nbbx[p] += nb;
-            st.ntri[p] += nt;
-            nbSum += nb; ntSum += nt; nRays++;
-        }
-    }
-    flush_work(cn, &cn->extensionRays, nRays, nbSum, ntSum);
-}
+// One kernel for both traversal stages. ANY = false: extend (closest hit, one item per queued path). ANY = true: connect
+// (any hit, one item per (queued path, light) pair).
+//
+// Warp-level scheduling (what keeps the SIMT lanes busy; none of it changes what a single ray does):
+//   * lane refill — a lane whose ray is finished takes the next item from the global cursor as soon as at least
+//     `refillMin` lanes of the warp are idle (one warp-aggregated atomicAdd), instead of waiting for the slowest ray of
+//     a fixed 32-ray chunk;
+//   * majority vote — each iteration the warp executes EITHER one inner-node step OR one triangle test, whichever more
+//     of its lanes are waiting for, so the two code paths are never serialised against each other.
+// The unlit / miss flags in st.occl (bits 31, 30) are written by extend and let connect skip items without loading the ray.
+constexpr uint32_t kOcclUnlit = 0x80000000u, kOcclMiss = 0x40000000u, kOcclMask = 0x3fffffffu;
 
-template <bool FAST>
-__global__ void __launch_bounds__(kTraverseThreads) k_connect(SceneDev sc, PathState st, const uint32_t *__restrict__ queue,
-                                                             Counters *__restrict__ cn, int bounce)
+template <bool ANY, bool FAST>
+__global__ void __launch_bounds__(kTraverseThreads) k_trace(SceneDev sc, PathState st, const uint32_t *__restrict__ queue,
+                                                           Counters *__restrict__ cn, int bounce, uint32_t refillMin)
 {
     extern __shared__ uint32_t smemStack[];
     uint32_t *stk = smemStack + threadIdx.x;
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned full = 0xffffffffu;
     const uint32_t count = cn->qcount[bounce];
+    const uint32_t nL = ANY ? sc.nLights : 1u;
+    const uint32_t total = count * nL;  // upload_scene guarantees capacity * nLights < 2^32
+    uint32_t *cursor = ANY ? &cn->curConnect[bounce] : &cn->curExtend[bounce];
+    TraceLane L;
+    L.cur = kDone;
+    bool have = false, exhausted = false;
+    uint32_t p = 0, li = 0;
     uint32_t nbSum = 0, ntSum = 0, nRays = 0;
-    uint32_t base;
-    while (fetch_chunk(&cn->curConnect[bounce], count, base))
+    while (true)
     {
-        const uint32_t k = base + (threadIdx.x & 31u);
-        if (k >= count) continue;
-        const uint32_t p = queue ? queue[k] : k;
-        const float4 h = st.hit[p];
-        const int htri = __float_as_int(h.x);
-        if (htri < 0) continue;  // miss: no direct lighting
-        const float4 o = st.org[p], d = st.dir[p];
-        const float4 q = f4(o.x + d.x * h.w, o.y + d.y * h.w, o.z + d.z * h.w, o.w + d.w * h.w);  // :538
-        uint32_t occl = 0, nb = 0, nt = 0;
-        bool lit = true;
-        if (FAST)
+        // ---- refill idle lanes
+        const unsigned idle = __ballot_sync(full, !have);
+        if (!exhausted && ((uint32_t)__popc(idle) >= refillMin || idle == full))
         {
-            // GLASS / WATER / METAL / UNKNOWN never read the direct light (:805-843): their shadow rays
-            // cannot change the image and are not traced
-            const float4 n = __ldg(&sc.tris[htri].n);
-            const uint4 ids = __ldg(&sc.shade[htri].ids);
-            const int mtype = sc.materials[dot4(n, d) < 0 ? ids.x : ids.y].type;
-            lit = (mtype == 0 || mtype == 3);
-        }
-        if (lit)
-            for (uint32_t li = 0; li < sc.nLights; li++)
+            const uint32_t n = (uint32_t)__popc(idle);
+            uint32_t base = 0;
+            if (lane == 0) base = atomicAdd(cursor, n);
+            base = __shfl_sync(full, base, 0);
+            if (base >= total || total - base <= n) exhausted = true;
+            if (!have)
             {
-                float4 ldir;
-                float bound;
-                shadow_setup(sc.lights[li], q, ldir, bound);
-                const Ray r = make_ray(q, ldir);
-                int tri;
-                float hs, ht, htp;
-                if (traverse<true, FAST>(sc, r, bound, tri, hs, ht, htp, nb, nt, stk, kTraverseThreads)) occl |= 1u << li;
-                nRays++;
+                const uint32_t k = base + (uint32_t)__popc(idle & ((1u << lane) - 1u));
+                if (base < total && k < total)
+                {
+                    if (!ANY)
+                    {
+                        p = queue ? queue[k] : k;
+                        lane_start(L, sc, make_ray(st.org[p], st.dir[p]), INFINITY);
+                        have = true;
+                    }
+                    else
+                    {
+                        const uint32_t kp = k / nL;
+                        li = k - kp * nL;
+                        p = queue ? queue[kp] : kp;
+                        if (!(st.occl[p] & (kOcclUnlit | kOcclMiss)))
+                        {
+                            const float4 h = st.hit[p], o = st.org[p], d = st.dir[p];
+                            const float4 q = f4(o.x + d.x * h.w, o.y + d.y * h.w, o.z + d.z * h.w, o.w + d.w * h.w);  // :538
+                            float4 ldir;
+                            float bound;
+                            shadow_setup(sc.lights[li], q, ldir, bound);
+                            lane_start(L, sc, make_ray(q, ldir), bound);
+                            have = true;
+                        }
+                    }
+                }
             }
-        st.occl[p] = occl;
-        st.nbbx[p] += nb;  // :946-947 the camera ray inherits its shadow rays' counters
-        st.ntri[p] += nt;
-        nbSum += nb; ntSum += nt;
+        }
+        if (!__any_sync(full, have))
+        {
+            if (exhausted) break;
+            continue;
+        }
+        // ---- one step for the majority
+        const bool wantNode = have && lane_at_inner(L);
+        const bool wantTri = have && lane_at_leaf(L);
+        const unsigned mN = __ballot_sync(full, wantNode), mT = __ballot_sync(full, wantTri);
+        if (__popc(mN) >= __popc(mT))
+        {
+            if (wantNode) node_step<FAST>(L, sc, stk, kTraverseThreads);
+        }
+        else if (wantTri)
+        {
+            if (!ANY) tri_step<false>(L, sc, stk, kTraverseThreads);
+            else
+                tri_step<true>(L, sc, stk, kTraverseThreads);
+        }
+        // ---- completion
+        if (have && L.cur == kDone)
+        {
+            if (!ANY)
+            {
+                st.hit[p] = f4(__int_as_float(L.hitTri), L.hs, L.ht, L.htp);
+                st.nbbx[p] += L.nb;
+                st.ntri[p] += L.nt;
+                uint32_t flags = 0;
+                if (L.hitTri < 0) flags = kOcclMiss;
+                else if (FAST && !(L.hmat == 0u || L.hmat == 3u)) flags = kOcclUnlit;  // GLASS / WATER / METAL / UNKNOWN never read the direct light (:805-843)
+                st.occl[p] = flags;
+            }
+            else
+            {
+                if (L.found) atomicOr(&st.occl[p], 1u << li);
+                if (L.nb) atomicAdd(&st.nbbx[p], L.nb);  // :946-947 the camera ray inherits its shadow rays' counters
+                if (L.nt) atomicAdd(&st.ntri[p], L.nt);
+            }
+            nbSum += L.nb; ntSum += L.nt; nRays++;
+            have = false;
+        }
     }
-    flush_work(cn, &cn->shadowRays, nRays, nbSum, ntSum);
+    flush_work(cn, ANY ? &cn->shadowRays : &cn->extensionRays, nRays, nbSum, ntSum);
 }
 
 // ------------------------------------------------------------------------------------------------ shade
@@ -253,7 +289,7 @@ __global__ void __launch_bounds__(kStreamThreads) k_shade(SceneDev sc, FramePara
                 Ns = normalize4(Ns);
                 // :901-954 direct illumination from the occlusion bits the connect stage left
                 float4 L = f4(0, 0, 0, 0);
-                const uint32_t occl = st.occl[p];
+                const uint32_t occl = st.occl[p] & kOcclMask;
                 if (!FAST || mat.type == 0 || mat.type == 3)
                     for (uint32_t li = 0; li < sc.nLights; li++)
                     {
@@ -470,19 +506,18 @@ __global__ void k_add_image(ImageDev img, uint32_t nPixels, const float4 *color,
 // ------------------------------------------------------------------------------------------------ launchers
 static const size_t kStackBytes = (size_t)kStackDepth * kTraverseThreads * sizeof(uint32_t);
 
+template <bool ANY, bool FAST>
+static int occupancy_of()
+{
+    int n = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_trace<ANY, FAST>, kTraverseThreads, kStackBytes);
+    return n;
+}
+
 int traverse_ctas_per_sm(bool fast)
 {
-    int n = 0, m = 0;
-    if (fast)
-    {
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_extend<true>, kTraverseThreads, kStackBytes);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&m, k_connect<true>, kTraverseThreads, kStackBytes);
-    }
-    else
-    {
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_extend<false>, kTraverseThreads, kStackBytes);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&m, k_connect<false>, kTraverseThreads, kStackBytes);
-    }
+    int n = fast ? occupancy_of<false, true>() : occupancy_of<false, false>();
+    int m = fast ? occupancy_of<true, true>() : occupancy_of<true, false>();
     n = n < m ? n : m;
     return n < 1 ? 1 : n;
 }
@@ -497,15 +532,15 @@ void launch_generate(cudaStream_t s, const LaunchCfg &lc, const FrameParams &fp,
 void launch_extend(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const PathState &st, const uint32_t *queue,
                    Counters *cn, int bounce)
 {
-    if (fast) k_extend<true><<<lc.traverseGrid, kTraverseThreads, kStackBytes, s>>>(sc, st, queue, cn, bounce);
-    else k_extend<false><<<lc.traverseGrid, kTraverseThreads, kStackBytes, s>>>(sc, st, queue, cn, bounce);
+    if (fast) k_trace<false, true><<<lc.traverseGrid, kTraverseThreads, kStackBytes, s>>>(sc, st, queue, cn, bounce, lc.refillMin);
+    else k_trace<false, false><<<lc.traverseGrid, kTraverseThreads, kStackBytes, s>>>(sc, st, queue, cn, bounce, lc.refillMin);
 }
 
 void launch_connect(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const PathState &st, const uint32_t *queue,
                     Counters *cn, int bounce)
 {
-    if (fast) k_connect<true><<<lc.traverseGrid, kTraverseThreads, kStackBytes, s>>>(sc, st, queue, cn, bounce);
-    else k_connect<false><<<lc.traverseGrid, kTraverseThreads, kStackBytes, s>>>(sc, st, queue, cn, bounce);
+    if (fast) k_trace<true, true><<<lc.traverseGrid, kTraverseThreads, kStackBytes, s>>>(sc, st, queue, cn, bounce, lc.refillMin);
+    else k_trace<true, false><<<lc.traverseGrid, kTraverseThreads, kStackBytes, s>>>(sc, st, queue, cn, bounce, lc.refillMin);
 }
 
 void launch_shade(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const FrameParams &fp, const PathState &st,

@@ -9,6 +9,7 @@ struct LaunchCfg
 {
     int traverseGrid;  // persistent extend / connect CTAs (multiple of the SM count)
     int streamGrid;    // grid of the streaming stages (generate / shade / accumulate)
+    uint32_t refillMin;  // idle lanes of a warp that trigger a refill from the work cursor (1..32)
 };
 
 int traverse_ctas_per_sm(bool fast);

@@ -1,23 +1,25 @@
-// pt_traverse.cuh — ray/box, ray/triangle and BVH2 traversal of the extend / connect stages.
+// pt_traverse.cuh — ray/box and ray/triangle tests and the warp-cooperative BVH2 traversal loop of the extend /
+// connect stages.
 //
 // Stage -> reference function map (Kernel/PathTracer_FullKernel.cl):
-//   box_test   BoundingBox_Intersects :64-139
-//   tri_test   Triangle_Intersects    :519-566 (geometric half; the material / colour half :568-586 is
-//              evaluated once per final hit by the shade stage)
-//   traverse   BVH_IntersectRay :620-702 (ANY = false), BVH_IntersectShadowRay :705-783 (ANY = true)
+//   box_test / box_test_ref   BoundingBox_Intersects :64-139
+//   tri_test                  Triangle_Intersects    :519-566 (geometric half; the material / colour half :568-586
+//                             is evaluated once per final hit by the shade stage)
+//   TraceLane::node_step / tri_step: one iteration of BVH_IntersectRay :620-702 (ANY = false) or
+//                             BVH_IntersectShadowRay :705-783 (ANY = true)
 //
-// Arithmetic: this translation unit is compiled with -fmad=false; every expression below keeps the
-// reference's association order, so all comparisons see bit-identical values in both modes.
+// Arithmetic: this translation unit is compiled with -fmad=false; every expression keeps the reference's
+// association order, so all comparisons see bit-identical values in both modes.
 //
 // Modes (template parameter FAST):
-//   PARITY  the last line of BoundingBox_Intersects compares the LINEAR entry distance with the
-//           SQUARED best distance (closest hit) or with the LINEAR light distance that the triangle
-//           test then compares with squared distances (shadow) — SURVEY.md F9a/F9b, kept as is.
-//   FAST    the same threshold is a squared distance in every use, so a box is skipped when
-//           tMin^2 > threshold (with a 1e-5 relative margin that keeps the cull conservative under
-//           rounding). Traversal order, triangle arithmetic and tie-break are unchanged, so the hit is
-//           the one the reference finds whenever the reference's own culling did not discard the true
-//           closest hit (only possible for hit distances < 1 scene unit).
+//   PARITY  the last line of BoundingBox_Intersects compares the LINEAR entry distance with the SQUARED best
+//           distance (closest hit) or with the LINEAR light distance that the triangle test then compares with
+//           squared distances (shadow) — SURVEY.md F9a/F9b, kept as is.
+//   FAST    the same threshold is a squared distance in every use, so a box is skipped when tMin^2 > threshold
+//           (with a 1e-5 relative margin that keeps the cull conservative under rounding). Traversal order,
+//           triangle arithmetic and tie-break are unchanged, so the hit is the one the reference finds whenever
+//           the reference's own culling did not discard the true closest hit (only possible for hit distances
+//           < 1 scene unit).
 #pragma once
 
 #include "pt_device.cuh"
@@ -43,35 +45,69 @@ __device__ __forceinline__ Ray make_ray(float4 o, float4 d)
     return r;
 }
 
-// BoundingBox_Intersects as one boolean expression over the same comparisons on the same values (the
-// early returns of the reference only decide the result, they have no side effect).
-template <bool FAST>
-__device__ __forceinline__ bool box_test(float nx, float ny, float nz, float xx, float xy, float xz, const Ray &r, float best)
+// A ray whose origin and reciprocal direction are all finite can only produce finite or infinite slab
+// distances (never NaN: no 0*inf, no inf-inf), which is what the min/max formulation below relies on.
+__device__ __forceinline__ bool ray_is_regular(const Ray &r)
 {
-    const bool px = r.dx > 0, py = r.dy > 0, pz = r.dz > 0;
-    float tMin = ((px ? nx : xx) - r.ox) * r.ix;
-    float tMax = ((px ? xx : nx) - r.ox) * r.ix;
+    const float big = 3.0e38f;
+    return fabsf(r.ox) < big && fabsf(r.oy) < big && fabsf(r.oz) < big && fabsf(r.ix) < big && fabsf(r.iy) < big && fabsf(r.iz) < big;
+}
+
+template <bool FAST>
+__device__ __forceinline__ bool box_final(float tMin, float best)
+{
+    if (FAST) return tMin < 0 || !(tMin * tMin > best * 1.00001f);
+    return tMin < 0 || !(tMin > best);  // :132-138
+}
+
+// BoundingBox_Intersects statement by statement (one boolean expression over the same comparisons on the same
+// values: the early returns of the reference only decide the result). Used for rays that are not "regular".
+template <bool FAST>
+__device__ __noinline__ bool box_test_ref(float nx, float ny, float nz, float xx, float xy, float xz, float ox, float oy, float oz,
+                                          float dx, float dy, float dz, float ix, float iy, float iz, float best)
+{
+    const bool px = dx > 0, py = dy > 0, pz = dz > 0;
+    float tMin = ((px ? nx : xx) - ox) * ix;
+    float tMax = ((px ? xx : nx) - ox) * ix;
     bool rej = (tMin < 0 && tMax < 0);
-    const float tyMin = ((py ? ny : xy) - r.oy) * r.iy;
-    const float tyMax = ((py ? xy : ny) - r.oy) * r.iy;
+    const float tyMin = ((py ? ny : xy) - oy) * iy;
+    const float tyMax = ((py ? xy : ny) - oy) * iy;
     rej |= (tyMin < 0 && tyMax < 0);
     rej |= (tMin > tyMax || tyMin > tMax);
     if (tyMin > tMin) tMin = tyMin;
     if (tyMax < tMax) tMax = tyMax;
-    const float tzMin = ((pz ? nz : xz) - r.oz) * r.iz;
-    const float tzMax = ((pz ? xz : nz) - r.oz) * r.iz;
+    const float tzMin = ((pz ? nz : xz) - oz) * iz;
+    const float tzMax = ((pz ? xz : nz) - oz) * iz;
     rej |= (tzMin < 0 && tzMax < 0);
     rej |= (tMin > tzMax || tzMin > tMax);
     if (tzMin > tMin) tMin = tzMin;
-    if (FAST) return !rej && (tMin < 0 || !(tMin * tMin > best * 1.00001f));
-    return !rej && (tMin < 0 || !(tMin > best));
+    return !rej && box_final<FAST>(tMin, best);
 }
 
-// uv/uu/vv are recomputed from the stored edges with the reference's association order; denom and d are
-// stored (ray independent, computed at upload with the same IEEE operations). The w lanes of the edge
-// dot products are exactly zero for conformant data (upload checks S1.w == S2.w == S3.w) and omitted.
+// The same predicate for regular rays. With t1 = (pMin - o) * inv and t2 = (pMax - o) * inv per axis (the very
+// products the reference forms; which one it calls "min" depends on the sign of the direction), near = min(t1,t2)
+// and far = max(t1,t2) per axis are the reference's tMin/tMax of that axis (near <= far by monotonicity of
+// rounding). Its tests are then: far < 0 on any axis -> reject (:85,:99,:121); pairwise interval overlap (:102,
+// :124), which for three intervals is max(near) <= min(far); finally the distance test on tMin = max(near).
+// No NaN can occur for a regular ray, so every comparison has the reference's outcome.
+template <bool FAST>
+__device__ __forceinline__ bool box_test(float nx, float ny, float nz, float xx, float xy, float xz, const Ray &r, float best)
+{
+    const float ax = (nx - r.ox) * r.ix, bx = (xx - r.ox) * r.ix;
+    const float ay = (ny - r.oy) * r.iy, by = (xy - r.oy) * r.iy;
+    const float az = (nz - r.oz) * r.iz, bz = (xz - r.oz) * r.iz;
+    const float tEnter = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fminf(az, bz));
+    const float tExit = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
+    return !(tExit < 0) && !(tEnter > tExit) && box_final<FAST>(tEnter, best);
+}
+
+// uv/uu/vv are recomputed from the stored edges with the reference's association order; denom and d are stored (ray
+// independent, computed at upload with the same IEEE operations). The w lanes of the edge dot products are exactly
+// zero for conformant data (upload checks S1.w == S2.w == S3.w) and omitted.
+// On acceptance hmat receives the MaterialType of the side that was hit (:568): both sides' types ride in the spare
+// lane of the record (e2.w, bits 3..0 positive side, bits 7..4 negative side).
 __device__ __forceinline__ bool tri_test(const DevTri *__restrict__ tris, uint32_t i, const Ray &r, float &best, float &hs,
-                                         float &ht, float &htp)
+                                         float &ht, float &htp, uint32_t &hmat)
 {
     const float4 n = __ldg(&tris[i].n);
     const float4 p = __ldg(&tris[i].p);
@@ -98,69 +134,124 @@ __device__ __forceinline__ bool tri_test(const DevTri *__restrict__ tris, uint32
     if ((((fx * r.dx + fy * r.dy) + fz * r.dz) + fw * r.dw) < 0) return false;
     best = nsd;
     hs = s; ht = t; htp = tp;
+    const uint32_t types = __float_as_uint(e2.w);
+    hmat = nd < 0 ? (types & 15u) : ((types >> 4) & 15u);
     return true;
 }
 
-// One ray through the BVH2 in the reference's order: children ordered by the sign of
-// direction[cutAxis] (:660-669), both boxes tested, near descended, far pushed; leaves scanned in
-// array order; a candidate at equal distance replaces the previous one (:543 is a strict test).
-// `stk` points at this thread's column of a [level][thread] shared-memory stack (conflict-free).
-template <bool ANY, bool FAST>
-__device__ __forceinline__ bool traverse(const SceneDev &sc, const Ray &r, float best, int &hitTri, float &hs, float &ht,
-                                         float &htp, uint32_t &nb, uint32_t &nt, uint32_t *stk, const int stride)
+// Per-lane traversal state. One ray is walked through the BVH2 in the reference's order: children ordered by the sign
+// of direction[cutAxis] (:660-669), both boxes tested, near descended, far pushed; leaves scanned in array order, one
+// triangle per tri_step; a candidate at equal distance replaces the previous one (:543 is a strict test).
+// The warp decides each iteration whether its lanes take a node step or a triangle step (see k_trace), so the state
+// machine is explicit: cur is an inner-node reference, a leaf being scanned (ti < te), or kDone.
+constexpr uint32_t kDone = 0xfffffffeu;
+
+struct TraceLane
 {
-    uint32_t cur = sc.rootRef;
-    if (cur == kInvalidRef) return false;
-    int sp = 0;
-    bool hit = false;
-    while (true)
+    Ray r;
+    float best;
+    uint32_t cur;     // inner node index, or kLeafBit-tagged while a leaf is being scanned, or kDone
+    uint32_t ti, te;  // triangle cursor / end of the leaf being scanned
+    int sp;
+    int hitTri;
+    float hs, ht, htp;
+    uint32_t hmat;    // MaterialType of the hit side
+    uint32_t nb, nt;
+    bool regular;
+    bool found;       // ANY: an occluder was accepted
+};
+
+__device__ __forceinline__ void lane_enter(TraceLane &L, const SceneDev &sc, uint32_t ref)
+{
+    // ref: child reference word of pt_device.cuh
+    if (ref & kLeafBit)
     {
-        if (cur & kLeafBit)
-        {
-            const uint32_t start = (cur & 0x7fffffffu) >> 4;
-            uint32_t cnt = cur & 15u;
-            if (cnt == 0) cnt = __ldg(&sc.bigLeafCount[start]);
-            for (uint32_t i = start; i < start + cnt; i++)
-            {
-                nt++;
-                if (tri_test(sc.tris, i, r, best, hs, ht, htp))
-                {
-                    if (ANY) return true;
-                    hit = true;
-                    hitTri = (int)i;
-                }
-            }
-            if (sp == 0) break;
-            cur = stk[(--sp) * stride];
-        }
-        else
-        {
-            const DevNode *nd = &sc.nodes[cur];
-            const float4 a = __ldg(&nd->a), b = __ldg(&nd->b), c = __ldg(&nd->c);
-            const uint4 d = __ldg(&nd->d);
-            nb += 2;
-            const bool bL = !(d.z & 4u) && box_test<FAST>(a.x, a.y, a.z, a.w, b.x, b.y, r, best);
-            const bool bR = !(d.z & 8u) && box_test<FAST>(b.z, b.w, c.x, c.y, c.z, c.w, r, best);
-            const uint32_t axis = d.z & 3u;
-            const float da = axis == 0 ? r.dx : (axis == 1 ? r.dy : r.dz);
-            const bool leftFirst = da > 0;
-            const uint32_t first = leftFirst ? d.x : d.y, second = leftFirst ? d.y : d.x;
-            const bool b1 = leftFirst ? bL : bR, b2 = leftFirst ? bR : bL;
-            if (b1)
-            {
-                if (b2) stk[(sp++) * stride] = second;
-                cur = first;
-            }
-            else if (b2)
-                cur = second;
-            else
-            {
-                if (sp == 0) break;
-                cur = stk[(--sp) * stride];
-            }
-        }
+        const uint32_t start = (ref & 0x7fffffffu) >> 4;
+        uint32_t cnt = ref & 15u;
+        if (cnt == 0) cnt = __ldg(&sc.bigLeafCount[start]);
+        L.ti = start;
+        L.te = start + cnt;
     }
-    return hit;
+    L.cur = ref;
+}
+
+__device__ __forceinline__ void lane_pop(TraceLane &L, const SceneDev &sc, const uint32_t *stk, const int stride)
+{
+    if (L.sp == 0) L.cur = kDone;
+    else lane_enter(L, sc, stk[(--L.sp) * stride]);
+}
+
+__device__ __forceinline__ void lane_start(TraceLane &L, const SceneDev &sc, const Ray &r, float best)
+{
+    L.r = r;
+    L.best = best;
+    L.sp = 0;
+    L.hitTri = -1;
+    L.hs = L.ht = L.htp = 0.f;
+    L.hmat = 0;
+    L.nb = L.nt = 0;
+    L.found = false;
+    L.regular = ray_is_regular(r);
+    L.ti = L.te = 0;
+    if (sc.rootRef == kInvalidRef) L.cur = kDone;
+    else lane_enter(L, sc, sc.rootRef);
+}
+
+__device__ __forceinline__ bool lane_at_inner(const TraceLane &L) { return !(L.cur & kLeafBit); }  // kDone has the leaf bit
+__device__ __forceinline__ bool lane_at_leaf(const TraceLane &L) { return (L.cur & kLeafBit) && L.cur != kDone; }
+
+template <bool FAST>
+__device__ __forceinline__ void node_step(TraceLane &L, const SceneDev &sc, uint32_t *stk, const int stride)
+{
+    const DevNode *nd = &sc.nodes[L.cur];
+    const float4 a = __ldg(&nd->a), b = __ldg(&nd->b), c = __ldg(&nd->c);
+    const uint4 d = __ldg(&nd->d);
+    L.nb += 2;
+    bool bL, bR;
+    if (L.regular)
+    {
+        bL = box_test<FAST>(a.x, a.y, a.z, a.w, b.x, b.y, L.r, L.best);
+        bR = box_test<FAST>(b.z, b.w, c.x, c.y, c.z, c.w, L.r, L.best);
+    }
+    else
+    {
+        const Ray &r = L.r;
+        bL = box_test_ref<FAST>(a.x, a.y, a.z, a.w, b.x, b.y, r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, r.ix, r.iy, r.iz, L.best);
+        bR = box_test_ref<FAST>(b.z, b.w, c.x, c.y, c.z, c.w, r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, r.ix, r.iy, r.iz, L.best);
+    }
+    bL = bL && !(d.z & 4u);
+    bR = bR && !(d.z & 8u);
+    const uint32_t axis = d.z & 3u;
+    const float da = axis == 0 ? L.r.dx : (axis == 1 ? L.r.dy : L.r.dz);
+    const bool leftFirst = da > 0;
+    const uint32_t first = leftFirst ? d.x : d.y, second = leftFirst ? d.y : d.x;
+    const bool b1 = leftFirst ? bL : bR, b2 = leftFirst ? bR : bL;
+    if (b1)
+    {
+        if (b2) stk[(L.sp++) * stride] = second;
+        lane_enter(L, sc, first);
+    }
+    else if (b2)
+        lane_enter(L, sc, second);
+    else
+        lane_pop(L, sc, stk, stride);
+}
+
+template <bool ANY>
+__device__ __forceinline__ void tri_step(TraceLane &L, const SceneDev &sc, const uint32_t *stk, const int stride)
+{
+    L.nt++;
+    if (tri_test(sc.tris, L.ti, L.r, L.best, L.hs, L.ht, L.htp, L.hmat))
+    {
+        if (ANY)
+        {
+            L.found = true;
+            L.cur = kDone;
+            return;
+        }
+        L.hitTri = (int)L.ti;
+    }
+    if (++L.ti == L.te) lane_pop(L, sc, stk, stride);
 }
 
 }  // namespace ptc

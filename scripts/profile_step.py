@@ -1,17 +1,29 @@
 #!/usr/bin/env python3
-"""One short render of the bench workload for ncu captures: atrium 1080p, FAST mode, `spp` iterations in one batch."""
-import sys
+"""One short render of the bench workload for ncu captures and tuning sweeps: atrium 1080p, `spp` iterations in one batch.
+usage: profile_step.py [spp] [fast|parity] [scene] [repeat]"""
 import os
+import sys
+import time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import opencl_pathtracer_b200 as pt
 
 spp = int(sys.argv[1]) if len(sys.argv) > 1 else 2
 mode = pt.MODE_PARITY if (len(sys.argv) > 2 and sys.argv[2] == "parity") else pt.MODE_FAST
 scene_name = sys.argv[3] if len(sys.argv) > 3 else "atrium"
+repeat = int(sys.argv[4]) if len(sys.argv) > 4 else 1
 W, H = 1920, 1080
 sc = pt.Scene(scene_name, W, H)
-with pt.PathTracerCUDA(W, H, mode=mode, flags=pt.FLAG_NO_VARIANCE, iterations_per_batch=spp) as r:
+with pt.PathTracerCUDA(W, H, mode=mode, flags=pt.FLAG_NO_VARIANCE | pt.FLAG_STAGE_TIMING, iterations_per_batch=spp) as r:
     r.upload(sc)
     r.render(0, spp, sync=True)
+    r.reset()
+    t0 = time.perf_counter()
+    for i in range(repeat):
+        r.render(spp * (i + 1), spp)
+    r.synchronize()
+    dt = time.perf_counter() - t0
     c = r.counters()
-    print({k: c[k] for k in ("paths", "extension_rays", "shadow_rays", "box_tests", "triangle_tests", "kernel_launches")})
+    rays = c["extension_rays"] + c["shadow_rays"]
+    print("env REFILL=%s CTAS=%s | %.1f Msamples/s %.0f Mrays/s | ms: ext %.1f con %.1f shade %.1f acc %.1f | box/path %.0f tri/path %.0f" % (
+        os.environ.get("PTC_REFILL_MIN"), os.environ.get("PTC_CTAS_PER_SM"), c["paths"] / dt / 1e6, rays / dt / 1e6,
+        c["ms_extend"], c["ms_connect"], c["ms_shade"], c["ms_accumulate"], c["box_tests"] / c["paths"], c["triangle_tests"] / c["paths"]))
