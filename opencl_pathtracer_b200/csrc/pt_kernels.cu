@@ -139,72 +139,17 @@ __global__ void __launch_bounds__(kTraverseThreads) k_trace(SceneDev sc, PathSta
     const uint32_t total = count * nL;  // upload_scene guarantees capacity * nLights < 2^32
     uint32_t *cursor = ANY ? &cn->curConnect[bounce] : &cn->curExtend[bounce];
     TraceLane L;
-    L.cur = kDone;
-    bool have = false, exhausted = false;
+    L.cur = kIdle;
+    L.nb = L.nt = 0;
+    L.found = false;
+    L.hitTri = -1;
+    bool exhausted = false;
     uint32_t p = 0, li = 0;
     uint32_t nbSum = 0, ntSum = 0, nRays = 0;
     while (true)
     {
-        // ---- refill idle lanes
-        const unsigned idle = __ballot_sync(full, !have);
-        if (!exhausted && ((uint32_t)__popc(idle) >= refillMin || idle == full))
-        {
-            const uint32_t n = (uint32_t)__popc(idle);
-            uint32_t base = 0;
-            if (lane == 0) base = atomicAdd(cursor, n);
-            base = __shfl_sync(full, base, 0);
-            if (base >= total || total - base <= n) exhausted = true;
-            if (!have)
-            {
-                const uint32_t k = base + (uint32_t)__popc(idle & ((1u << lane) - 1u));
-                if (base < total && k < total)
-                {
-                    if (!ANY)
-                    {
-                        p = queue ? queue[k] : k;
-                        lane_start(L, sc, make_ray(st.org[p], st.dir[p]), INFINITY);
-                        have = true;
-                    }
-                    else
-                    {
-                        const uint32_t kp = k / nL;
-                        li = k - kp * nL;
-                        p = queue ? queue[kp] : kp;
-                        if (!(st.occl[p] & (kOcclUnlit | kOcclMiss)))
-                        {
-                            const float4 h = st.hit[p], o = st.org[p], d = st.dir[p];
-                            const float4 q = f4(o.x + d.x * h.w, o.y + d.y * h.w, o.z + d.z * h.w, o.w + d.w * h.w);  // :538
-                            float4 ldir;
-                            float bound;
-                            shadow_setup(sc.lights[li], q, ldir, bound);
-                            lane_start(L, sc, make_ray(q, ldir), bound);
-                            have = true;
-                        }
-                    }
-                }
-            }
-        }
-        if (!__any_sync(full, have))
-        {
-            if (exhausted) break;
-            continue;
-        }
-        // ---- one step for the majority
-        const bool wantNode = have && lane_at_inner(L);
-        const bool wantTri = have && lane_at_leaf(L);
-        const unsigned mN = __ballot_sync(full, wantNode), mT = __ballot_sync(full, wantTri);
-        if (__popc(mN) >= __popc(mT))
-        {
-            if (wantNode) node_step<FAST>(L, sc, stk, kTraverseThreads);
-        }
-        else if (wantTri)
-        {
-            if (!ANY) tri_step<false>(L, sc, stk, kTraverseThreads);
-            else
-                tri_step<true>(L, sc, stk, kTraverseThreads);
-        }
-        // ---- completion
-        if (have && L.cur == kDone)
+        // ---- completion: write the result of a finished ray
+        if (L.cur == kDone)
         {
             if (!ANY)
             {
@@ -223,7 +168,63 @@ __global__ void __launch_bounds__(kTraverseThreads) k_trace(SceneDev sc, PathSta
                 if (L.nt) atomicAdd(&st.ntri[p], L.nt);
             }
             nbSum += L.nb; ntSum += L.nt; nRays++;
-            have = false;
+            L.cur = kIdle;
+        }
+        // ---- refill idle lanes from the work cursor
+        const unsigned idle = __ballot_sync(full, L.cur == kIdle);
+        if (!exhausted && (uint32_t)__popc(idle) >= refillMin)
+        {
+            const uint32_t n = (uint32_t)__popc(idle);
+            uint32_t base = 0;
+            if (lane == 0) base = atomicAdd(cursor, n);
+            base = __shfl_sync(full, base, 0);
+            if (base >= total || total - base <= n) exhausted = true;
+            const uint32_t k = base + (uint32_t)__popc(idle & ((1u << lane) - 1u));
+            if (L.cur == kIdle && base < total && k < total)
+            {
+                if (!ANY)
+                {
+                    p = queue ? queue[k] : k;
+                    lane_start(L, sc, make_ray(st.org[p], st.dir[p]), INFINITY);
+                }
+                else
+                {
+                    const uint32_t kp = k / nL;
+                    li = k - kp * nL;
+                    p = queue ? queue[kp] : kp;
+                    if (!(st.occl[p] & (kOcclUnlit | kOcclMiss)))
+                    {
+                        const float4 h = st.hit[p], o = st.org[p], d = st.dir[p];
+                        const float4 q = f4(o.x + d.x * h.w, o.y + d.y * h.w, o.z + d.z * h.w, o.w + d.w * h.w);  // :538
+                        float4 ldir;
+                        float bound;
+                        shadow_setup(sc.lights[li], q, ldir, bound);
+                        lane_start(L, sc, make_ray(q, ldir), bound);
+                    }
+                }
+            }
+            continue;  // lanes that drew an item needing no trace stay idle: look again
+        }
+        if (idle == full)
+        {
+            if (exhausted) break;
+            continue;  // (only reachable with refillMin > 32)
+        }
+        // ---- node phase: node steps while at least as many lanes wait for a node as for a triangle
+        while (true)
+        {
+            const bool wantNode = lane_at_inner(L);
+            const int nN = __popc(__ballot_sync(full, wantNode)), nT = __popc(__ballot_sync(full, lane_at_leaf(L)));
+            if (nN == 0 || nN < nT) break;
+            if (wantNode) node_step<FAST>(L, sc, stk, kTraverseThreads);
+        }
+        // ---- triangle phase
+        while (true)
+        {
+            const bool wantTri = lane_at_leaf(L);
+            const int nT = __popc(__ballot_sync(full, wantTri)), nN = __popc(__ballot_sync(full, lane_at_inner(L)));
+            if (nT == 0 || nT <= nN) break;
+            if (wantTri) tri_step<ANY>(L, sc, stk, kTraverseThreads);
         }
     }
     flush_work(cn, ANY ? &cn->shadowRays : &cn->extensionRays, nRays, nbSum, ntSum);

@@ -142,15 +142,16 @@ __device__ __forceinline__ bool tri_test(const DevTri *__restrict__ tris, uint32
 // Per-lane traversal state. One ray is walked through the BVH2 in the reference's order: children ordered by the sign
 // of direction[cutAxis] (:660-669), both boxes tested, near descended, far pushed; leaves scanned in array order, one
 // triangle per tri_step; a candidate at equal distance replaces the previous one (:543 is a strict test).
-// The warp decides each iteration whether its lanes take a node step or a triangle step (see k_trace), so the state
-// machine is explicit: cur is an inner-node reference, a leaf being scanned (ti < te), or kDone.
-constexpr uint32_t kDone = 0xfffffffeu;
+// The warp decides whether its lanes take node steps or triangle steps (see k_trace), so the state machine is
+// explicit: cur is an inner-node index, a leaf reference while the leaf is being scanned (ti < te), kDone (ray
+// finished, result not yet written) or kIdle (no ray).
+constexpr uint32_t kDone = 0xfffffffeu, kIdle = 0xffffffffu;
 
 struct TraceLane
 {
     Ray r;
     float best;
-    uint32_t cur;     // inner node index, or kLeafBit-tagged while a leaf is being scanned, or kDone
+    uint32_t cur;
     uint32_t ti, te;  // triangle cursor / end of the leaf being scanned
     int sp;
     int hitTri;
@@ -161,24 +162,19 @@ struct TraceLane
     bool found;       // ANY: an occluder was accepted
 };
 
+__device__ __forceinline__ bool lane_at_inner(const TraceLane &L) { return !(L.cur & kLeafBit); }
+__device__ __forceinline__ bool lane_at_leaf(const TraceLane &L) { return (L.cur & kLeafBit) && L.cur < kDone; }
+
+// ref: child reference word of pt_device.cuh (or kDone). Straight-line code: the leaf range is decoded unconditionally
+// (harmless for inner references), only the rare "big leaf" count is a predicated load.
 __device__ __forceinline__ void lane_enter(TraceLane &L, const SceneDev &sc, uint32_t ref)
 {
-    // ref: child reference word of pt_device.cuh
-    if (ref & kLeafBit)
-    {
-        const uint32_t start = (ref & 0x7fffffffu) >> 4;
-        uint32_t cnt = ref & 15u;
-        if (cnt == 0) cnt = __ldg(&sc.bigLeafCount[start]);
-        L.ti = start;
-        L.te = start + cnt;
-    }
+    const uint32_t start = (ref & 0x7fffffffu) >> 4;
+    uint32_t cnt = ref & 15u;
+    if ((ref & kLeafBit) && cnt == 0 && ref < kDone) cnt = __ldg(&sc.bigLeafCount[start]);
+    L.ti = start;
+    L.te = start + cnt;
     L.cur = ref;
-}
-
-__device__ __forceinline__ void lane_pop(TraceLane &L, const SceneDev &sc, const uint32_t *stk, const int stride)
-{
-    if (L.sp == 0) L.cur = kDone;
-    else lane_enter(L, sc, stk[(--L.sp) * stride]);
 }
 
 __device__ __forceinline__ void lane_start(TraceLane &L, const SceneDev &sc, const Ray &r, float best)
@@ -192,13 +188,8 @@ __device__ __forceinline__ void lane_start(TraceLane &L, const SceneDev &sc, con
     L.nb = L.nt = 0;
     L.found = false;
     L.regular = ray_is_regular(r);
-    L.ti = L.te = 0;
-    if (sc.rootRef == kInvalidRef) L.cur = kDone;
-    else lane_enter(L, sc, sc.rootRef);
+    lane_enter(L, sc, sc.rootRef == kInvalidRef ? kDone : sc.rootRef);
 }
-
-__device__ __forceinline__ bool lane_at_inner(const TraceLane &L) { return !(L.cur & kLeafBit); }  // kDone has the leaf bit
-__device__ __forceinline__ bool lane_at_leaf(const TraceLane &L) { return (L.cur & kLeafBit) && L.cur != kDone; }
 
 template <bool FAST>
 __device__ __forceinline__ void node_step(TraceLane &L, const SceneDev &sc, uint32_t *stk, const int stride)
@@ -226,32 +217,40 @@ __device__ __forceinline__ void node_step(TraceLane &L, const SceneDev &sc, uint
     const bool leftFirst = da > 0;
     const uint32_t first = leftFirst ? d.x : d.y, second = leftFirst ? d.y : d.x;
     const bool b1 = leftFirst ? bL : bR, b2 = leftFirst ? bR : bL;
-    if (b1)
+    // branch-free successor: near child if hit, else far child if hit, else the top of the stack (or done)
+    uint32_t next;
+    if (b1 && b2) stk[(L.sp++) * stride] = second;
+    if (!b1 && !b2)
     {
-        if (b2) stk[(L.sp++) * stride] = second;
-        lane_enter(L, sc, first);
+        next = kDone;
+        if (L.sp > 0) next = stk[(--L.sp) * stride];
     }
-    else if (b2)
-        lane_enter(L, sc, second);
     else
-        lane_pop(L, sc, stk, stride);
+        next = b1 ? first : second;
+    lane_enter(L, sc, next);
 }
 
 template <bool ANY>
 __device__ __forceinline__ void tri_step(TraceLane &L, const SceneDev &sc, const uint32_t *stk, const int stride)
 {
     L.nt++;
+    bool done = false;
     if (tri_test(sc.tris, L.ti, L.r, L.best, L.hs, L.ht, L.htp, L.hmat))
     {
         if (ANY)
         {
             L.found = true;
-            L.cur = kDone;
-            return;
+            done = true;
         }
         L.hitTri = (int)L.ti;
     }
-    if (++L.ti == L.te) lane_pop(L, sc, stk, stride);
+    if (done) L.cur = kDone;
+    else if (++L.ti == L.te)
+    {
+        uint32_t next = kDone;
+        if (L.sp > 0) next = stk[(--L.sp) * stride];
+        lane_enter(L, sc, next);
+    }
 }
 
 }  // namespace ptc
