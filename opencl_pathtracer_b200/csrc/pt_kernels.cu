@@ -210,21 +210,23 @@ __global__ void __launch_bounds__(kTraverseThreads) k_trace(SceneDev sc, PathSta
             if (exhausted) break;
             continue;  // (only reachable with refillMin > 32)
         }
-        // ---- node phase: node steps while at least as many lanes wait for a node as for a triangle
+        // ---- node phase: node steps while at least half of the lanes that hold a ray wait for a node
+        const int nHave = 32 - __popc(__ballot_sync(full, L.cur >= kDone));
         while (true)
         {
             const bool wantNode = lane_at_inner(L);
-            const int nN = __popc(__ballot_sync(full, wantNode)), nT = __popc(__ballot_sync(full, lane_at_leaf(L)));
-            if (nN == 0 || nN < nT) break;
+            const int nN = __popc(__ballot_sync(full, wantNode));
+            if (nN == 0 || 2 * nN < nHave) break;
             if (wantNode) node_step<FAST>(L, sc, stk, kTraverseThreads);
         }
-        // ---- triangle phase
+        // ---- triangle phase: at least one step if any lane waits for a triangle, then while they are the majority
         while (true)
         {
             const bool wantTri = lane_at_leaf(L);
-            const int nT = __popc(__ballot_sync(full, wantTri)), nN = __popc(__ballot_sync(full, lane_at_inner(L)));
-            if (nT == 0 || nT <= nN) break;
+            const int nT = __popc(__ballot_sync(full, wantTri));
+            if (nT == 0) break;
             if (wantTri) tri_step<ANY>(L, sc, stk, kTraverseThreads);
+            if (2 * nT <= nHave) break;
         }
     }
     flush_work(cn, ANY ? &cn->shadowRays : &cn->extensionRays, nRays, nbSum, ntSum);

@@ -31,6 +31,15 @@ __device__ __forceinline__ float4 cross3(float4 a, float4 b)
 {
     return f4(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x, 0.f);
 }
+// 256-bit read-only global load (sm_100a: LDG.E.256): one L1 request per lane for half a 64-byte record instead of two.
+// p must be 32-byte aligned.
+__device__ __forceinline__ void ldg256(const void *p, float4 &a, float4 &b)
+{
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+                 : "l"(p));
+}
+
 // OpenCL max(x, y) = (x < y) ? y : x  — NOT fmaxf (differs on NaN)
 __device__ __forceinline__ float clmax(float x, float y) { return x < y ? y : x; }
 

@@ -109,10 +109,9 @@ __device__ __forceinline__ bool box_test(float nx, float ny, float nz, float xx,
 __device__ __forceinline__ bool tri_test(const DevTri *__restrict__ tris, uint32_t i, const Ray &r, float &best, float &hs,
                                          float &ht, float &htp, uint32_t &hmat)
 {
-    const float4 n = __ldg(&tris[i].n);
-    const float4 p = __ldg(&tris[i].p);
-    const float4 e1 = __ldg(&tris[i].e1);
-    const float4 e2 = __ldg(&tris[i].e2);
+    float4 n, p, e1, e2;
+    ldg256(&tris[i].n, n, p);
+    ldg256(&tris[i].e1, e1, e2);
     const float nd = ((n.x * r.dx + n.y * r.dy) + n.z * r.dz) + n.w * r.dw;
     if ((nd > -0.00001f) && (nd < 0.00001f)) return false;
     const float no = ((n.x * r.ox + n.y * r.oy) + n.z * r.oz) + n.w * r.ow;
@@ -143,8 +142,10 @@ __device__ __forceinline__ bool tri_test(const DevTri *__restrict__ tris, uint32
 // of direction[cutAxis] (:660-669), both boxes tested, near descended, far pushed; leaves scanned in array order, one
 // triangle per tri_step; a candidate at equal distance replaces the previous one (:543 is a strict test).
 // The warp decides whether its lanes take node steps or triangle steps (see k_trace), so the state machine is
-// explicit: cur is an inner-node index, a leaf reference while the leaf is being scanned (ti < te), kDone (ray
-// finished, result not yet written) or kIdle (no ray).
+// explicit. `cur` is: an inner-node index; or a leaf reference that doubles as the scan cursor (bits 30..4 = next
+// triangle, bits 3..0 = triangles left; after a test cur += 15, i.e. next + 1 and left - 1); or a "big leaf"
+// reference (count field 0, more than 15 triangles, scanned through ti/te); or kDone (ray finished, result not yet
+// written); or kIdle (no ray).
 constexpr uint32_t kDone = 0xfffffffeu, kIdle = 0xffffffffu;
 
 struct TraceLane
@@ -152,29 +153,36 @@ struct TraceLane
     Ray r;
     float best;
     uint32_t cur;
-    uint32_t ti, te;  // triangle cursor / end of the leaf being scanned
+    uint32_t ti, te;   // big leaves only
+    uint32_t dirPos;   // bit a set <=> direction[a] > 0 (child order, :660)
     int sp;
     int hitTri;
     float hs, ht, htp;
-    uint32_t hmat;    // MaterialType of the hit side
+    uint32_t hmat;     // MaterialType of the hit side
     uint32_t nb, nt;
     bool regular;
-    bool found;       // ANY: an occluder was accepted
+    bool found;        // ANY: an occluder was accepted
 };
 
 __device__ __forceinline__ bool lane_at_inner(const TraceLane &L) { return !(L.cur & kLeafBit); }
 __device__ __forceinline__ bool lane_at_leaf(const TraceLane &L) { return (L.cur & kLeafBit) && L.cur < kDone; }
 
-// ref: child reference word of pt_device.cuh (or kDone). Straight-line code: the leaf range is decoded unconditionally
-// (harmless for inner references), only the rare "big leaf" count is a predicated load.
+// ref: child reference word of pt_device.cuh (or kDone). Only big leaves need any decoding.
 __device__ __forceinline__ void lane_enter(TraceLane &L, const SceneDev &sc, uint32_t ref)
 {
-    const uint32_t start = (ref & 0x7fffffffu) >> 4;
-    uint32_t cnt = ref & 15u;
-    if ((ref & kLeafBit) && cnt == 0 && ref < kDone) cnt = __ldg(&sc.bigLeafCount[start]);
-    L.ti = start;
-    L.te = start + cnt;
     L.cur = ref;
+    if ((ref & (kLeafBit | 15u)) == kLeafBit)  // leaf with count field 0 (kDone / kIdle have the low bits set)
+    {
+        L.ti = (ref >> 4) & 0x7ffffffu;
+        L.te = L.ti + __ldg(&sc.bigLeafCount[L.ti]);
+    }
+}
+
+__device__ __forceinline__ void lane_pop(TraceLane &L, const SceneDev &sc, const uint32_t *stk, const int stride)
+{
+    uint32_t next = kDone;
+    if (L.sp > 0) next = stk[(--L.sp) * stride];
+    lane_enter(L, sc, next);
 }
 
 __device__ __forceinline__ void lane_start(TraceLane &L, const SceneDev &sc, const Ray &r, float best)
@@ -188,6 +196,7 @@ __device__ __forceinline__ void lane_start(TraceLane &L, const SceneDev &sc, con
     L.nb = L.nt = 0;
     L.found = false;
     L.regular = ray_is_regular(r);
+    L.dirPos = (r.dx > 0 ? 1u : 0u) | (r.dy > 0 ? 2u : 0u) | (r.dz > 0 ? 4u : 0u);
     lane_enter(L, sc, sc.rootRef == kInvalidRef ? kDone : sc.rootRef);
 }
 
@@ -195,62 +204,62 @@ template <bool FAST>
 __device__ __forceinline__ void node_step(TraceLane &L, const SceneDev &sc, uint32_t *stk, const int stride)
 {
     const DevNode *nd = &sc.nodes[L.cur];
-    const float4 a = __ldg(&nd->a), b = __ldg(&nd->b), c = __ldg(&nd->c);
-    const uint4 d = __ldg(&nd->d);
+    float4 a, b, c, dd;
+    ldg256(&nd->a, a, b);
+    ldg256(&nd->c, c, dd);
+    const uint4 d = make_uint4(__float_as_uint(dd.x), __float_as_uint(dd.y), __float_as_uint(dd.z), 0u);
     L.nb += 2;
-    bool bL, bR;
+    bool hitL, hitR;
     if (L.regular)
     {
-        bL = box_test<FAST>(a.x, a.y, a.z, a.w, b.x, b.y, L.r, L.best);
-        bR = box_test<FAST>(b.z, b.w, c.x, c.y, c.z, c.w, L.r, L.best);
+        hitL = box_test<FAST>(a.x, a.y, a.z, a.w, b.x, b.y, L.r, L.best);
+        hitR = box_test<FAST>(b.z, b.w, c.x, c.y, c.z, c.w, L.r, L.best);
     }
     else
     {
         const Ray &r = L.r;
-        bL = box_test_ref<FAST>(a.x, a.y, a.z, a.w, b.x, b.y, r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, r.ix, r.iy, r.iz, L.best);
-        bR = box_test_ref<FAST>(b.z, b.w, c.x, c.y, c.z, c.w, r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, r.ix, r.iy, r.iz, L.best);
+        hitL = box_test_ref<FAST>(a.x, a.y, a.z, a.w, b.x, b.y, r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, r.ix, r.iy, r.iz, L.best);
+        hitR = box_test_ref<FAST>(b.z, b.w, c.x, c.y, c.z, c.w, r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, r.ix, r.iy, r.iz, L.best);
     }
-    bL = bL && !(d.z & 4u);
-    bR = bR && !(d.z & 8u);
-    const uint32_t axis = d.z & 3u;
-    const float da = axis == 0 ? L.r.dx : (axis == 1 ? L.r.dy : L.r.dz);
-    const bool leftFirst = da > 0;
-    const uint32_t first = leftFirst ? d.x : d.y, second = leftFirst ? d.y : d.x;
-    const bool b1 = leftFirst ? bL : bR, b2 = leftFirst ? bR : bL;
-    // branch-free successor: near child if hit, else far child if hit, else the top of the stack (or done)
-    uint32_t next;
-    if (b1 && b2) stk[(L.sp++) * stride] = second;
-    if (!b1 && !b2)
+    hitL = hitL && !(d.z & 4u);  // an empty child box never intersects (:68)
+    hitR = hitR && !(d.z & 8u);
+    // near child first (:660-669): left is near when direction[cutAxis] > 0
+    const bool leftFirst = (L.dirPos >> (d.z & 3u)) & 1u;
+    if (hitL && hitR)
     {
-        next = kDone;
-        if (L.sp > 0) next = stk[(--L.sp) * stride];
+        stk[(L.sp++) * stride] = leftFirst ? d.y : d.x;
+        lane_enter(L, sc, leftFirst ? d.x : d.y);
     }
+    else if (hitL || hitR)
+        lane_enter(L, sc, hitL ? d.x : d.y);
     else
-        next = b1 ? first : second;
-    lane_enter(L, sc, next);
+        lane_pop(L, sc, stk, stride);
 }
 
 template <bool ANY>
 __device__ __forceinline__ void tri_step(TraceLane &L, const SceneDev &sc, const uint32_t *stk, const int stride)
 {
+    const bool big = (L.cur & 15u) == 0u;
+    const uint32_t i = big ? L.ti : ((L.cur >> 4) & 0x7ffffffu);
     L.nt++;
-    bool done = false;
-    if (tri_test(sc.tris, L.ti, L.r, L.best, L.hs, L.ht, L.htp, L.hmat))
+    if (tri_test(sc.tris, i, L.r, L.best, L.hs, L.ht, L.htp, L.hmat))
     {
+        L.hitTri = (int)i;
         if (ANY)
         {
             L.found = true;
-            done = true;
+            L.cur = kDone;
+            return;
         }
-        L.hitTri = (int)L.ti;
     }
-    if (done) L.cur = kDone;
-    else if (++L.ti == L.te)
+    bool last;
+    if (big) last = (++L.ti == L.te);
+    else
     {
-        uint32_t next = kDone;
-        if (L.sp > 0) next = stk[(--L.sp) * stride];
-        lane_enter(L, sc, next);
+        last = (L.cur & 15u) == 1u;
+        L.cur += 15u;
     }
+    if (last) lane_pop(L, sc, stk, stride);
 }
 
 }  // namespace ptc
