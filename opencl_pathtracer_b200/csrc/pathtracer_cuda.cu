@@ -273,7 +273,8 @@ int ptc_create(const ptc_config *config, ptc_ctx **out_ctx)
     while ((uint64_t)b * c->nPix > (1ull << 30) && b > 1) b--;
     c->batchIters = b;
     c->capacity = (size_t)b * c->nPix;
-    c->lc.traverseGrid = c->smCount * traverse_ctas_per_sm(c->fast);
+    c->lc.stackDepth = 32;
+    c->lc.traverseGrid = c->smCount * traverse_ctas_per_sm(c->fast, c->lc.stackDepth);
     c->lc.streamGrid = c->smCount * 8;
     c->lc.refillMin = 16;  // measured on B200: 4 -> 85.8, 8 -> 91.0, 16 -> 95.3, 24 -> 92.7 Msamples/s (profiles/r01_sweeps.txt)
     if (const char *e = std::getenv("PTC_REFILL_MIN")) c->lc.refillMin = (uint32_t)std::max(1, std::min(32, std::atoi(e)));
@@ -496,6 +497,12 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
     sc.bigLeafCount = bigLeaf.empty() ? nullptr : ctx->bigLeaf.p;
     sc.rootRef = rootRef; sc.nLights = nL; sc.nTriangles = nT; sc.sky = sky;
     ctx->cam = Camera{to4(s->camera_position), to4(s->camera_direction), to4(s->camera_right), to4(s->camera_up)};
+    // traversal stack: one entry per level below the root is enough (a push happens only when descending)
+    if (!std::getenv("PTC_FULL_STACK"))
+    {
+        ctx->lc.stackDepth = (int)std::min<uint32_t>(32u, std::max<uint32_t>(4u, maxDepth + 1));
+        if (!std::getenv("PTC_CTAS_PER_SM")) ctx->lc.traverseGrid = ctx->smCount * traverse_ctas_per_sm(ctx->fast, ctx->lc.stackDepth);
+    }
     ctx->sceneLoaded = true;
     return PTC_OK;
 }

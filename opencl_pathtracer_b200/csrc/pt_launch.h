@@ -10,9 +10,10 @@ struct LaunchCfg
     int traverseGrid;  // persistent extend / connect CTAs (multiple of the SM count)
     int streamGrid;    // grid of the streaming stages (generate / shade / accumulate)
     uint32_t refillMin;  // idle lanes of a warp that trigger a refill from the work cursor (1..32)
+    int stackDepth;      // traversal stack entries per thread (BVH depth + 1, at most kStackDepth)
 };
 
-int traverse_ctas_per_sm(bool fast);
+int traverse_ctas_per_sm(bool fast, int stackDepth);
 
 void launch_reset(cudaStream_t s, Counters *cn, uint32_t nPaths);
 void launch_generate(cudaStream_t s, const LaunchCfg &lc, const FrameParams &fp, const Camera &cam, const PathState &st);
