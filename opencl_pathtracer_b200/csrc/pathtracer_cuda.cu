@@ -238,7 +238,7 @@ int ptc_create(const ptc_config *config, ptc_ctx **out_ctx)
     if (config->struct_size != sizeof(ptc_config)) return fail(nullptr, PTC_ERR_INVALID, "ptc_create: struct_size %u != %zu", config->struct_size, sizeof(ptc_config));
     if (config->image_width == 0 || config->image_height == 0)
         return fail(nullptr, PTC_ERR_INVALID, "Image dimensions must be positive");  // reference PathTracer.cpp:147-153
-    if ((uint64_t)config->image_width * config->image_height > (1ull << 28)) return fail(nullptr, PTC_ERR_INVALID, "image too large");
+    if ((uint64_t)config->image_width * config->image_height >= (1ull << 27)) return fail(nullptr, PTC_ERR_INVALID, "image too large (one wavefront pass holds fewer than 2^27 paths)");
     if (config->ray_max_depth > (uint32_t)kMaxBounces) return fail(nullptr, PTC_ERR_LIMIT, "ray_max_depth %u exceeds %d", config->ray_max_depth, kMaxBounces);
     if (config->sampler > 2u || config->mode > 1u) return fail(nullptr, PTC_ERR_INVALID, "unknown sampler or mode");
     int nDev = 0;
@@ -270,13 +270,13 @@ int ptc_create(const ptc_config *config, ptc_ctx **out_ctx)
     uint32_t b = config->iterations_per_batch;
     if (b == 0) b = ((1u << 21) + c->nPix - 1) / c->nPix;
     if (b > 64) b = 64;
-    while ((uint64_t)b * c->nPix > (1ull << 30) && b > 1) b--;
+    while ((uint64_t)b * c->nPix >= (1ull << 27) && b > 1) b--;  // staged items carry the path slot in 27 bits
     c->batchIters = b;
     c->capacity = (size_t)b * c->nPix;
     c->lc.stackDepth = 32;
     c->lc.traverseGrid = c->smCount * traverse_ctas_per_sm(c->fast, c->lc.stackDepth);
     c->lc.streamGrid = c->smCount * 8;
-    c->lc.refillMin = 16;  // measured on B200: 4 -> 85.8, 8 -> 91.0, 16 -> 95.3, 24 -> 92.7 Msamples/s (profiles/r01_sweeps.txt)
+    c->lc.refillMin = 4;  // idle lanes that trigger a refill from the warp's staged rays (profiles/r01_sweeps.txt)
     if (const char *e = std::getenv("PTC_REFILL_MIN")) c->lc.refillMin = (uint32_t)std::max(1, std::min(32, std::atoi(e)));
     if (const char *e = std::getenv("PTC_CTAS_PER_SM")) c->lc.traverseGrid = c->smCount * std::max(1, std::atoi(e));
 

@@ -82,17 +82,8 @@ __global__ void __launch_bounds__(kStreamThreads) k_generate(FrameParams fp, Cam
 }
 
 // ------------------------------------------------------------------------------------------------ traversal
-// Persistent kernels: each warp pulls chunks of 32 queue entries from a global cursor until the queue of
-// this bounce is exhausted; per-thread traversal stacks live in shared memory, laid out [level][thread].
-__device__ __forceinline__ bool fetch_chunk(uint32_t *cursor, uint32_t count, uint32_t &base)
-{
-    const unsigned lane = threadIdx.x & 31u;
-    uint32_t b = 0;
-    if (lane == 0) b = atomicAdd(cursor, 32u);
-    base = __shfl_sync(0xffffffffu, b, 0);
-    return base < count;
-}
-
+// Persistent kernels: warps draw work from a global cursor until the queue of this bounce is exhausted; per-thread
+// traversal stacks live in shared memory, laid out [level][thread].
 __device__ __forceinline__ void flush_work(Counters *cn, unsigned long long *rayCounter, uint32_t nRays, uint32_t nb, uint32_t nt)
 {
     for (int o = 16; o; o >>= 1)
@@ -118,21 +109,36 @@ __device__ __forceinline__ void flush_work(Counters *cn, unsigned long long *ray
 // (any hit, one item per (queued path, light) pair).
 //
 // Warp-level scheduling (what keeps the SIMT lanes busy; none of it changes what a single ray does):
-//   * lane refill — a lane whose ray is finished takes the next item from the global cursor as soon as at least
-//     `refillMin` lanes of the warp are idle (one warp-aggregated atomicAdd), instead of waiting for the slowest ray of
-//     a fixed 32-ray chunk;
-//   * majority vote — each iteration the warp executes EITHER one inner-node step OR one triangle test, whichever more
-//     of its lanes are waiting for, so the two code paths are never serialised against each other.
-// The unlit / miss flags in st.occl (bits 31, 30) are written by extend and let connect skip items without loading the ray.
+//   * ray staging — when a warp's staging buffer is empty, its 32 lanes together draw 32 items from the global cursor
+//     (one atomicAdd), load / construct the rays with all lanes active (the long-latency state loads, the shadow-ray
+//     setup and the reciprocal direction happen here, once per 32 rays) and ballot-compact the ones that need a
+//     traversal into a per-warp buffer in shared memory;
+//   * lane refill — a lane whose ray finished takes the next staged ray at once (a few LDS), as soon as `popMin`
+//     lanes are idle, instead of waiting for the slowest ray of a fixed 32-ray chunk;
+//   * majority vote — the warp executes node steps while at least half of its rays wait for a node, then triangle
+//     tests while those are the majority, so the two code paths are never serialised against each other.
+// The unlit / miss flags in st.occl (bits 31, 30) are written by extend and let connect drop items at staging time.
 constexpr uint32_t kOcclUnlit = 0x80000000u, kOcclMiss = 0x40000000u, kOcclMask = 0x3fffffffu;
+constexpr uint32_t kLightShift = 27;  // staged item word: path slot | light << 27 (ptc_create keeps slots below 2^27)
+
+struct StagedRays  // one per warp
+{
+    float4 org[32];
+    float4 dir[32];
+    float4 invBest[32];  // reciprocal direction (header.cl:280-282) and the initial distance bound
+    uint32_t item[32];
+};
+constexpr size_t kStageBytes = sizeof(StagedRays) * (kTraverseThreads / 32);
 
 template <bool ANY, bool FAST>
 __global__ void __launch_bounds__(kTraverseThreads) k_trace(SceneDev sc, PathState st, const uint32_t *__restrict__ queue,
-                                                           Counters *__restrict__ cn, int bounce, uint32_t refillMin)
+                                                           Counters *__restrict__ cn, int bounce, uint32_t popMin, int stackDepth)
 {
-    extern __shared__ uint32_t smemStack[];
+    extern __shared__ __align__(16) uint32_t smemStack[];
     uint32_t *stk = smemStack + threadIdx.x;
+    StagedRays &stage = reinterpret_cast<StagedRays *>(smemStack + stackDepth * kTraverseThreads)[threadIdx.x >> 5];
     const unsigned lane = threadIdx.x & 31u;
+    const unsigned lt = (1u << lane) - 1u;
     const unsigned full = 0xffffffffu;
     const uint32_t count = cn->qcount[bounce];
     const uint32_t nL = ANY ? sc.nLights : 1u;
@@ -144,18 +150,19 @@ __global__ void __launch_bounds__(kTraverseThreads) k_trace(SceneDev sc, PathSta
     L.found = false;
     L.hitTri = -1;
     bool exhausted = false;
+    uint32_t qHead = 0, qCount = 0;  // staged rays [qHead, qCount) are waiting (warp-uniform)
     uint32_t p = 0, li = 0;
     uint32_t nbSum = 0, ntSum = 0, nRays = 0;
     while (true)
     {
-        // ---- completion: write the result of a finished ray
+        // ---- completion: write the result of a finished ray (the counters are fire-and-forget reductions)
         if (L.cur == kDone)
         {
             if (!ANY)
             {
                 st.hit[p] = f4(__int_as_float(L.hitTri), L.hs, L.ht, L.htp);
-                st.nbbx[p] += L.nb;
-                st.ntri[p] += L.nt;
+                atomicAdd(&st.nbbx[p], L.nb);
+                atomicAdd(&st.ntri[p], L.nt);
                 uint32_t flags = 0;
                 if (L.hitTri < 0) flags = kOcclMiss;
                 else if (FAST && !(L.hmat == 0u || L.hmat == 3u)) flags = kOcclUnlit;  // GLASS / WATER / METAL / UNKNOWN never read the direct light (:805-843)
@@ -170,46 +177,84 @@ __global__ void __launch_bounds__(kTraverseThreads) k_trace(SceneDev sc, PathSta
             nbSum += L.nb; ntSum += L.nt; nRays++;
             L.cur = kIdle;
         }
-        // ---- refill idle lanes from the work cursor
-        const unsigned idle = __ballot_sync(full, L.cur == kIdle);
-        if (!exhausted && (uint32_t)__popc(idle) >= refillMin)
+        unsigned idle = __ballot_sync(full, L.cur == kIdle);
+        if (idle)
         {
-            const uint32_t n = (uint32_t)__popc(idle);
-            uint32_t base = 0;
-            if (lane == 0) base = atomicAdd(cursor, n);
-            base = __shfl_sync(full, base, 0);
-            if (base >= total || total - base <= n) exhausted = true;
-            const uint32_t k = base + (uint32_t)__popc(idle & ((1u << lane) - 1u));
-            if (L.cur == kIdle && base < total && k < total)
+            // ---- staging: the whole warp prepares the next 32 items
+            while (qHead == qCount && !exhausted)
             {
-                if (!ANY)
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd(cursor, 32u);
+                base = __shfl_sync(full, base, 0);
+                if (base >= total || total - base <= 32u) exhausted = true;
+                const uint32_t k = base + lane;
+                bool valid = base < total && k < total;
+                float4 o = f4(0, 0, 0, 0), d = o;
+                float bound = INFINITY;
+                uint32_t item = 0;
+                if (valid)
                 {
-                    p = queue ? queue[k] : k;
-                    lane_start(L, sc, make_ray(st.org[p], st.dir[p]), INFINITY);
-                }
-                else
-                {
-                    // path-major: the shadow rays of one path are adjacent items (measured: light-major order is 10 % slower)
-                    const uint32_t kp = k / nL;
-                    li = k - kp * nL;
-                    p = queue ? queue[kp] : kp;
-                    if (!(st.occl[p] & (kOcclUnlit | kOcclMiss)))
+                    if (!ANY)
                     {
-                        const float4 h = st.hit[p], o = st.org[p], d = st.dir[p];
-                        const float4 q = f4(o.x + d.x * h.w, o.y + d.y * h.w, o.z + d.z * h.w, o.w + d.w * h.w);  // :538
-                        float4 ldir;
-                        float bound;
-                        shadow_setup(sc.lights[li], q, ldir, bound);
-                        lane_start(L, sc, make_ray(q, ldir), bound);
+                        item = queue ? queue[k] : k;
+                        o = st.org[item];
+                        d = st.dir[item];
+                    }
+                    else
+                    {
+                        // path-major: the shadow rays of one path are adjacent items (measured: light-major order is 10 % slower)
+                        const uint32_t kp = k / nL, l = k - kp * nL;
+                        const uint32_t pp = queue ? queue[kp] : kp;
+                        item = pp | (l << kLightShift);
+                        valid = !(st.occl[pp] & (kOcclUnlit | kOcclMiss));
+                        if (valid)
+                        {
+                            const float4 h = st.hit[pp], po = st.org[pp], pd = st.dir[pp];
+                            const float4 q = f4(po.x + pd.x * h.w, po.y + pd.y * h.w, po.z + pd.z * h.w, po.w + pd.w * h.w);  // :538
+                            shadow_setup(sc.lights[l], q, d, bound);
+                            o = q;
+                        }
                     }
                 }
+                const unsigned m = __ballot_sync(full, valid);
+                if (valid)
+                {
+                    const uint32_t slot = (uint32_t)__popc(m & lt);
+                    stage.org[slot] = o;
+                    stage.dir[slot] = d;
+                    stage.invBest[slot] = f4(1.0f / d.x, 1.0f / d.y, 1.0f / d.z, bound);  // header.cl:280-282
+                    stage.item[slot] = item;
+                }
+                qHead = 0;
+                qCount = (uint32_t)__popc(m);
+                __syncwarp();
             }
-            continue;  // lanes that drew an item needing no trace stay idle: look again
-        }
-        if (idle == full)
-        {
-            if (exhausted) break;
-            continue;  // (only reachable with refillMin > 32)
+            // ---- refill: idle lanes take staged rays
+            const uint32_t nIdle = (uint32_t)__popc(idle);
+            if (qHead < qCount && (nIdle >= popMin || exhausted))
+            {
+                const uint32_t e = qHead + (uint32_t)__popc(idle & lt);
+                if (L.cur == kIdle && e < qCount)
+                {
+                    const float4 o = stage.org[e], d = stage.dir[e], ib = stage.invBest[e];
+                    const uint32_t item = stage.item[e];
+                    p = ANY ? (item & ((1u << kLightShift) - 1u)) : item;
+                    li = ANY ? (item >> kLightShift) : 0u;
+                    Ray r;
+                    r.ox = o.x; r.oy = o.y; r.oz = o.z; r.ow = o.w;
+                    r.dx = d.x; r.dy = d.y; r.dz = d.z; r.dw = d.w;
+                    r.ix = ib.x; r.iy = ib.y; r.iz = ib.z;
+                    lane_start(L, sc, r, ib.w);
+                }
+                qHead = min(qHead + nIdle, qCount);
+                __syncwarp();
+                idle = __ballot_sync(full, L.cur == kIdle);
+            }
+            if (idle == full)
+            {
+                if (exhausted && qHead == qCount) break;
+                continue;
+            }
         }
         // ---- node phase: node steps while at least half of the lanes that hold a ray wait for a node
         const int nHave = 32 - __popc(__ballot_sync(full, L.cur >= kDone));
@@ -508,8 +553,7 @@ __global__ void k_add_image(ImageDev img, uint32_t nPixels, const float4 *color,
 }
 
 // ------------------------------------------------------------------------------------------------ launchers
-static const size_t kStackBytes = (size_t)kStackDepth * kTraverseThreads * sizeof(uint32_t);
-static inline size_t stack_bytes(const LaunchCfg &lc) { return (size_t)lc.stackDepth * kTraverseThreads * sizeof(uint32_t); }
+static inline size_t stack_bytes(const LaunchCfg &lc) { return (size_t)lc.stackDepth * kTraverseThreads * sizeof(uint32_t) + kStageBytes; }
 
 template <bool ANY, bool FAST>
 static int occupancy_of(size_t kStackBytes)
@@ -521,7 +565,7 @@ static int occupancy_of(size_t kStackBytes)
 
 int traverse_ctas_per_sm(bool fast, int stackDepth)
 {
-    const size_t kStackBytes = (size_t)stackDepth * kTraverseThreads * sizeof(uint32_t);
+    const size_t kStackBytes = (size_t)stackDepth * kTraverseThreads * sizeof(uint32_t) + kStageBytes;
     int n = fast ? occupancy_of<false, true>(kStackBytes) : occupancy_of<false, false>(kStackBytes);
     int m = fast ? occupancy_of<true, true>(kStackBytes) : occupancy_of<true, false>(kStackBytes);
     n = n < m ? n : m;
@@ -538,15 +582,15 @@ void launch_generate(cudaStream_t s, const LaunchCfg &lc, const FrameParams &fp,
 void launch_extend(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const PathState &st, const uint32_t *queue,
                    Counters *cn, int bounce)
 {
-    if (fast) k_trace<false, true><<<lc.traverseGrid, kTraverseThreads, stack_bytes(lc), s>>>(sc, st, queue, cn, bounce, lc.refillMin);
-    else k_trace<false, false><<<lc.traverseGrid, kTraverseThreads, stack_bytes(lc), s>>>(sc, st, queue, cn, bounce, lc.refillMin);
+    if (fast) k_trace<false, true><<<lc.traverseGrid, kTraverseThreads, stack_bytes(lc), s>>>(sc, st, queue, cn, bounce, lc.refillMin, lc.stackDepth);
+    else k_trace<false, false><<<lc.traverseGrid, kTraverseThreads, stack_bytes(lc), s>>>(sc, st, queue, cn, bounce, lc.refillMin, lc.stackDepth);
 }
 
 void launch_connect(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const PathState &st, const uint32_t *queue,
                     Counters *cn, int bounce)
 {
-    if (fast) k_trace<true, true><<<lc.traverseGrid, kTraverseThreads, stack_bytes(lc), s>>>(sc, st, queue, cn, bounce, lc.refillMin);
-    else k_trace<true, false><<<lc.traverseGrid, kTraverseThreads, stack_bytes(lc), s>>>(sc, st, queue, cn, bounce, lc.refillMin);
+    if (fast) k_trace<true, true><<<lc.traverseGrid, kTraverseThreads, stack_bytes(lc), s>>>(sc, st, queue, cn, bounce, lc.refillMin, lc.stackDepth);
+    else k_trace<true, false><<<lc.traverseGrid, kTraverseThreads, stack_bytes(lc), s>>>(sc, st, queue, cn, bounce, lc.refillMin, lc.stackDepth);
 }
 
 void launch_shade(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const FrameParams &fp, const PathState &st,

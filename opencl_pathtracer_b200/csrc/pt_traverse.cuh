@@ -144,8 +144,8 @@ __device__ __forceinline__ bool tri_test(const DevTri *__restrict__ tris, uint32
 // The warp decides whether its lanes take node steps or triangle steps (see k_trace), so the state machine is
 // explicit. `cur` is: an inner-node index; or a leaf reference that doubles as the scan cursor (bits 30..4 = next
 // triangle, bits 3..0 = triangles left; after a test cur += 15, i.e. next + 1 and left - 1); or a "big leaf"
-// reference (count field 0, more than 15 triangles, scanned through ti/te); or kDone (ray finished, result not yet
-// written); or kIdle (no ray).
+// reference (count field 0, more than 15 triangles: cur += 16 per test, the end of the scan is looked up on the first
+// test and kept in `te`); or kDone (ray finished, result not yet written); or kIdle (no ray).
 constexpr uint32_t kDone = 0xfffffffeu, kIdle = 0xffffffffu;
 
 struct TraceLane
@@ -153,7 +153,7 @@ struct TraceLane
     Ray r;
     float best;
     uint32_t cur;
-    uint32_t ti, te;   // big leaves only
+    uint32_t te;       // big leaves only: one past the last triangle of the leaf being scanned, 0 = not looked up yet
     uint32_t dirPos;   // bit a set <=> direction[a] > 0 (child order, :660)
     int sp;
     int hitTri;
@@ -167,22 +167,14 @@ struct TraceLane
 __device__ __forceinline__ bool lane_at_inner(const TraceLane &L) { return !(L.cur & kLeafBit); }
 __device__ __forceinline__ bool lane_at_leaf(const TraceLane &L) { return (L.cur & kLeafBit) && L.cur < kDone; }
 
-// ref: child reference word of pt_device.cuh (or kDone). Only big leaves need any decoding.
-__device__ __forceinline__ void lane_enter(TraceLane &L, const SceneDev &sc, uint32_t ref)
+// Next subtree from the stack, or kDone when it is empty. Written so that it compiles to predicated code (one LDS).
+__device__ __forceinline__ uint32_t stack_pop(int &sp, const uint32_t *stk, const int stride, bool doPop)
 {
-    L.cur = ref;
-    if ((ref & (kLeafBit | 15u)) == kLeafBit)  // leaf with count field 0 (kDone / kIdle have the low bits set)
-    {
-        L.ti = (ref >> 4) & 0x7ffffffu;
-        L.te = L.ti + __ldg(&sc.bigLeafCount[L.ti]);
-    }
-}
-
-__device__ __forceinline__ void lane_pop(TraceLane &L, const SceneDev &sc, const uint32_t *stk, const int stride)
-{
+    const bool has = doPop && sp > 0;
     uint32_t next = kDone;
-    if (L.sp > 0) next = stk[(--L.sp) * stride];
-    lane_enter(L, sc, next);
+    if (has) next = stk[(sp - 1) * stride];
+    sp -= has ? 1 : 0;
+    return next;
 }
 
 __device__ __forceinline__ void lane_start(TraceLane &L, const SceneDev &sc, const Ray &r, float best)
@@ -194,12 +186,15 @@ __device__ __forceinline__ void lane_start(TraceLane &L, const SceneDev &sc, con
     L.hs = L.ht = L.htp = 0.f;
     L.hmat = 0;
     L.nb = L.nt = 0;
+    L.te = 0;
     L.found = false;
     L.regular = ray_is_regular(r);
     L.dirPos = (r.dx > 0 ? 1u : 0u) | (r.dy > 0 ? 2u : 0u) | (r.dz > 0 ? 4u : 0u);
-    lane_enter(L, sc, sc.rootRef == kInvalidRef ? kDone : sc.rootRef);
+    L.cur = sc.rootRef == kInvalidRef ? kDone : sc.rootRef;
 }
 
+// One inner-node visit: both child boxes tested (:660-672), then the successor chosen without divergent branches:
+// both hit -> near child, far child pushed; one hit -> that child; none -> pop.
 template <bool FAST>
 __device__ __forceinline__ void node_step(TraceLane &L, const SceneDev &sc, uint32_t *stk, const int stride)
 {
@@ -207,7 +202,7 @@ __device__ __forceinline__ void node_step(TraceLane &L, const SceneDev &sc, uint
     float4 a, b, c, dd;
     ldg256(&nd->a, a, b);
     ldg256(&nd->c, c, dd);
-    const uint4 d = make_uint4(__float_as_uint(dd.x), __float_as_uint(dd.y), __float_as_uint(dd.z), 0u);
+    const uint32_t refL = __float_as_uint(dd.x), refR = __float_as_uint(dd.y), meta = __float_as_uint(dd.z);
     L.nb += 2;
     bool hitL, hitR;
     if (L.regular)
@@ -221,45 +216,42 @@ __device__ __forceinline__ void node_step(TraceLane &L, const SceneDev &sc, uint
         hitL = box_test_ref<FAST>(a.x, a.y, a.z, a.w, b.x, b.y, r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, r.ix, r.iy, r.iz, L.best);
         hitR = box_test_ref<FAST>(b.z, b.w, c.x, c.y, c.z, c.w, r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, r.ix, r.iy, r.iz, L.best);
     }
-    hitL = hitL && !(d.z & 4u);  // an empty child box never intersects (:68)
-    hitR = hitR && !(d.z & 8u);
+    hitL = hitL && !(meta & 4u);  // an empty child box never intersects (:68)
+    hitR = hitR && !(meta & 8u);
     // near child first (:660-669): left is near when direction[cutAxis] > 0
-    const bool leftFirst = (L.dirPos >> (d.z & 3u)) & 1u;
-    if (hitL && hitR)
-    {
-        stk[(L.sp++) * stride] = leftFirst ? d.y : d.x;  // (prefetching the postponed child into L1 measured 2 % slower)
-        lane_enter(L, sc, leftFirst ? d.x : d.y);
-    }
-    else if (hitL || hitR)
-        lane_enter(L, sc, hitL ? d.x : d.y);
-    else
-        lane_pop(L, sc, stk, stride);
+    const bool leftFirst = (L.dirPos >> (meta & 3u)) & 1u;
+    const bool both = hitL && hitR;
+    const uint32_t nearRef = leftFirst ? refL : refR, farRef = leftFirst ? refR : refL;
+    const uint32_t descend = both ? nearRef : (hitL ? refL : refR);
+    if (both) stk[L.sp * stride] = farRef;  // (prefetching the postponed child into L1 measured 2 % slower)
+    L.sp += both ? 1 : 0;
+    const uint32_t popped = stack_pop(L.sp, stk, stride, !(hitL || hitR));
+    L.cur = (hitL || hitR) ? descend : popped;
 }
 
 template <bool ANY>
 __device__ __forceinline__ void tri_step(TraceLane &L, const SceneDev &sc, const uint32_t *stk, const int stride)
 {
+    const uint32_t i = (L.cur >> 4) & 0x7ffffffu;
     const bool big = (L.cur & 15u) == 0u;
-    const uint32_t i = big ? L.ti : ((L.cur >> 4) & 0x7ffffffu);
+    if (big && L.te == 0u) L.te = i + __ldg(&sc.bigLeafCount[i]);  // rare: leaves of more than 15 triangles
     L.nt++;
+    bool stop = false;
     if (tri_test(sc.tris, i, L.r, L.best, L.hs, L.ht, L.htp, L.hmat))
     {
         L.hitTri = (int)i;
         if (ANY)
         {
             L.found = true;
-            L.cur = kDone;
-            return;
+            stop = true;
         }
     }
-    bool last;
-    if (big) last = (++L.ti == L.te);
-    else
-    {
-        last = (L.cur & 15u) == 1u;
-        L.cur += 15u;
-    }
-    if (last) lane_pop(L, sc, stk, stride);
+    const bool last = big ? (i + 1u == L.te) : ((L.cur & 15u) == 1u);
+    L.cur += big ? 16u : 15u;
+    if (last) L.te = 0u;
+    const uint32_t popped = stack_pop(L.sp, stk, stride, last && !stop);
+    if (last) L.cur = popped;
+    if (stop) L.cur = kDone;
 }
 
 }  // namespace ptc
