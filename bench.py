@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """bench.py — headline benchmark of the path-tracing hot path (see DESIGN.md "Measurement").
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload atrium|cornell] [--mode fast|parity]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload atrium|cornell|terrain|terrain_1080p] [--mode fast|parity]
   python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...
 
 Workload (BASELINE.json configs[2], the one the metric's 1/2/4/8-GPU samples/s + traversal roofline is quoted on):
@@ -27,11 +27,18 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-W, H, DEPTH = 1920, 1080, 10
+DEPTH = 10
 WORKLOADS = {
-    "atrium": dict(scene="atrium", desc="C3: procedural atrium ~262k tris, diffuse+varnished+glass, 3 lights, 1920x1080, depth 10, jittered"),
-    "cornell": dict(scene="cornell", desc="C2: Cornell box 30 tris, diffuse + point light, 1920x1080, depth 10, jittered"),
-    "atrium_small": dict(scene="atrium:4", desc="atrium at 1/4 tessellation (~16k tris), 1920x1080 (smoke only)"),
+    "atrium": dict(scene="atrium", size=(1920, 1080), sky=False, spp=8,
+                   desc="C3: procedural atrium ~262k tris, diffuse+varnished+glass, 3 lights, 1920x1080, depth 10, jittered"),
+    "cornell": dict(scene="cornell", size=(1920, 1080), sky=False, spp=8,
+                    desc="C2: Cornell box 30 tris, diffuse + point light, 1920x1080, depth 10, jittered"),
+    "terrain": dict(scene="terrain", size=(3840, 2160), sky=True, spp=1,
+                    desc="C4: procedural terrain + 64x64 flattened rock instances ~10.1M tris, 16 textures 1024^2, sun + sky cube map, 3840x2160, depth 10, jittered"),
+    "terrain_1080p": dict(scene="terrain", size=(1920, 1080), sky=True, spp=4,
+                          desc="C4 scene (~10.1M tris, textures, sun + sky) at 1920x1080, depth 10, jittered"),
+    "atrium_small": dict(scene="atrium:4", size=(1920, 1080), sky=False, spp=8,
+                         desc="atrium at 1/4 tessellation (~16k tris), 1920x1080 (smoke only)"),
 }
 
 
@@ -88,8 +95,8 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
-def reference_rows(step, rows_per_step):
-    r0 = (300 + step * rows_per_step) % (H - rows_per_step)
+def reference_rows(step, rows_per_step, H):
+    r0 = (H // 4 + step * rows_per_step) % (H - rows_per_step)
     return r0, r0 + rows_per_step
 
 
@@ -100,12 +107,13 @@ def run_reference(args, rank):
     import opencl_pathtracer_b200 as pt
     from oracle import ptref
     wl = WORKLOADS[args.workload]
-    scene = pt.Scene(wl["scene"], W, H)
+    W, H = wl["size"]
+    scene = pt.Scene(wl["scene"], W, H, load_sky=wl["sky"])
     cores = ptref.max_threads()
     rows = args.ref_rows
     times = []
     for step in range(args.warmup + args.steps):
-        r0, r1 = reference_rows(step, rows)
+        r0, r1 = reference_rows(step, rows, H)
         t0 = time.perf_counter()
         ptref.render(scene, W, H, DEPTH, 0, 0, 1, rows=(r0, r1))
         dt = time.perf_counter() - t0
@@ -133,9 +141,11 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="atrium", choices=sorted(WORKLOADS))
     ap.add_argument("--mode", default="fast", choices=["fast", "parity"])
-    ap.add_argument("--spp-per-step", type=int, default=8)
+    ap.add_argument("--spp-per-step", type=int, default=0, help="iterations per step per GPU (0 = the workload's default)")
     ap.add_argument("--ref-rows", type=int, default=16)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--progressive", type=int, default=0, metavar="FRAMES",
+                    help="C5: time FRAMES progressive frames (1 spp each, moving camera, RGB8 read-back) instead of the throughput run")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -143,10 +153,14 @@ def main():
     if args.impl == "reference":
         run_reference(args, rank)
         return
+    if args.progressive:
+        if rank == 0:
+            run_progressive(args)
+        return
     run_ours(args, rank, local_rank, world)
 
 
-from bench_impl import run_ours  # noqa: E402  (second half of this file, split to keep each file small)
+from bench_impl import run_ours, run_progressive  # noqa: E402  (second half of this file, split to keep each file small)
 
 if __name__ == "__main__":
     main()

@@ -19,7 +19,7 @@ def run_ours(args, rank, local_rank, world):
     import torch.distributed as dist
 
     import opencl_pathtracer_b200 as pt
-    from bench import DEPTH, H, W, WORKLOADS, ClockSampler, load_peaks
+    from bench import DEPTH, WORKLOADS, ClockSampler, load_peaks
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — this benchmark has no CPU fallback (use --impl reference for the CPU reference)")
@@ -28,11 +28,13 @@ def run_ours(args, rank, local_rank, world):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     wl = WORKLOADS[args.workload]
-    S, K, WU = args.spp_per_step, args.steps, args.warmup
+    W, H = wl["size"]
+    S, K, WU = (args.spp_per_step or wl["spp"]), args.steps, args.warmup
     mode = pt.MODE_FAST if args.mode == "fast" else pt.MODE_PARITY
     n_pix = W * H
-    scene = pt.Scene(wl["scene"], W, H)
+    scene = pt.Scene(wl["scene"], W, H, load_sky=wl["sky"])
     info = scene.info
+    scene_mb = (info.triangulationSize * 64 + (info.bvhSize // 2) * 64) / 1e6  # DevTri + DevNode (one per inner node)
     stream = torch.cuda.Stream(device=dev)
 
     def first_iter(step):
@@ -142,13 +144,13 @@ def run_ours(args, rank, local_rank, world):
             tp = os.path.join(ROOT, "profiles", "traffic.json")
             if os.path.exists(tp):
                 with open(tp) as f:
-                    traffic = json.load(f).get(dom)
+                    traffic = json.load(f).get(args.workload, {}).get(dom)
 
             def roofline(name):
                 b, t_ms, n, nrays = kern[name]
                 ach = b / (t_ms * 1e-3) / 1e9 if t_ms > 0 else 0.0
                 return {"kernel": name, "bound": "hbm", "achieved": ach, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": ach / peaks["hbm_gbs"],
-                        "peak_kind": peak_kind + " HBM copy bandwidth (working set is L2-resident: see DESIGN.md)",
+                        "peak_kind": peak_kind + " HBM copy bandwidth (%s)" % ("working set is L2-resident: see DESIGN.md" if scene_mb < 100 else "node + triangle records exceed the L2"),
                         "algorithmic_bytes_per_launch": b / max(n, 1), "avg_launch_ms": t_ms / max(n, 1), "launches": n,
                         "mrays_per_s": nrays / (t_ms * 1e-3) / 1e6 if t_ms > 0 else 0.0}
 
@@ -183,7 +185,7 @@ def run_ours(args, rank, local_rank, world):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
             from oracle import ptref
-            rows = (508, 572)
+            rows = (H // 2 - 32, H // 2 + 32)
             t0 = time.perf_counter()
             ptref.render(scene, W, H, DEPTH, 0, 0, 1, rows=rows)
             dt = time.perf_counter() - t0
@@ -202,8 +204,8 @@ def run_ours(args, rank, local_rank, world):
                 "config": {"workload": wl["desc"], "image": [W, H], "ray_max_depth": DEPTH, "sampler": "jittered", "mode": args.mode,
                            "spp_per_step_per_gpu": S, "triangles": int(info.triangulationSize), "bvh_nodes": int(info.bvhSize),
                            "parallelism": "iteration-range sharding x%d, one NCCL reduce of the accumulators per run" % world,
-                           "l2": "not flushed: each step streams ~%.1f GB of path state (> L2); the %.0f MB scene is L2-resident by design"
-                                 % (S * n_pix * 112 / 1e9, (info.triangulationSize * 64 + info.bvhSize * 32) / 1e6)},
+                           "l2": "not flushed: each step streams ~%.1f GB of path state (> L2); scene records %.0f MB (%s the 126 MB L2)"
+                                 % (S * n_pix * 112 / 1e9, scene_mb, "inside" if scene_mb < 100 else "larger than")},
                 "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": 64, "d2h_bytes_per_step": n_pix * 20,
                         "ms_per_step": 1000.0 * e2e_s / K},
                 "gpu_launches": int(launches), "clocks": clk, "roofline": roof, "cpu_baseline": cpu, "mean_rgb": mean_rgb}
@@ -211,3 +213,72 @@ def run_ours(args, rank, local_rank, world):
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def run_progressive(args):
+    """BASELINE.json configs[4] (C5): progressive 1 spp/frame 1080p with a moving camera (the Maya viewport mode).
+    Per frame, through the C ABI with host buffers: ptc_set_camera -> ptc_reset_accumulation -> ptc_render(1 iteration) ->
+    ptc_read_rgb8 (display epilogue on the device, 3 bytes/pixel back to the host). Reports p50 / p99 frame latency."""
+    import numpy as np
+    import torch
+
+    import opencl_pathtracer_b200 as pt
+    from bench import DEPTH, WORKLOADS
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — this benchmark has no CPU fallback")
+    wl = WORKLOADS[args.workload]
+    W, H = wl["size"]
+    scene = pt.Scene(wl["scene"], W, H, load_sky=wl["sky"])
+    tris = scene.triangles()
+    lo = np.array([min(tris[k][a].min() for k in ("S1", "S2", "S3")) for a in "xyz"], dtype=np.float64)
+    hi = np.array([max(tris[k][a].max() for k in ("S1", "S2", "S3")) for a in "xyz"], dtype=np.float64)
+    centre = 0.5 * (lo + hi)
+    cam0 = scene.camera().astype(np.float64).reshape(4, 4)  # position, direction, right, up
+    axis = cam0[3, :3] / np.linalg.norm(cam0[3, :3])
+
+    def rotated(angle):
+        c, s = np.cos(angle), np.sin(angle)
+
+        def rot(v):  # Rodrigues
+            return v * c + np.cross(axis, v) * s + axis * np.dot(axis, v) * (1 - c)
+
+        cam = cam0.copy()
+        cam[0, :3] = centre + rot(cam0[0, :3] - centre)
+        for r in (1, 2, 3):
+            cam[r, :3] = rot(cam0[r, :3])
+        return cam.astype(np.float32).reshape(16)
+
+    mode = pt.MODE_FAST if args.mode == "fast" else pt.MODE_PARITY
+    frames, warm = args.progressive, max(3, args.warmup)
+    lat = []
+    with pt.PathTracerCUDA(W, H, ray_max_depth=DEPTH, mode=mode, device=0, flags=pt.FLAG_NO_VARIANCE, iterations_per_batch=1) as r:
+        r.upload(scene)
+        rgb = np.empty((H, W, 3), dtype=np.uint8)
+        c0 = None
+        for f in range(warm + frames):
+            if f == warm:
+                c0 = r.counters()["kernel_launches"]
+                t_all = time.perf_counter()
+            t0 = time.perf_counter()
+            r.set_camera(rotated(np.radians(0.5) * f))
+            r.reset()
+            r.render(f, 1)
+            r._ck(r._lib.ptc_read_rgb8(r._h, rgb.ctypes.data))
+            if f >= warm:
+                lat.append((time.perf_counter() - t0) * 1e3)
+        total = time.perf_counter() - t_all
+        # reset zeroes the launch counter with the other counters: count the launches of one frame instead
+        r.reset()
+        r.render(0, 1, sync=True)
+        per_frame = r.counters()["kernel_launches"] + 1  # + the RGB8 epilogue kernel
+    lat.sort()
+    p50, p99 = lat[len(lat) // 2], lat[min(len(lat) - 1, int(len(lat) * 0.99))]
+    line = {"metric": "frame latency p50 (progressive 1 spp/frame, moving camera)", "value": p50, "unit": "ms", "n_gpus": 1, "steps": frames,
+            "warmup": warm, "ms_per_step": 1e3 * total / frames, "higher_is_better": False, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "p99_ms": p99, "frames_per_s": frames / total, "samples_per_s": frames * W * H / total,
+            "config": {"workload": "C5: " + wl["desc"] + "; camera orbits 0.5 deg/frame, accumulation reset every frame", "image": [W, H],
+                       "ray_max_depth": DEPTH, "mode": args.mode, "per_frame": "ptc_set_camera + ptc_reset_accumulation + ptc_render(1) + ptc_read_rgb8"},
+            "e2e": {"value": p50, "unit": "ms", "h2d_bytes_per_step": 64, "d2h_bytes_per_step": W * H * 3},
+            "gpu_launches": int(per_frame) * frames, "mean_rgb8": float(rgb.mean())}
+    print(json.dumps(line), flush=True)

@@ -448,12 +448,14 @@ __device__ __forceinline__ void add_sample_atomic(const ImageDev &img, uint32_t 
     atomicAdd(img.rayNb + pix, 1.f);
 }
 
-// :1319-1331; the depth histogram (<= 65 bins) is privatised in shared memory
-__device__ __forceinline__ void count_path(const ImageDev &img, uint32_t *sDepth, uint32_t meta, uint32_t nb, uint32_t nt)
+// :1319-1331; the three histograms are privatised in shared memory (most paths of a frame fall into a few bins: global
+// atomics on them serialise) and flushed once per CTA
+constexpr uint32_t kHistBins = 5000u;  // MAX_INTERSECTION_NUMBER
+__device__ __forceinline__ void count_path(uint32_t *sDepth, uint32_t *sBbx, uint32_t *sTri, uint32_t meta, uint32_t nb, uint32_t nt)
 {
     atomicAdd(&sDepth[meta & 0xffu], 1u);
-    if (nb < 5000u) atomicAdd(&img.rayBbx[nb], 1u);
-    if (nt < 5000u) atomicAdd(&img.rayTri[nt], 1u);
+    if (nb < kHistBins) atomicAdd(&sBbx[nb], 1u);
+    if (nt < kHistBins) atomicAdd(&sTri[nt], 1u);
 }
 
 // ORDERED (jittered / uniform samplers: a path lands in its own pixel): one thread per pixel adds the
@@ -463,7 +465,9 @@ template <bool ORDERED>
 __global__ void __launch_bounds__(kStreamThreads) k_accumulate(FrameParams fp, PathState st, ImageDev img, Counters *cn)
 {
     __shared__ uint32_t sDepth[kMaxBounces + 1];
+    __shared__ uint32_t sBbx[kHistBins], sTri[kHistBins];
     for (int i = threadIdx.x; i <= kMaxBounces; i += blockDim.x) sDepth[i] = 0;
+    for (uint32_t i = threadIdx.x; i < kHistBins; i += blockDim.x) sBbx[i] = sTri[i] = 0;
     __syncthreads();
     const uint32_t nPix = fp.width * fp.height;
     uint32_t nPaths = 0;
@@ -475,7 +479,7 @@ __global__ void __launch_bounds__(kStreamThreads) k_accumulate(FrameParams fp, P
                 const uint32_t k = li * nPix + pix;
                 const float4 x = st.rad[k];
                 const uint32_t tp = target_pixel(st.sample[k], fp.width, fp.height);
-                count_path(img, sDepth, st.meta[k], st.nbbx[k], st.ntri[k]);
+                count_path(sDepth, sBbx, sTri, st.meta[k], st.nbbx[k], st.ntri[k]);
                 if (tp == pix) add_sample(img, pix, x, fp.firstIteration + li);
                 else add_sample_atomic(img, tp, x);
                 nPaths++;
@@ -486,7 +490,7 @@ __global__ void __launch_bounds__(kStreamThreads) k_accumulate(FrameParams fp, P
         const uint32_t total = nPix * fp.nIterations;
         for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < total; k += gridDim.x * blockDim.x)
         {
-            count_path(img, sDepth, st.meta[k], st.nbbx[k], st.ntri[k]);
+            count_path(sDepth, sBbx, sTri, st.meta[k], st.nbbx[k], st.ntri[k]);
             add_sample_atomic(img, target_pixel(st.sample[k], fp.width, fp.height), st.rad[k]);
             nPaths++;
         }
@@ -494,6 +498,11 @@ __global__ void __launch_bounds__(kStreamThreads) k_accumulate(FrameParams fp, P
     __syncthreads();
     for (uint32_t i = threadIdx.x; i <= fp.maxDepth && i <= (uint32_t)kMaxBounces; i += blockDim.x)
         if (sDepth[i]) atomicAdd(&img.rayDepths[i], sDepth[i]);
+    for (uint32_t i = threadIdx.x; i < kHistBins; i += blockDim.x)
+    {
+        if (sBbx[i]) atomicAdd(&img.rayBbx[i], sBbx[i]);
+        if (sTri[i]) atomicAdd(&img.rayTri[i], sTri[i]);
+    }
     for (int o = 16; o; o >>= 1) nPaths += __shfl_xor_sync(0xffffffffu, nPaths, o);
     if ((threadIdx.x & 31u) == 0 && nPaths) atomicAdd(&cn->paths, (unsigned long long)nPaths);
 }
@@ -603,8 +612,9 @@ void launch_shade(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev
 void launch_accumulate(cudaStream_t s, const LaunchCfg &lc, const FrameParams &fp, const PathState &st, const ImageDev &img,
                        Counters *cn)
 {
-    if (fp.sampler == 1) k_accumulate<false><<<lc.streamGrid, kStreamThreads, 0, s>>>(fp, st, img, cn);
-    else k_accumulate<true><<<lc.streamGrid, kStreamThreads, 0, s>>>(fp, st, img, cn);
+    const int grid = lc.streamGrid / 2;  // 40 KB of histograms per CTA: 4 CTAs per SM
+    if (fp.sampler == 1) k_accumulate<false><<<grid, kStreamThreads, 0, s>>>(fp, st, img, cn);
+    else k_accumulate<true><<<grid, kStreamThreads, 0, s>>>(fp, st, img, cn);
 }
 
 void launch_probe_primary(cudaStream_t s, const FrameParams &fp, const PathState &st, int32_t *hit, float2 *stOut, float *dist2,
