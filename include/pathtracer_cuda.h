@@ -65,7 +65,9 @@ enum
 {
     PTC_FLAG_STAGE_TIMING = 1u << 0, /* bracket every stage launch with CUDA events (ptc_read_counters) */
     PTC_FLAG_NO_VARIANCE = 1u << 1,  /* do not maintain imageV (only the dead supersampling path reads it) */
-    PTC_FLAG_NO_GRAPH = 1u << 2      /* launch stages directly instead of replaying a captured CUDA graph */
+    PTC_FLAG_NO_GRAPH = 1u << 2,     /* launch stages directly instead of replaying a captured CUDA graph */
+    PTC_FLAG_BVH2 = 1u << 3          /* FAST mode: traverse the reference BVH2 itself instead of the 8-wide compressed BVH
+                                        that ptc_upload_scene collapses it into (PARITY always walks the BVH2) */
 };
 
 /* Replaces the `-D` build options of reference Controleur/PathTracer_OpenCL.cpp:292-314: all run-time here. */
@@ -191,6 +193,22 @@ PTC_API int ptc_trace_primary(ptc_ctx *ctx, uint32_t iteration, int32_t *hit, fl
 
 /* Parity probe: per-pixel radiance of exactly one iteration (what Kernel_Main adds to imageColor). */
 PTC_API int ptc_render_single(ptc_ctx *ctx, uint32_t iteration, float *radiance);
+
+/* Host utility: the 8-wide compressed BVH that ptc_upload_scene collapses the reference BVH2 into in FAST mode
+ * (opencl_pathtracer_b200/csrc/pt_wide_build.cu), exposed for inspection and structural tests. nodes = n_nodes records of
+ * 80 bytes (DevNode8, csrc/pt_wide.cuh); tri_order[i] = index in the BVH-ordered triangulation of the i-th triangle
+ * in wide order; depth = levels of wide nodes. Needs no CUDA device. Release with ptc_wide_bvh_free. */
+typedef struct ptc_wide_bvh
+{
+    void *nodes;
+    uint32_t *tri_order;
+    uint32_t n_nodes;
+    uint32_t n_triangles;
+    uint32_t depth;
+    uint32_t reserved;
+} ptc_wide_bvh;
+PTC_API int ptc_wide_bvh_build(const ptc_scene_view *scene, ptc_wide_bvh *out);
+PTC_API void ptc_wide_bvh_free(ptc_wide_bvh *bvh);
 
 /* Pinned host memory for read-backs inside timed regions. */
 PTC_API void *ptc_host_alloc(size_t bytes);

@@ -16,7 +16,7 @@ PTC_OK = 0
 PTC_ERR_INVALID, PTC_ERR_CUDA, PTC_ERR_NO_DEVICE, PTC_ERR_STATE, PTC_ERR_LIMIT, PTC_ERR_UNSUPPORTED = 1, 2, 3, 4, 5, 6
 SAMPLER_JITTERED, SAMPLER_RANDOM, SAMPLER_UNIFORM = 0, 1, 2
 MODE_PARITY, MODE_FAST = 0, 1
-FLAG_STAGE_TIMING, FLAG_NO_VARIANCE, FLAG_NO_GRAPH = 1, 2, 4
+FLAG_STAGE_TIMING, FLAG_NO_VARIANCE, FLAG_NO_GRAPH, FLAG_BVH2 = 1, 2, 4, 8
 MAX_INTERSECTION_NUMBER = 5000
 
 
@@ -51,6 +51,11 @@ class DeviceBuffers(C.Structure):
                 ("ray_bbx", C.c_void_p), ("ray_tri", C.c_void_p), ("stream", C.c_void_p)]
 
 
+class WideBvh(C.Structure):
+    _fields_ = [("nodes", C.c_void_p), ("tri_order", C.c_void_p), ("n_nodes", C.c_uint32), ("n_triangles", C.c_uint32),
+                ("depth", C.c_uint32), ("reserved", C.c_uint32)]
+
+
 class SceneInfo(C.Structure):
     _fields_ = [("bvhSize", C.c_uint32), ("bvhMaxDepth", C.c_uint32), ("triangulationSize", C.c_uint32), ("lightsSize", C.c_uint32),
                 ("materiauxSize", C.c_uint32), ("texturesSize", C.c_uint32), ("texturesDataSize", C.c_uint32), ("imageWidth", C.c_uint32),
@@ -63,7 +68,7 @@ class SceneInfo(C.Structure):
 PTC_SYMBOLS = ["ptc_create", "ptc_upload_scene", "ptc_set_camera", "ptc_reset_accumulation", "ptc_render", "ptc_synchronize",
                "ptc_read_image", "ptc_read_variance", "ptc_read_stats", "ptc_read_rgb8", "ptc_add_image", "ptc_read_counters",
                "ptc_get_device_buffers", "ptc_trace_primary", "ptc_render_single", "ptc_host_alloc", "ptc_host_free",
-               "ptc_last_error", "ptc_version", "ptc_device_count", "ptc_destroy"]
+               "ptc_last_error", "ptc_version", "ptc_device_count", "ptc_destroy", "ptc_wide_bvh_build", "ptc_wide_bvh_free"]
 
 _cuda = None
 _host = None
@@ -98,6 +103,9 @@ def cuda_lib():
     L.ptc_add_image.argtypes = [vp, vp, vp]
     L.ptc_read_counters.argtypes = [vp, P(Counters)]
     L.ptc_get_device_buffers.argtypes = [vp, P(DeviceBuffers)]
+    L.ptc_wide_bvh_build.argtypes = [P(SceneView), P(WideBvh)]
+    L.ptc_wide_bvh_free.argtypes = [P(WideBvh)]
+    L.ptc_wide_bvh_free.restype = None
     L.ptc_trace_primary.argtypes = [vp, u32, vp, vp, vp, vp, vp, vp]
     L.ptc_render_single.argtypes = [vp, u32, vp]
     L.ptc_host_alloc.argtypes = [C.c_size_t]

@@ -15,6 +15,7 @@
 #include <vector>
 
 #include "pt_launch.h"
+#include "pt_wide_build.h"
 
 using namespace ptc;
 
@@ -73,6 +74,10 @@ struct ptc_ctx
     DevBuf<uint4> textures;
     DevBuf<uchar4> texels;
     DevBuf<uint32_t> bigLeaf;
+    DevBuf<DevNode8> nodes8;  // FAST + wide BVH only
+    DevBuf<DevTri> tris8;
+    DevBuf<uint32_t> tri8Index;
+    bool wide = false;
     SceneDev sc{};
     Camera cam{};
 
@@ -203,6 +208,7 @@ void ptc_destroy(ptc_ctx *ctx)
     for (auto e : ctx->eventPool) cudaEventDestroy(e);
     ctx->nodes.release(); ctx->tris.release(); ctx->shade.release(); ctx->materials.release(); ctx->lights.release();
     ctx->textures.release(); ctx->texels.release(); ctx->bigLeaf.release();
+    ctx->nodes8.release(); ctx->tris8.release(); ctx->tri8Index.release();
     ctx->org.release(); ctx->dir.release(); ctx->thr.release(); ctx->rad.release(); ctx->hit.release();
     ctx->seed.release(); ctx->sample.release(); ctx->meta.release(); ctx->nbbx.release(); ctx->ntri.release();
     ctx->occl.release(); ctx->queue[0].release(); ctx->queue[1].release(); ctx->counters.release();
@@ -254,6 +260,8 @@ int ptc_create(const ptc_config *config, ptc_ctx **out_ctx)
     c->cfg = *config;
     c->device = config->device;
     c->fast = config->mode == PTC_MODE_FAST;
+    c->wide = c->fast && !(config->flags & PTC_FLAG_BVH2);
+    if (const char *e = std::getenv("PTC_WIDE")) c->wide = c->fast && std::atoi(e) != 0;
     c->nPix = config->image_width * config->image_height;
     c->smCount = prop.multiProcessorCount;
     if (config->stream) c->stream = (cudaStream_t)config->stream;
@@ -274,7 +282,8 @@ int ptc_create(const ptc_config *config, ptc_ctx **out_ctx)
     c->batchIters = b;
     c->capacity = (size_t)b * c->nPix;
     c->lc.stackDepth = 32;
-    c->lc.traverseGrid = c->smCount * traverse_ctas_per_sm(c->fast, c->lc.stackDepth);
+    c->lc.wide = false;
+    c->lc.traverseGrid = c->smCount * traverse_ctas_per_sm(c->fast, false, c->lc.stackDepth);
     c->lc.streamGrid = c->smCount * 8;
     c->lc.refillMin = 4;  // idle lanes that trigger a refill from the warp's staged rays (profiles/r01_sweeps.txt)
     if (const char *e = std::getenv("PTC_REFILL_MIN")) c->lc.refillMin = (uint32_t)std::max(1, std::min(32, std::atoi(e)));
@@ -476,8 +485,22 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
     sky.sinRot = s->sky->sinRotationAngle;
     static_assert(sizeof(DevLight) == sizeof(ptc_light), "Light is uploaded as is");
 
+    // ---- FAST mode: the 8-wide compressed BVH (pt_wide_build.cu) and the intersection records in its order
+    WideBvh wideBvh;
+    std::vector<DevTri> hTris8;
+    if (ctx->wide)
+    {
+        std::string werr;
+        if (!build_wide_bvh(s, wideBvh, werr)) return fail(ctx, PTC_ERR_INVALID, "%s", werr.c_str());
+        if (wideBvh.depth + 1 > 64u) return fail(ctx, PTC_ERR_LIMIT, "wide BVH of %u levels", wideBvh.depth);
+        hTris8.resize(wideBvh.triOrder.size());
+#pragma omp parallel for schedule(static)
+        for (long long i = 0; i < (long long)hTris8.size(); i++) hTris8[i] = hTris[wideBvh.triOrder[i]];
+    }
+
     // ---- upload (pending renders use the old buffers: wait for them first)
     CK(cudaStreamSynchronize(ctx->stream));
+    CK(ctx->nodes8.alloc(wideBvh.nodes.size())); CK(ctx->tris8.alloc(hTris8.size())); CK(ctx->tri8Index.alloc(wideBvh.triOrder.size()));
     CK(ctx->nodes.alloc(nInner)); CK(ctx->tris.alloc(nT)); CK(ctx->shade.alloc(nT)); CK(ctx->materials.alloc(nM));
     CK(ctx->lights.alloc(nL)); CK(ctx->textures.alloc(nX)); CK(ctx->texels.alloc(nTexel)); CK(ctx->bigLeaf.alloc(bigLeaf.size()));
     auto up = [&](void *dst, const void *src, size_t bytes) { return bytes ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream) : cudaSuccess; };
@@ -489,22 +512,59 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
     CK(up(ctx->textures.p, hTex.data(), sizeof(uint4) * nX));
     CK(up(ctx->texels.p, s->textures_data, sizeof(uchar4) * nTexel));
     CK(up(ctx->bigLeaf.p, bigLeaf.data(), sizeof(uint32_t) * bigLeaf.size()));
+    CK(up(ctx->nodes8.p, wideBvh.nodes.data(), sizeof(DevNode8) * wideBvh.nodes.size()));
+    CK(up(ctx->tris8.p, hTris8.data(), sizeof(DevTri) * hTris8.size()));
+    CK(up(ctx->tri8Index.p, wideBvh.triOrder.data(), sizeof(uint32_t) * wideBvh.triOrder.size()));
     CK(cudaStreamSynchronize(ctx->stream));  // host staging vectors die at return
 
     SceneDev &sc = ctx->sc;
     sc.nodes = ctx->nodes.p; sc.tris = ctx->tris.p; sc.shade = ctx->shade.p; sc.materials = ctx->materials.p;
     sc.lights = ctx->lights.p; sc.textures = ctx->textures.p; sc.texels = ctx->texels.p;
     sc.bigLeafCount = bigLeaf.empty() ? nullptr : ctx->bigLeaf.p;
+    sc.nodes8 = ctx->wide ? ctx->nodes8.p : nullptr; sc.tris8 = ctx->wide ? ctx->tris8.p : nullptr;
+    sc.tri8Index = ctx->wide ? ctx->tri8Index.p : nullptr; sc.nNodes8 = ctx->wide ? (uint32_t)wideBvh.nodes.size() : 0u;
+    ctx->lc.wide = ctx->wide;
     sc.rootRef = rootRef; sc.nLights = nL; sc.nTriangles = nT; sc.sky = sky;
     ctx->cam = Camera{to4(s->camera_position), to4(s->camera_direction), to4(s->camera_right), to4(s->camera_up)};
     // traversal stack: one entry per level below the root is enough (a push happens only when descending)
     if (!std::getenv("PTC_FULL_STACK"))
     {
         ctx->lc.stackDepth = (int)std::min<uint32_t>(32u, std::max<uint32_t>(4u, maxDepth + 1));
-        if (!std::getenv("PTC_CTAS_PER_SM")) ctx->lc.traverseGrid = ctx->smCount * traverse_ctas_per_sm(ctx->fast, ctx->lc.stackDepth);
+        if (ctx->wide) ctx->lc.stackDepth = (int)std::max<uint32_t>(2u, wideBvh.depth + 1);  // one postponed sibling group per level
+        if (!std::getenv("PTC_CTAS_PER_SM")) ctx->lc.traverseGrid = ctx->smCount * traverse_ctas_per_sm(ctx->fast, ctx->wide, ctx->lc.stackDepth);
     }
     ctx->sceneLoaded = true;
     return PTC_OK;
+}
+
+int ptc_wide_bvh_build(const ptc_scene_view *scene, ptc_wide_bvh *out)
+{
+    if (!scene || !out || scene->struct_size != sizeof(ptc_scene_view)) return PTC_ERR_INVALID;
+    std::memset(out, 0, sizeof(*out));
+    WideBvh w;
+    std::string err;
+    if (!build_wide_bvh(scene, w, err)) return fail(nullptr, PTC_ERR_INVALID, "%s", err.c_str());
+    out->n_nodes = (uint32_t)w.nodes.size();
+    out->n_triangles = (uint32_t)w.triOrder.size();
+    out->depth = w.depth;
+    out->nodes = std::malloc(std::max<size_t>(1, sizeof(DevNode8) * w.nodes.size()));
+    out->tri_order = (uint32_t *)std::malloc(std::max<size_t>(1, sizeof(uint32_t) * w.triOrder.size()));
+    if (!out->nodes || !out->tri_order)
+    {
+        ptc_wide_bvh_free(out);
+        return fail(nullptr, PTC_ERR_INVALID, "ptc_wide_bvh_build: out of memory");
+    }
+    std::memcpy(out->nodes, w.nodes.data(), sizeof(DevNode8) * w.nodes.size());
+    std::memcpy(out->tri_order, w.triOrder.data(), sizeof(uint32_t) * w.triOrder.size());
+    return PTC_OK;
+}
+
+void ptc_wide_bvh_free(ptc_wide_bvh *bvh)
+{
+    if (!bvh) return;
+    std::free(bvh->nodes);
+    std::free(bvh->tri_order);
+    std::memset(bvh, 0, sizeof(*bvh));
 }
 
 int ptc_set_camera(ptc_ctx *ctx, const float camera[16])

@@ -86,6 +86,11 @@ struct SceneDev
     const uint4 *textures;  // width height offset 0
     const uchar4 *texels;
     const uint32_t *bigLeafCount;  // may be null
+    // FAST mode with the wide BVH (pt_wide.cuh); null / 0 otherwise
+    const struct DevNode8 *nodes8;
+    const DevTri *tris8;           // the intersection records again, in wide order
+    const uint32_t *tri8Index;     // wide order -> BVH order
+    uint32_t nNodes8;
     uint32_t rootRef;
     uint32_t nLights;
     uint32_t nTriangles;

@@ -11,6 +11,7 @@
 #include "pt_launch.h"
 #include "pt_shade.cuh"
 #include "pt_traverse.cuh"
+#include "pt_wide.cuh"
 
 namespace ptc
 {
@@ -130,13 +131,14 @@ struct StagedRays  // one per warp
 };
 constexpr size_t kStageBytes = sizeof(StagedRays) * (kTraverseThreads / 32);
 
-template <bool ANY, bool FAST>
-__global__ void __launch_bounds__(kTraverseThreads) k_trace(SceneDev sc, PathState st, const uint32_t *__restrict__ queue,
+template <bool ANY, bool FAST, typename LaneT>
+__global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas) k_trace(SceneDev sc, PathState st, const uint32_t *__restrict__ queue,
                                                            Counters *__restrict__ cn, int bounce, uint32_t popMin, int stackDepth)
 {
-    extern __shared__ __align__(16) uint32_t smemStack[];
-    uint32_t *stk = smemStack + threadIdx.x;
-    StagedRays &stage = reinterpret_cast<StagedRays *>(smemStack + stackDepth * kTraverseThreads)[threadIdx.x >> 5];
+    typedef typename LaneT::StackT StackT;
+    extern __shared__ __align__(16) unsigned char smemRaw[];
+    StackT *stk = reinterpret_cast<StackT *>(smemRaw) + threadIdx.x;
+    StagedRays &stage = reinterpret_cast<StagedRays *>(smemRaw + sizeof(StackT) * stackDepth * kTraverseThreads)[threadIdx.x >> 5];
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt = (1u << lane) - 1u;
     const unsigned full = 0xffffffffu;
@@ -144,11 +146,8 @@ __global__ void __launch_bounds__(kTraverseThreads) k_trace(SceneDev sc, PathSta
     const uint32_t nL = ANY ? sc.nLights : 1u;
     const uint32_t total = count * nL;  // upload_scene guarantees capacity * nLights < 2^32
     uint32_t *cursor = ANY ? &cn->curConnect[bounce] : &cn->curExtend[bounce];
-    TraceLane L;
-    L.cur = kIdle;
-    L.nb = L.nt = 0;
-    L.found = false;
-    L.hitTri = -1;
+    LaneT L;
+    L.reset();
     bool exhausted = false;
     uint32_t qHead = 0, qCount = 0;  // staged rays [qHead, qCount) are waiting (warp-uniform)
     uint32_t p = 0, li = 0;
@@ -156,7 +155,7 @@ __global__ void __launch_bounds__(kTraverseThreads) k_trace(SceneDev sc, PathSta
     while (true)
     {
         // ---- completion: write the result of a finished ray (the counters are fire-and-forget reductions)
-        if (L.cur == kDone)
+        if (L.finished())
         {
             if (!ANY)
             {
@@ -175,9 +174,9 @@ __global__ void __launch_bounds__(kTraverseThreads) k_trace(SceneDev sc, PathSta
                 if (L.nt) atomicAdd(&st.ntri[p], L.nt);
             }
             nbSum += L.nb; ntSum += L.nt; nRays++;
-            L.cur = kIdle;
+            L.set_idle();
         }
-        unsigned idle = __ballot_sync(full, L.cur == kIdle);
+        unsigned idle = __ballot_sync(full, L.idle());
         if (idle)
         {
             // ---- staging: the whole warp prepares the next 32 items
@@ -234,7 +233,7 @@ __global__ void __launch_bounds__(kTraverseThreads) k_trace(SceneDev sc, PathSta
             if (qHead < qCount && (nIdle >= popMin || exhausted))
             {
                 const uint32_t e = qHead + (uint32_t)__popc(idle & lt);
-                if (L.cur == kIdle && e < qCount)
+                if (L.idle() && e < qCount)
                 {
                     const float4 o = stage.org[e], d = stage.dir[e], ib = stage.invBest[e];
                     const uint32_t item = stage.item[e];
@@ -244,11 +243,11 @@ __global__ void __launch_bounds__(kTraverseThreads) k_trace(SceneDev sc, PathSta
                     r.ox = o.x; r.oy = o.y; r.oz = o.z; r.ow = o.w;
                     r.dx = d.x; r.dy = d.y; r.dz = d.z; r.dw = d.w;
                     r.ix = ib.x; r.iy = ib.y; r.iz = ib.z;
-                    lane_start(L, sc, r, ib.w);
+                    lane_begin(L, sc, r, ib.w);
                 }
                 qHead = min(qHead + nIdle, qCount);
                 __syncwarp();
-                idle = __ballot_sync(full, L.cur == kIdle);
+                idle = __ballot_sync(full, L.idle());
             }
             if (idle == full)
             {
@@ -257,21 +256,21 @@ __global__ void __launch_bounds__(kTraverseThreads) k_trace(SceneDev sc, PathSta
             }
         }
         // ---- node phase: node steps while at least half of the lanes that hold a ray wait for a node
-        const int nHave = 32 - __popc(__ballot_sync(full, L.cur >= kDone));
+        const int nHave = 32 - __popc(__ballot_sync(full, L.idle() || L.finished()));
         while (true)
         {
-            const bool wantNode = lane_at_inner(L);
+            const bool wantNode = L.wants_node();
             const int nN = __popc(__ballot_sync(full, wantNode));
             if (nN == 0 || 2 * nN < nHave) break;
-            if (wantNode) node_step<FAST>(L, sc, stk, kTraverseThreads);
+            if (wantNode) lane_node_step<FAST>(L, sc, stk, kTraverseThreads);
         }
         // ---- triangle phase: at least one step if any lane waits for a triangle, then while they are the majority
         while (true)
         {
-            const bool wantTri = lane_at_leaf(L);
+            const bool wantTri = L.wants_tri();
             const int nT = __popc(__ballot_sync(full, wantTri));
             if (nT == 0) break;
-            if (wantTri) tri_step<ANY>(L, sc, stk, kTraverseThreads);
+            if (wantTri) lane_tri_step<ANY>(L, sc, stk, kTraverseThreads);
             if (2 * nT <= nHave) break;
         }
     }
@@ -562,21 +561,26 @@ __global__ void k_add_image(ImageDev img, uint32_t nPixels, const float4 *color,
 }
 
 // ------------------------------------------------------------------------------------------------ launchers
-static inline size_t stack_bytes(const LaunchCfg &lc) { return (size_t)lc.stackDepth * kTraverseThreads * sizeof(uint32_t) + kStageBytes; }
+static inline size_t stack_bytes(bool wide, int stackDepth)
+{
+    return (size_t)stackDepth * kTraverseThreads * (wide ? sizeof(uint2) : sizeof(uint32_t)) + kStageBytes;
+}
 
-template <bool ANY, bool FAST>
-static int occupancy_of(size_t kStackBytes)
+template <bool ANY, bool FAST, typename LaneT>
+static int occupancy_of(size_t bytes)
 {
     int n = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_trace<ANY, FAST>, kTraverseThreads, kStackBytes);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_trace<ANY, FAST, LaneT>, kTraverseThreads, bytes);
     return n;
 }
 
-int traverse_ctas_per_sm(bool fast, int stackDepth)
+int traverse_ctas_per_sm(bool fast, bool wide, int stackDepth)
 {
-    const size_t kStackBytes = (size_t)stackDepth * kTraverseThreads * sizeof(uint32_t) + kStageBytes;
-    int n = fast ? occupancy_of<false, true>(kStackBytes) : occupancy_of<false, false>(kStackBytes);
-    int m = fast ? occupancy_of<true, true>(kStackBytes) : occupancy_of<true, false>(kStackBytes);
+    const size_t bytes = stack_bytes(wide, stackDepth);
+    int n, m;
+    if (wide) { n = occupancy_of<false, true, WideLane>(bytes); m = occupancy_of<true, true, WideLane>(bytes); }
+    else if (fast) { n = occupancy_of<false, true, TraceLane>(bytes); m = occupancy_of<true, true, TraceLane>(bytes); }
+    else { n = occupancy_of<false, false, TraceLane>(bytes); m = occupancy_of<true, false, TraceLane>(bytes); }
     n = n < m ? n : m;
     return n < 1 ? 1 : n;
 }
@@ -588,18 +592,26 @@ void launch_generate(cudaStream_t s, const LaunchCfg &lc, const FrameParams &fp,
     k_generate<<<lc.streamGrid, kStreamThreads, 0, s>>>(fp, cam, st);
 }
 
+template <bool ANY>
+static void launch_trace(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const PathState &st, const uint32_t *queue,
+                         Counters *cn, int bounce)
+{
+    const size_t smem = stack_bytes(lc.wide, lc.stackDepth);
+    if (lc.wide) k_trace<ANY, true, WideLane><<<lc.traverseGrid, kTraverseThreads, smem, s>>>(sc, st, queue, cn, bounce, lc.refillMin, lc.stackDepth);
+    else if (fast) k_trace<ANY, true, TraceLane><<<lc.traverseGrid, kTraverseThreads, smem, s>>>(sc, st, queue, cn, bounce, lc.refillMin, lc.stackDepth);
+    else k_trace<ANY, false, TraceLane><<<lc.traverseGrid, kTraverseThreads, smem, s>>>(sc, st, queue, cn, bounce, lc.refillMin, lc.stackDepth);
+}
+
 void launch_extend(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const PathState &st, const uint32_t *queue,
                    Counters *cn, int bounce)
 {
-    if (fast) k_trace<false, true><<<lc.traverseGrid, kTraverseThreads, stack_bytes(lc), s>>>(sc, st, queue, cn, bounce, lc.refillMin, lc.stackDepth);
-    else k_trace<false, false><<<lc.traverseGrid, kTraverseThreads, stack_bytes(lc), s>>>(sc, st, queue, cn, bounce, lc.refillMin, lc.stackDepth);
+    launch_trace<false>(s, lc, fast, sc, st, queue, cn, bounce);
 }
 
 void launch_connect(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const PathState &st, const uint32_t *queue,
                     Counters *cn, int bounce)
 {
-    if (fast) k_trace<true, true><<<lc.traverseGrid, kTraverseThreads, stack_bytes(lc), s>>>(sc, st, queue, cn, bounce, lc.refillMin, lc.stackDepth);
-    else k_trace<true, false><<<lc.traverseGrid, kTraverseThreads, stack_bytes(lc), s>>>(sc, st, queue, cn, bounce, lc.refillMin, lc.stackDepth);
+    launch_trace<true>(s, lc, fast, sc, st, queue, cn, bounce);
 }
 
 void launch_shade(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const FrameParams &fp, const PathState &st,

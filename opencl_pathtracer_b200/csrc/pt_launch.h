@@ -11,9 +11,10 @@ struct LaunchCfg
     int streamGrid;    // grid of the streaming stages (generate / shade / accumulate)
     uint32_t refillMin;  // idle lanes of a warp that trigger a refill from the work cursor (1..32)
     int stackDepth;      // traversal stack entries per thread (BVH depth + 1, at most kStackDepth)
+    bool wide;           // FAST mode: traverse the 8-wide compressed BVH (stackDepth then counts 8-byte entries)
 };
 
-int traverse_ctas_per_sm(bool fast, int stackDepth);
+int traverse_ctas_per_sm(bool fast, bool wide, int stackDepth);
 
 void launch_reset(cudaStream_t s, Counters *cn, uint32_t nPaths);
 void launch_generate(cudaStream_t s, const LaunchCfg &lc, const FrameParams &fp, const Camera &cam, const PathState &st);

@@ -162,6 +162,16 @@ struct TraceLane
     uint32_t nb, nt;
     bool regular;
     bool found;        // ANY: an occluder was accepted
+
+    // the interface k_trace drives (shared with WideLane, pt_wide.cuh)
+    typedef uint32_t StackT;
+    static constexpr int kMinCtas = 1;
+    __device__ __forceinline__ void reset() { cur = kIdle; nb = nt = 0; found = false; hitTri = -1; }
+    __device__ __forceinline__ bool idle() const { return cur == kIdle; }
+    __device__ __forceinline__ void set_idle() { cur = kIdle; }
+    __device__ __forceinline__ bool finished() const { return cur == kDone; }
+    __device__ __forceinline__ bool wants_node() const { return !(cur & kLeafBit); }
+    __device__ __forceinline__ bool wants_tri() const { return (cur & kLeafBit) && cur < kDone; }
 };
 
 __device__ __forceinline__ bool lane_at_inner(const TraceLane &L) { return !(L.cur & kLeafBit); }
@@ -177,7 +187,7 @@ __device__ __forceinline__ uint32_t stack_pop(int &sp, const uint32_t *stk, cons
     return next;
 }
 
-__device__ __forceinline__ void lane_start(TraceLane &L, const SceneDev &sc, const Ray &r, float best)
+__device__ __forceinline__ void lane_begin(TraceLane &L, const SceneDev &sc, const Ray &r, float best)
 {
     L.r = r;
     L.best = best;
@@ -196,7 +206,7 @@ __device__ __forceinline__ void lane_start(TraceLane &L, const SceneDev &sc, con
 // One inner-node visit: both child boxes tested (:660-672), then the successor chosen without divergent branches:
 // both hit -> near child, far child pushed; one hit -> that child; none -> pop.
 template <bool FAST>
-__device__ __forceinline__ void node_step(TraceLane &L, const SceneDev &sc, uint32_t *stk, const int stride)
+__device__ __forceinline__ void lane_node_step(TraceLane &L, const SceneDev &sc, uint32_t *stk, const int stride)
 {
     const DevNode *nd = &sc.nodes[L.cur];
     float4 a, b, c, dd;
@@ -230,7 +240,7 @@ __device__ __forceinline__ void node_step(TraceLane &L, const SceneDev &sc, uint
 }
 
 template <bool ANY>
-__device__ __forceinline__ void tri_step(TraceLane &L, const SceneDev &sc, const uint32_t *stk, const int stride)
+__device__ __forceinline__ void lane_tri_step(TraceLane &L, const SceneDev &sc, const uint32_t *stk, const int stride)
 {
     const uint32_t i = (L.cur >> 4) & 0x7ffffffu;
     const bool big = (L.cur & 15u) == 0u;

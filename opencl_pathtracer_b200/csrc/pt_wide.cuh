@@ -1,0 +1,185 @@
+// pt_wide.cuh — FAST mode only: traversal of the 8-wide compressed BVH that ptc_upload_scene collapses the reference
+// BVH2 into (pt_wide_build.cu). The reference has no such structure (Kernel/PathTracer_FullKernel.cl:620-783 walks the
+// BVH2 of Controleur/PathTracer_BVH.cpp); this is the "option of widening" of the north star. What stays the reference's:
+// the triangle test (tri_test: Triangle_Intersects :519-566, same operations, same order, same acceptance rule), so a
+// hit carries the same (s, t, distance) bits as in PARITY mode. What changes is WHICH triangles get tested and in which
+// order: boxes are quantised outwards (never smaller than the exact box) and children are visited front to back by
+// ray octant, so the closest hit is the one PARITY finds except between candidates at exactly the same distance.
+//
+// Node layout (80 bytes, after Ylitie, Karras, Laine: "Efficient Incoherent Ray Traversal on GPUs Through Compressed
+// Wide BVHs", HPG 2017): child boxes are 8-bit offsets on a per-node grid p + q * 2^e; inner children are stored
+// consecutively from childBase, the triangles of leaf children consecutively from triBase (at most 3 per child slot);
+// meta[i] = 0 (empty slot), (0b001 << 5) | (24 + i) (inner child in slot i) or (unary count << 5) | offset (leaf).
+#pragma once
+
+#include "pt_traverse.cuh"
+
+namespace ptc
+{
+struct __align__(16) DevNode8
+{
+    float px, py, pz;       // grid origin = lower corner of the node
+    uint32_t eimask;        // bytes 0..2: IEEE biased exponents of the grid step per axis; byte 3: mask of inner children
+    uint32_t childBase;     // index of the first inner child
+    uint32_t triBase;       // index (wide order) of the first triangle of the leaf children
+    uint32_t meta[2];       // 8 x 8 bit
+    uint32_t qlo[3][2];     // 8 x 8 bit per axis
+    uint32_t qhi[3][2];
+};
+static_assert(sizeof(DevNode8) == 80, "DevNode8");
+
+struct WideLane
+{
+    Ray r;             // ix, iy, iz clamped to finite values
+    float best;        // squared distance bound, the reference's `squaredDistance`
+    float tmax;        // the same bound as a ray parameter, padded
+    uint32_t gx, gy;   // node group: first child index | bits 31..24 children still to visit (front to back), bits 7..0 imask
+    uint32_t tx, ty;   // triangle group: first triangle | 24 bits of triangles still to test
+    uint32_t octinv4;  // (7 - ray octant) in every byte
+    int sp;            // stack entries, -1 = no ray
+    int hitTri;
+    float hs, ht, htp;
+    uint32_t hmat;
+    uint32_t nb, nt;
+    bool found;
+
+    typedef uint2 StackT;
+    static constexpr int kMinCtas = 8;  // 64 registers: 8 CTAs of 4 warps per SM
+    __device__ __forceinline__ void reset() { sp = -1; gy = ty = 0; nb = nt = 0; found = false; hitTri = -1; }
+    __device__ __forceinline__ bool idle() const { return sp < 0; }
+    __device__ __forceinline__ void set_idle() { sp = -1; }
+    __device__ __forceinline__ bool finished() const { return sp == 0 && ty == 0u && gy <= 0x00ffffffu; }
+    __device__ __forceinline__ bool wants_node() const { return sp >= 0 && ty == 0u && gy > 0x00ffffffu; }
+    __device__ __forceinline__ bool wants_tri() const { return sp >= 0 && ty != 0u; }
+};
+
+__device__ __forceinline__ float finite_inverse(float inv, float d)
+{
+    return fabsf(inv) < 1.0e30f ? inv : copysignf(1.0e30f, d);  // d = +-0 or denormal: a huge slope instead of inf (no 0 * inf)
+}
+
+__device__ __forceinline__ float bound_as_parameter(float best)
+{
+    return sqrtf(best) * 1.00001f;  // directions are unit length; the pad keeps the cull conservative
+}
+
+__device__ __forceinline__ void lane_begin(WideLane &L, const SceneDev &sc, const Ray &r, float best)
+{
+    L.r = r;
+    L.r.ix = finite_inverse(r.ix, r.dx);
+    L.r.iy = finite_inverse(r.iy, r.dy);
+    L.r.iz = finite_inverse(r.iz, r.dz);
+    L.best = best;
+    L.tmax = bound_as_parameter(best);
+    const uint32_t oct = (r.dx < 0 ? 4u : 0u) | (r.dy < 0 ? 2u : 0u) | (r.dz < 0 ? 1u : 0u);
+    L.octinv4 = (7u - oct) * 0x01010101u;
+    L.gx = 0u;
+    L.gy = sc.nNodes8 ? 0x80000000u : 0u;  // "slot 7 ^ octinv of an imask-less group at index 0" = the root
+    L.tx = L.ty = 0u;
+    L.sp = 0;
+    L.hitTri = -1;
+    L.hs = L.ht = L.htp = 0.f;
+    L.hmat = 0;
+    L.nb = L.nt = 0;
+    L.found = false;
+}
+
+// nothing left in the current groups: continue with the most recently postponed siblings
+__device__ __forceinline__ void wide_normalise(WideLane &L, const uint2 *stk, const int stride)
+{
+    const bool pop = L.ty == 0u && L.gy <= 0x00ffffffu && L.sp > 0;
+    if (pop)
+    {
+        const uint2 e = stk[(L.sp - 1) * stride];
+        L.gx = e.x;
+        L.gy = e.y;
+    }
+    L.sp -= pop ? 1 : 0;
+}
+
+__device__ __forceinline__ float q8(uint32_t w, int j) { return (float)((w >> (8 * j)) & 0xffu); }
+
+// One node visit: take the nearest unvisited child of the current group, postpone its siblings, test its 8 children.
+template <bool FAST>
+__device__ __forceinline__ void lane_node_step(WideLane &L, const SceneDev &sc, uint2 *stk, const int stride)
+{
+    const uint32_t hits = L.gy;
+    const int bit = 31 - __clz((int)hits);
+    const uint32_t slot = (uint32_t)(bit - 24) ^ (L.octinv4 & 7u);
+    const uint32_t rest = hits & ~(1u << bit);
+    const uint32_t rel = (uint32_t)__popc(hits & 0xffu & ((1u << slot) - 1u));
+    const uint4 *np = reinterpret_cast<const uint4 *>(sc.nodes8 + (L.gx + rel));
+    const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+    if (rest > 0x00ffffffu) stk[L.sp * stride] = make_uint2(L.gx, rest);
+    L.sp += rest > 0x00ffffffu ? 1 : 0;
+    L.nb += 8;
+
+    // the ray in the node's grid: t(q) = q * (2^e / d) + (p - o) / d, the constant term padded outwards by 2^-21
+    const float adx = __uint_as_float((n0.w & 0xffu) << 23) * L.r.ix;
+    const float ady = __uint_as_float(((n0.w >> 8) & 0xffu) << 23) * L.r.iy;
+    const float adz = __uint_as_float(((n0.w >> 16) & 0xffu) << 23) * L.r.iz;
+    const float bx = (__uint_as_float(n0.x) - L.r.ox) * L.r.ix;
+    const float by = (__uint_as_float(n0.y) - L.r.oy) * L.r.iy;
+    const float bz = (__uint_as_float(n0.z) - L.r.oz) * L.r.iz;
+    const float kPad = 4.76837158e-7f;
+    const float bxl = __fmaf_rn(-fabsf(bx), kPad, bx), bxh = __fmaf_rn(fabsf(bx), kPad, bx);
+    const float byl = __fmaf_rn(-fabsf(by), kPad, by), byh = __fmaf_rn(fabsf(by), kPad, by);
+    const float bzl = __fmaf_rn(-fabsf(bz), kPad, bz), bzh = __fmaf_rn(fabsf(bz), kPad, bz);
+    // entry planes are the low ones along axes the ray travels up, the high ones otherwise
+    const bool nx = L.r.ix < 0, ny = L.r.iy < 0, nz = L.r.iz < 0;
+    // words: n2 = qlo.x[0] qlo.x[1] qlo.y[0] qlo.y[1]; n3 = qlo.z[0] qlo.z[1] qhi.x[0] qhi.x[1]; n4 = qhi.y[0] qhi.y[1] qhi.z[0] qhi.z[1]
+    uint32_t hitmask = 0;
+#pragma unroll
+    for (int h = 0; h < 2; h++)
+    {
+        const uint32_t meta4 = h ? n1.w : n1.z;
+        const uint32_t isInner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+        const uint32_t innerMask4 = (isInner4 >> 4) * 0xffu;
+        const uint32_t bitIndex4 = (meta4 ^ (L.octinv4 & innerMask4)) & 0x1f1f1f1fu;
+        const uint32_t childBits4 = (meta4 >> 5) & 0x07070707u;
+        const uint32_t lox = h ? n2.y : n2.x, loy = h ? n2.w : n2.z, loz = h ? n3.y : n3.x;
+        const uint32_t hix = h ? n3.w : n3.z, hiy = h ? n4.y : n4.x, hiz = h ? n4.w : n4.z;
+        const uint32_t ex = nx ? hix : lox, fx = nx ? lox : hix;
+        const uint32_t ey = ny ? hiy : loy, fy = ny ? loy : hiy;
+        const uint32_t ez = nz ? hiz : loz, fz = nz ? loz : hiz;
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+        {
+            const float tex = __fmaf_rn(q8(ex, j), adx, bxl), tfx = __fmaf_rn(q8(fx, j), adx, bxh);
+            const float tey = __fmaf_rn(q8(ey, j), ady, byl), tfy = __fmaf_rn(q8(fy, j), ady, byh);
+            const float tez = __fmaf_rn(q8(ez, j), adz, bzl), tfz = __fmaf_rn(q8(fz, j), adz, bzh);
+            const float tEnter = fmaxf(fmaxf(tex, tey), fmaxf(tez, 0.f));
+            const float tExit = fminf(fminf(tfx, tfy), fminf(tfz, L.tmax));
+            if (tEnter <= tExit) hitmask |= ((childBits4 >> (8 * j)) & 0xffu) << ((bitIndex4 >> (8 * j)) & 0xffu);
+        }
+    }
+    L.gx = n1.x;
+    L.gy = (hitmask & 0xff000000u) | (n0.w >> 24);
+    L.tx = n1.y;
+    L.ty = hitmask & 0x00ffffffu;
+    wide_normalise(L, stk, stride);
+}
+
+template <bool ANY>
+__device__ __forceinline__ void lane_tri_step(WideLane &L, const SceneDev &sc, const uint2 *stk, const int stride)
+{
+    const int bit = __ffs((int)L.ty) - 1;
+    L.ty &= L.ty - 1u;
+    const uint32_t i = L.tx + (uint32_t)bit;
+    L.nt++;
+    if (tri_test(sc.tris8, i, L.r, L.best, L.hs, L.ht, L.htp, L.hmat))
+    {
+        L.hitTri = (int)__ldg(&sc.tri8Index[i]);  // back to BVH order, which the shade stage and the reference's `id`s use
+        L.tmax = bound_as_parameter(L.best);
+        if (ANY)
+        {
+            L.found = true;
+            L.gy = L.ty = 0u;
+            L.sp = 0;
+            return;
+        }
+    }
+    wide_normalise(L, stk, stride);
+}
+
+}  // namespace ptc

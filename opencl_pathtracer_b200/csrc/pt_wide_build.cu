@@ -1,0 +1,247 @@
+// pt_wide_build.cu — host side of the FAST-mode wide BVH: collapses the reference BVH2 (the output of BVH_Create,
+// Controleur/PathTracer_BVH.cpp:12-356, handed over in the reference's Node layout) into the 8-wide compressed
+// nodes of pt_wide.cuh. Nothing of the reference is restated here: the BVH2 is only read (child links, leaf ranges);
+// boxes are recomputed from the triangle vertices so that they do not depend on the importer's AABB fields.
+//
+//   1. binary tree with at most 3 triangles per leaf: reference leaves of more triangles are halved in array order;
+//   2. top-down collapse: starting from a node's two children, the inner child with the largest surface area is
+//      replaced by its own two children until 8 children are reached or only leaves are left;
+//   3. children are assigned to the 8 slots so that, for a ray of octant o, visiting slots by decreasing (slot ^ (7-o))
+//      is approximately front to back (greedy assignment on centroid offsets, after Ylitie et al. 2017);
+//   4. child boxes are quantised outwards to 8 bits on the node's grid; inner children get consecutive node indices,
+//      the triangles of leaf children consecutive positions in the wide triangle order.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "pt_wide_build.h"
+
+namespace ptc
+{
+namespace
+{
+struct Box
+{
+    float lo[3], hi[3];
+    void reset() { for (int a = 0; a < 3; a++) { lo[a] = INFINITY; hi[a] = -INFINITY; } }
+    void add(const float *p) { for (int a = 0; a < 3; a++) { lo[a] = std::min(lo[a], p[a]); hi[a] = std::max(hi[a], p[a]); } }
+    void add(const Box &b) { for (int a = 0; a < 3; a++) { lo[a] = std::min(lo[a], b.lo[a]); hi[a] = std::max(hi[a], b.hi[a]); } }
+    double area() const
+    {
+        const double x = (double)hi[0] - lo[0], y = (double)hi[1] - lo[1], z = (double)hi[2] - lo[2];
+        return 2.0 * (x * y + y * z + z * x);
+    }
+};
+
+struct BNode  // binary tree, leaves hold <= 3 triangles of the BVH-ordered array
+{
+    Box box;
+    int left, right;  // -1 for leaves
+    uint32_t first, count;
+};
+
+struct Builder
+{
+    const ptc_scene_view *s;
+    std::vector<BNode> b;
+
+    Box triBox(uint32_t first, uint32_t count) const
+    {
+        Box r;
+        r.reset();
+        for (uint32_t i = first; i < first + count; i++)
+        {
+            const ptc_triangle &t = s->triangulation[i];
+            const float v[3][3] = {{t.S1.x, t.S1.y, t.S1.z}, {t.S2.x, t.S2.y, t.S2.z}, {t.S3.x, t.S3.y, t.S3.z}};
+            for (int k = 0; k < 3; k++) r.add(v[k]);
+        }
+        return r;
+    }
+
+    int makeLeaves(uint32_t first, uint32_t count)
+    {
+        if (count <= 3)
+        {
+            BNode n;
+            n.box = triBox(first, count);
+            n.left = n.right = -1;
+            n.first = first;
+            n.count = count;
+            b.push_back(n);
+            return (int)b.size() - 1;
+        }
+        const uint32_t half = count / 2;
+        const int l = makeLeaves(first, half), r = makeLeaves(first + half, count - half);
+        return join(l, r);
+    }
+
+    int join(int l, int r)
+    {
+        BNode n;
+        n.box = b[l].box;
+        n.box.add(b[r].box);
+        n.left = l;
+        n.right = r;
+        n.first = n.count = 0;
+        b.push_back(n);
+        return (int)b.size() - 1;
+    }
+
+    // reference node -> binary node index, or -1 for a subtree without triangles
+    int convert(uint32_t id)
+    {
+        const ptc_node &n = s->bvh[id];
+        if (n.isLeaf) return n.nbTriangles ? makeLeaves(n.triangleStartIndex, n.nbTriangles) : -1;
+        const int l = convert(n.son1Id), r = convert(n.son2Id);
+        if (l < 0) return r;
+        if (r < 0) return l;
+        return join(l, r);
+    }
+};
+
+// smallest e with 255 * 2^e >= extent, as an IEEE biased exponent byte
+uint32_t gridExponent(double extent)
+{
+    int e = -126;
+    if (extent > 0)
+    {
+        e = (int)std::ceil(std::log2(extent / 255.0));
+        while (std::ldexp(255.0, e) < extent) e++;
+        while (e > -126 && std::ldexp(255.0, e - 1) >= extent) e--;
+    }
+    e = std::max(-126, std::min(127, e));
+    return (uint32_t)(e + 127);
+}
+}  // namespace
+
+bool build_wide_bvh(const ptc_scene_view *s, WideBvh &out, std::string &err)
+{
+    out.nodes.clear();
+    out.triOrder.clear();
+    out.depth = 0;
+    if (s->triangulation_size == 0 || s->bvh_size == 0) return true;
+    Builder B;
+    B.s = s;
+    B.b.reserve((size_t)s->triangulation_size);
+    const int root = B.convert(0);
+    if (root < 0) return true;
+    const std::vector<BNode> &b = B.b;
+    out.triOrder.reserve(s->triangulation_size);
+    out.nodes.reserve(s->triangulation_size / 4 + 16);
+
+    struct Item { int bnode; uint32_t index; uint32_t depth; };
+    std::vector<Item> todo;
+    out.nodes.emplace_back();
+    todo.push_back({root, 0u, 1u});
+    while (!todo.empty())
+    {
+        const Item it = todo.back();
+        todo.pop_back();
+        out.depth = std::max(out.depth, it.depth);
+        // ---- 2. collapse
+        int child[8];
+        int nc = 0;
+        if (b[it.bnode].left < 0) child[nc++] = it.bnode;  // the whole scene is one small leaf
+        else { child[nc++] = b[it.bnode].left; child[nc++] = b[it.bnode].right; }
+        while (nc < 8)
+        {
+            int pick = -1;
+            double bestArea = -1;
+            for (int i = 0; i < nc; i++)
+                if (b[child[i]].left >= 0 && b[child[i]].box.area() > bestArea) { bestArea = b[child[i]].box.area(); pick = i; }
+            if (pick < 0) break;
+            const int c = child[pick];
+            child[pick] = b[c].left;
+            child[nc++] = b[c].right;
+        }
+        Box nb;
+        nb.reset();
+        for (int i = 0; i < nc; i++) nb.add(b[child[i]].box);
+        // ---- 3. slot assignment: slot s should hold the child that a ray of octant s reaches first
+        int slotOf[8], childAt[8];
+        for (int i = 0; i < 8; i++) { slotOf[i] = -1; childAt[i] = -1; }
+        double cost[8][8];
+        for (int i = 0; i < nc; i++)
+            for (int sl = 0; sl < 8; sl++)
+            {
+                double c = 0;
+                for (int a = 0; a < 3; a++)
+                {
+                    const double centre = 0.5 * ((double)b[child[i]].box.lo[a] + b[child[i]].box.hi[a]) - 0.5 * ((double)nb.lo[a] + nb.hi[a]);
+                    const bool negative = (sl >> (2 - a)) & 1;  // octant bit 2 = x, 1 = y, 0 = z (pt_wide.cuh)
+                    c += negative ? -centre : centre;
+                }
+                cost[i][sl] = c;
+            }
+        for (int round = 0; round < nc; round++)
+        {
+            int bi = -1, bs = -1;
+            double bc = INFINITY;
+            for (int i = 0; i < nc; i++)
+            {
+                if (slotOf[i] >= 0) continue;
+                for (int sl = 0; sl < 8; sl++)
+                    if (childAt[sl] < 0 && cost[i][sl] < bc) { bc = cost[i][sl]; bi = i; bs = sl; }
+            }
+            slotOf[bi] = bs;
+            childAt[bs] = bi;
+        }
+        // ---- 4. encode
+        DevNode8 n;
+        std::memset(&n, 0, sizeof(n));
+        n.px = nb.lo[0]; n.py = nb.lo[1]; n.pz = nb.lo[2];
+        uint32_t ebyte[3];
+        double step[3];
+        for (int a = 0; a < 3; a++)
+        {
+            ebyte[a] = gridExponent((double)nb.hi[a] - nb.lo[a]);
+            step[a] = std::ldexp(1.0, (int)ebyte[a] - 127);
+        }
+        uint32_t imask = 0, nInner = 0, nTri = 0;
+        n.childBase = (uint32_t)out.nodes.size();
+        n.triBase = (uint32_t)out.triOrder.size();
+        uint8_t meta[8] = {0, 0, 0, 0, 0, 0, 0, 0}, qlo[3][8], qhi[3][8];
+        std::memset(qlo, 0, sizeof(qlo));
+        std::memset(qhi, 0, sizeof(qhi));
+        for (int sl = 0; sl < 8; sl++)
+        {
+            if (childAt[sl] < 0) continue;
+            const BNode &c = b[child[childAt[sl]]];
+            for (int a = 0; a < 3; a++)
+            {
+                const double l = std::floor(((double)c.box.lo[a] - nb.lo[a]) / step[a]);
+                const double h = std::ceil(((double)c.box.hi[a] - nb.lo[a]) / step[a]);
+                qlo[a][sl] = (uint8_t)std::max(0.0, std::min(255.0, l));
+                qhi[a][sl] = (uint8_t)std::max(0.0, std::min(255.0, h));
+                if (h > 255.0) { err = "wide BVH: quantisation overflow"; return false; }
+            }
+            if (c.left >= 0)
+            {
+                imask |= 1u << sl;
+                meta[sl] = (uint8_t)((1u << 5) | (24u + (uint32_t)sl));
+                nInner++;
+            }
+            else
+            {
+                meta[sl] = (uint8_t)((((1u << c.count) - 1u) << 5) | nTri);
+                for (uint32_t k = 0; k < c.count; k++) out.triOrder.push_back(c.first + k);
+                nTri += c.count;
+            }
+        }
+        n.eimask = ebyte[0] | (ebyte[1] << 8) | (ebyte[2] << 16) | (imask << 24);
+        std::memcpy(n.meta, meta, 8);
+        for (int a = 0; a < 3; a++) { std::memcpy(n.qlo[a], qlo[a], 8); std::memcpy(n.qhi[a], qhi[a], 8); }
+        out.nodes[it.index] = n;
+        // inner children: consecutive nodes in slot order
+        out.nodes.resize(out.nodes.size() + nInner);
+        uint32_t rank = 0;
+        for (int sl = 0; sl < 8; sl++)
+            if (childAt[sl] >= 0 && b[child[childAt[sl]]].left >= 0) todo.push_back({child[childAt[sl]], n.childBase + rank++, it.depth + 1u});
+    }
+    if (out.triOrder.size() >= (1u << 27)) { err = "wide BVH: too many triangles"; return false; }
+    return true;
+}
+
+}  // namespace ptc

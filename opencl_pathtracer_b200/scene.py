@@ -26,6 +26,12 @@ MATERIAL = np.dtype({"names": ["simpleColor", "textureName", "opacity", "texture
                      "formats": [F4, "<u8", "<f4", "<i4", "<i4", "u1", "u1"], "offsets": [0, 16, 24, 28, 32, 36, 37], "itemsize": 48})
 
 
+# csrc/pt_wide.cuh DevNode8
+NODE8 = np.dtype([("p", "<f4", 3), ("e", "u1", 3), ("imask", "u1"), ("childBase", "<u4"), ("triBase", "<u4"), ("meta", "u1", 8),
+                  ("qlo", "u1", (3, 8)), ("qhi", "u1", (3, 8))])
+assert NODE8.itemsize == 80
+
+
 def _as_array(ptr, count, dtype):
     if not ptr or count == 0:
         return np.zeros(0, dtype=dtype)
@@ -80,6 +86,21 @@ class Scene:
     def materials(self):
         i = self.info
         return _as_array(i.materiaux, i.materiauxSize, MATERIAL)
+
+    def wide_bvh(self):
+        """The 8-wide compressed BVH FAST mode traverses (csrc/pt_wide_build.cu): (nodes[n] as NODE8 records,
+        tri_order[nT] wide order -> BVH order, depth)."""
+        lib = N.cuda_lib()
+        w = N.WideBvh()
+        v = self.view()
+        if lib.ptc_wide_bvh_build(C.byref(v), C.byref(w)) != N.PTC_OK:
+            raise RuntimeError(lib.ptc_last_error(None).decode())
+        try:
+            nodes = _as_array(w.nodes, w.n_nodes, NODE8).copy()
+            order = _as_array(w.tri_order, w.n_triangles, np.dtype("<u4")).copy()
+            return nodes, order, int(w.depth)
+        finally:
+            lib.ptc_wide_bvh_free(C.byref(w))
 
     def camera(self):
         return np.array(self.info.camera, dtype=np.float32)

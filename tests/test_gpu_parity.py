@@ -113,22 +113,54 @@ def test_iteration_ranges_compose(scene_factory):
     assert np.array_equal(a.view(np.uint32), b.view(np.uint32)) and np.array_equal(na, nb)
 
 
-def test_fast_mode_matches_parity(ptref, scene_factory):
-    """FAST = same arithmetic, correct distance culling, unlit shadow rays skipped: identical hits, same image."""
+@pytest.mark.parametrize("flags,label", [(pt.FLAG_BVH2, "BVH2"), (0, "wide BVH8")])
+def test_fast_mode_matches_parity(ptref, scene_factory, flags, label):
+    """FAST = the reference's triangle arithmetic, correct distance culling, unlit shadow rays skipped; on the reference
+    BVH2 (FLAG_BVH2) or on the 8-wide compressed BVH it is collapsed into (default): same hits, same image."""
     w, h = 160, 120
     sc = scene_factory("gallery", w, h, True)
-    with pt.PathTracerCUDA(w, h, mode=pt.MODE_PARITY) as p, pt.PathTracerCUDA(w, h, mode=pt.MODE_FAST) as f:
+    with pt.PathTracerCUDA(w, h, mode=pt.MODE_PARITY) as p, pt.PathTracerCUDA(w, h, mode=pt.MODE_FAST, flags=flags) as f:
         p.upload(sc)
         f.upload(sc)
         hp, hf = p.trace_primary(1), f.trace_primary(1)
         mism = (hp["hit"] != hf["hit"]).mean()
-        print("primary hit mismatch fraction FAST vs PARITY: %g" % mism)
+        print("primary hit mismatch fraction FAST (%s) vs PARITY: %g" % (label, mism))
         assert mism <= 1e-4
-        assert (hf["counts"][:, 0] <= hp["counts"][:, 0]).all(), "FAST must never test more boxes than PARITY"
-        assert hf["counts"][:, 0].sum() < hp["counts"][:, 0].sum()
+        same = hp["hit"] == hf["hit"]
+        assert np.array_equal(hp["st"][same].view(np.uint32), hf["st"][same].view(np.uint32)), "same hit => same (s, t) bits"
+        assert np.array_equal(hp["dist2"][same].view(np.uint32), hf["dist2"][same].view(np.uint32))
+        if flags & pt.FLAG_BVH2:
+            assert (hf["counts"][:, 0] <= hp["counts"][:, 0]).all(), "FAST on the BVH2 must never test more boxes than PARITY"
+            assert hf["counts"][:, 0].sum() < hp["counts"][:, 0].sum()
+        else:
+            assert hf["counts"][:, 0].sum() / 8 < hp["counts"][:, 0].sum() / 2, "fewer node visits on the wide BVH"
         rp, rf = p.render_single(2), f.render_single(2)
         bad = _rel_mismatch(rf, rp).mean()
-        print("1-spp radiance mismatch fraction FAST vs PARITY: %g" % bad)
+        print("1-spp radiance mismatch fraction FAST (%s) vs PARITY: %g" % (label, bad))
+        assert bad <= 2e-3
+
+
+@pytest.mark.parametrize("name", ["cornell_specular", "atrium:4"])
+def test_wide_bvh_hits_equal_bvh2_hits(scene_factory, name):
+    """Closest hits through the wide BVH against FAST on the reference BVH2, every pixel of three iterations, plus the
+    accumulated image of 4 spp (any-hit shadow rays included)."""
+    w, h = 320, 200
+    sc = scene_factory(name, w, h, False)
+    with pt.PathTracerCUDA(w, h, mode=pt.MODE_FAST, flags=pt.FLAG_BVH2) as a, pt.PathTracerCUDA(w, h, mode=pt.MODE_FAST) as b:
+        a.upload(sc)
+        b.upload(sc)
+        for it in (0, 5, 17):
+            ha, hb = a.trace_primary(it), b.trace_primary(it)
+            mism = (ha["hit"] != hb["hit"]).mean()
+            print("%s iteration %d: primary hit mismatch fraction wide vs BVH2: %g" % (name, it, mism))
+            assert mism <= 1e-4
+        a.render(0, 4)
+        b.render(0, 4)
+        ca, na = a.read_image()
+        cb, nb = b.read_image()
+        assert np.array_equal(na, nb)
+        bad = _rel_mismatch(cb, ca).mean()
+        print("%s 4-spp image mismatch fraction wide vs BVH2: %g" % (name, bad))
         assert bad <= 2e-3
 
 

@@ -1,0 +1,146 @@
+"""CPU checks of the FAST-mode 8-wide compressed BVH (csrc/pt_wide_build.cu, decoded as csrc/pt_wide.cuh does):
+structure, conservative boxes, and a scalar restatement of the traversal against brute force."""
+import numpy as np
+import pytest
+
+
+def _decode(nodes, i):
+    n = nodes[i]
+    step = np.ldexp(1.0, n["e"].astype(np.int64) - 127)  # per axis
+    lo = n["p"].astype(np.float64)[:, None] + n["qlo"].astype(np.float64) * step[:, None]
+    hi = n["p"].astype(np.float64)[:, None] + n["qhi"].astype(np.float64) * step[:, None]
+    return n, lo, hi  # lo/hi: [axis, slot]
+
+
+def _children(n):
+    """(slot, kind, first, count): inner -> node index, leaf -> wide-order triangle range."""
+    out = []
+    for s in range(8):
+        m = int(n["meta"][s])
+        if m == 0:
+            continue
+        if (m & 0x18) == 0x18 and (m >> 5) == 1:
+            assert (m & 0x1f) == 24 + s and (int(n["imask"]) >> s) & 1
+            rel = bin(int(n["imask"]) & ((1 << s) - 1)).count("1")
+            out.append((s, "inner", int(n["childBase"]) + rel, 1))
+        else:
+            bits = m >> 5
+            assert bits in (1, 3, 7) and not (int(n["imask"]) >> s) & 1
+            out.append((s, "leaf", int(n["triBase"]) + (m & 0x1f), bin(bits).count("1")))
+    return out
+
+
+@pytest.mark.parametrize("name", ["cornell", "gallery", "atrium:8"])
+def test_wide_bvh_structure_and_boxes(scene_factory, name):
+    sc = scene_factory(name, 64, 48, load_sky=(name == "gallery"))
+    nodes, order, depth = sc.wide_bvh()
+    tris = sc.triangles()
+    nT = len(tris)
+    assert sorted(order.tolist()) == list(range(nT)), "every triangle exactly once"
+    verts = np.stack([np.stack([tris[k][a] for a in "xyz"], -1) for k in ("S1", "S2", "S3")], 1).astype(np.float64)  # [tri, vertex, axis]
+    seen_nodes, seen_tris, max_depth = set(), 0, 0
+
+    def walk(i, d):
+        """returns the exact bounds of the subtree and checks every child box contains its subtree"""
+        nonlocal seen_tris, max_depth
+        assert i not in seen_nodes
+        seen_nodes.add(i)
+        max_depth = max(max_depth, d)
+        n, lo, hi = _decode(nodes, i)
+        blo, bhi = np.full(3, np.inf), np.full(3, -np.inf)
+        for s, kind, first, count in _children(n):
+            if kind == "inner":
+                clo, chi = walk(first, d + 1)
+            else:
+                v = verts[order[first:first + count]].reshape(-1, 3)
+                clo, chi = v.min(0), v.max(0)
+                seen_tris += count
+            assert (lo[:, s] <= clo).all() and (hi[:, s] >= chi).all(), "quantised box must contain the child"
+            # and not be looser than one grid step per side
+            step = np.ldexp(1.0, n["e"].astype(np.int64) - 127)
+            assert (clo - lo[:, s] < step * 1.0001).all() and (hi[:, s] - chi < step * 1.0001).all()
+            blo, bhi = np.minimum(blo, clo), np.maximum(bhi, chi)
+        assert (n["p"].astype(np.float64) <= blo).all()
+        return blo, bhi
+
+    walk(0, 1)
+    assert len(seen_nodes) == len(nodes) and seen_tris == nT and max_depth == depth
+
+
+def _tri_hit(o, d, v):
+    e1, e2 = v[1] - v[0], v[2] - v[0]
+    p = np.cross(d, e2)
+    det = e1 @ p
+    if abs(det) < 1e-14:
+        return None
+    t0 = o - v[0]
+    u = (t0 @ p) / det
+    q = np.cross(t0, e1)
+    w = (d @ q) / det
+    t = (e2 @ q) / det
+    if u < -1e-9 or w < -1e-9 or u + w > 1 + 1e-9 or t <= 1e-6:
+        return None
+    return t
+
+
+def test_wide_bvh_traversal_matches_brute_force(scene_factory):
+    """The traversal of pt_wide.cuh restated in scalar Python (same decode rules: octant ordering, hit masks,
+    relative child indices, triangle groups) finds the brute-force closest hit."""
+    sc = scene_factory("atrium:8", 64, 48)
+    nodes, order, _ = sc.wide_bvh()
+    tris = sc.triangles()
+    verts = np.stack([np.stack([tris[k][a] for a in "xyz"], -1) for k in ("S1", "S2", "S3")], 1).astype(np.float64)
+    rng = np.random.default_rng(7)
+    lo, hi = verts.reshape(-1, 3).min(0), verts.reshape(-1, 3).max(0)
+    visited_total = 0
+    for _ in range(120):
+        o = lo + (hi - lo) * rng.uniform(0.2, 0.8, 3)
+        d = rng.normal(size=3)
+        d /= np.linalg.norm(d)
+        # brute force
+        best, best_t = -1, np.inf
+        for i in range(len(verts)):
+            t = _tri_hit(o, d, verts[i])
+            if t is not None and t < best_t:
+                best, best_t = i, t
+        # wide traversal
+        inv = 1.0 / np.where(np.abs(d) < 1e-30, 1e-30, d)
+        octinv = 7 - ((4 if d[0] < 0 else 0) | (2 if d[1] < 0 else 0) | (1 if d[2] < 0 else 0))
+        stack, g = [], (0, 0x80000000)
+        hit, tmax = -1, np.inf
+        while True:
+            if g[1] > 0x00ffffff:
+                bit = g[1].bit_length() - 1
+                slot = (bit - 24) ^ octinv
+                rest = g[1] & ~(1 << bit)
+                rel = bin(g[1] & 0xff & ((1 << slot) - 1)).count("1")
+                if rest > 0x00ffffff:
+                    stack.append((g[0], rest))
+                n, blo, bhi = _decode(nodes, g[0] + rel)
+                visited_total += 1
+                hitmask = 0
+                for s in range(8):
+                    m = int(n["meta"][s])
+                    if m == 0:
+                        continue
+                    t1, t2 = (blo[:, s] - o) * inv, (bhi[:, s] - o) * inv
+                    tn, tf = max(np.minimum(t1, t2).max(), 0.0), min(np.maximum(t1, t2).min(), tmax)
+                    if tn <= tf:
+                        inner = (m & 0x18) == 0x18
+                        idx = ((m ^ (octinv if inner else 0)) & 0x1f)
+                        hitmask |= (m >> 5) << idx
+                g = (int(n["childBase"]), (hitmask & 0xff000000) | int(n["imask"]))
+                tg = [int(n["triBase"]), hitmask & 0x00ffffff]
+                while tg[1]:
+                    b = (tg[1] & -tg[1]).bit_length() - 1
+                    tg[1] &= tg[1] - 1
+                    k = int(order[tg[0] + b])
+                    t = _tri_hit(o, d, verts[k])
+                    if t is not None and t < tmax:
+                        hit, tmax = k, t
+            elif stack:
+                g = stack.pop()
+            else:
+                break
+        assert hit == best or (best >= 0 and hit >= 0 and abs(tmax - best_t) < 1e-9 * max(1.0, best_t)), (hit, best, tmax, best_t)
+    assert visited_total > 0
