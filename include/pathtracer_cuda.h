@@ -191,6 +191,13 @@ PTC_API int ptc_get_device_buffers(ptc_ctx *ctx, ptc_device_buffers *out);
 PTC_API int ptc_trace_primary(ptc_ctx *ctx, uint32_t iteration, int32_t *hit, float *st, float *dist2, float *dir,
                               int32_t *seed_after, uint32_t *counts);
 
+/* Parity probe: closest hits of n caller-supplied rays (origin, direction: 4 floats per ray; the direction is normalised
+ * over its four lanes as Ray3D_Create does, reference Kernel/PathTracer_FullKernel_header.cl:286-305) through the extend
+ * stage = BVH_IntersectRay (Kernel/PathTracer_FullKernel.cl:620-702). Outputs as ptc_trace_primary; any may be NULL.
+ * n must not exceed the context's path slots (image pixels x iterations_per_batch). Does not touch the accumulators. */
+PTC_API int ptc_trace_rays(ptc_ctx *ctx, uint32_t n, const float *origin, const float *direction, int32_t *hit, float *st,
+                           float *dist2, float *dir, uint32_t *counts);
+
 /* Parity probe: per-pixel radiance of exactly one iteration (what Kernel_Main adds to imageColor). */
 PTC_API int ptc_render_single(ptc_ctx *ctx, uint32_t iteration, float *radiance);
 

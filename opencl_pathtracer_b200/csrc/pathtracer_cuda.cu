@@ -815,6 +815,47 @@ int ptc_trace_primary(ptc_ctx *ctx, uint32_t iteration, int32_t *hit, float *st,
     return PTC_OK;
 }
 
+int ptc_trace_rays(ptc_ctx *ctx, uint32_t n, const float *origin, const float *direction, int32_t *hit, float *st, float *dist2,
+                   float *dir, uint32_t *counts)
+{
+    if (!ctx || !origin || !direction) return PTC_ERR_INVALID;
+    if (!ctx->sceneLoaded) return fail(ctx, PTC_ERR_STATE, "ptc_trace_rays before ptc_upload_scene");
+    if (n == 0) return PTC_OK;
+    if ((size_t)n > ctx->capacity) return fail(ctx, PTC_ERR_LIMIT, "ptc_trace_rays: %u rays, the context holds %zu path slots", n, ctx->capacity);
+    CK(cudaSetDevice(ctx->device));
+    DevBuf<float4> dOrg, dDirIn, dDir;
+    DevBuf<int32_t> dHit;
+    DevBuf<float2> dSt;
+    DevBuf<float> dD2;
+    DevBuf<uint2> dCnt;
+    CK(dOrg.alloc(n)); CK(dDirIn.alloc(n));
+    if (hit) CK(dHit.alloc(n));
+    if (st) CK(dSt.alloc(n));
+    if (dist2) CK(dD2.alloc(n));
+    if (dir) CK(dDir.alloc(n));
+    if (counts) CK(dCnt.alloc(n));
+    CK(cudaMemcpyAsync(dOrg.p, origin, sizeof(float4) * n, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(dDirIn.p, direction, sizeof(float4) * n, cudaMemcpyHostToDevice, ctx->stream));
+    FrameParams fp{};
+    fp.width = n; fp.height = 1; fp.maxDepth = ctx->cfg.ray_max_depth; fp.nIterations = 1;
+    launch_reset(ctx->stream, ctx->counters.p, n);
+    launch_probe_rays(ctx->stream, n, dOrg.p, dDirIn.p, ctx->st);
+    launch_extend(ctx->stream, ctx->lc, ctx->fast, ctx->sc, ctx->st, nullptr, ctx->counters.p, 0);
+    launch_probe_primary(ctx->stream, fp, ctx->st, dHit.p, dSt.p, dD2.p, dDir.p, nullptr, dCnt.p);
+    ctx->launches += 4;
+    int rc = PTC_OK;
+    if (rc == PTC_OK && hit) rc = readBack(ctx, hit, dHit.p, sizeof(int32_t) * n);
+    if (rc == PTC_OK && st) rc = readBack(ctx, st, dSt.p, sizeof(float2) * n);
+    if (rc == PTC_OK && dist2) rc = readBack(ctx, dist2, dD2.p, sizeof(float) * n);
+    if (rc == PTC_OK && dir) rc = readBack(ctx, dir, dDir.p, sizeof(float4) * n);
+    if (rc == PTC_OK && counts) rc = readBack(ctx, counts, dCnt.p, sizeof(uint2) * n);
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    dOrg.release(); dDirIn.release(); dHit.release(); dSt.release(); dD2.release(); dDir.release(); dCnt.release();
+    if (rc != PTC_OK) return rc;
+    if (e != cudaSuccess) return fail(ctx, PTC_ERR_CUDA, "ptc_trace_rays: %s", cudaGetErrorString(e));
+    return PTC_OK;
+}
+
 int ptc_render_single(ptc_ctx *ctx, uint32_t iteration, float *radiance)
 {
     if (!ctx || !radiance) return PTC_ERR_INVALID;

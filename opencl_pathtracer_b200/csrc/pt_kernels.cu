@@ -210,7 +210,16 @@ __global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas) k_trace(Sce
                         {
                             const float4 h = st.hit[pp], po = st.org[pp], pd = st.dir[pp];
                             const float4 q = f4(po.x + pd.x * h.w, po.y + pd.y * h.w, po.z + pd.z * h.w, po.w + pd.w * h.w);  // :538
-                            shadow_setup(sc.lights[l], q, d, bound);
+                            const DevLight light = sc.lights[l];
+                            if (FAST)
+                            {
+                                // a light that sends exactly zero power towards the shading normal (:403-421: behind the surface,
+                                // outside a spot cone) adds +-0 to the pixel whether it is occluded or not: no ray
+                                const int tri = __float_as_int(h.x);
+                                const float4 Ns = shading_normal(&sc.shade[tri], __ldg(&sc.tris[tri].n), pd, h.y, h.z);
+                                valid = !(light_power_toward(light, q, Ns) == 0.0f);
+                            }
+                            shadow_setup(light, q, d, bound);
                             o = q;
                         }
                     }
@@ -330,11 +339,7 @@ __global__ void __launch_bounds__(kStreamThreads) k_shade(SceneDev sc, FramePara
                 // :1267-1274 normals
                 const bool same = dot4(d, N) > 0;
                 const float4 Ng = same ? -N : N;
-                const float4 n1 = __ldg(&sh->n1), n2 = __ldg(&sh->n2), n3 = __ldg(&sh->n3);
-                float4 Ns = normalize4((n2 * s) + (n3 * t) + (n1 * (1 - s - t)));
-                if (same) Ns = -Ns;
-                put_in_same_hemisphere(Ns, -d);
-                Ns = normalize4(Ns);
+                const float4 Ns = shading_normal(sh, N, d, s, t);
                 // :901-954 direct illumination from the occlusion bits the connect stage left
                 float4 L = f4(0, 0, 0, 0);
                 const uint32_t occl = st.occl[p] & kOcclMask;
@@ -530,6 +535,21 @@ __global__ void k_probe_primary(FrameParams fp, PathState st, int32_t *hit, floa
     }
 }
 
+// ray probe: caller-supplied rays take the place of k_generate's camera rays (Ray3D_Create header.cl:286-305 normalises)
+__global__ void k_probe_rays(uint32_t n, const float4 *origin, const float4 *direction, PathState st)
+{
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x)
+    {
+        st.org[k] = origin[k];
+        st.dir[k] = normalize4(direction[k]);
+        st.seed[k] = 1;
+        st.meta[k] = 0;
+        st.nbbx[k] = 0;
+        st.ntri[k] = 0;
+        st.occl[k] = 0;
+    }
+}
+
 // reference Alone/PathTracer_bitmap.cpp:259-279 (its test reads .x three times; a negative red marks the pixel)
 __global__ void k_rgb8(ImageDev img, uint32_t nPixels, uint8_t *rgb)
 {
@@ -633,6 +653,11 @@ void launch_probe_primary(cudaStream_t s, const FrameParams &fp, const PathState
                           float4 *dir, int32_t *seedAfter, uint2 *counts)
 {
     k_probe_primary<<<1024, 256, 0, s>>>(fp, st, hit, stOut, dist2, dir, seedAfter, counts);
+}
+
+void launch_probe_rays(cudaStream_t s, uint32_t n, const float4 *origin, const float4 *direction, const PathState &st)
+{
+    k_probe_rays<<<1024, 256, 0, s>>>(n, origin, direction, st);
 }
 
 void launch_rgb8(cudaStream_t s, const ImageDev &img, uint32_t nPixels, uint8_t *rgb) { k_rgb8<<<1024, 256, 0, s>>>(img, nPixels, rgb); }

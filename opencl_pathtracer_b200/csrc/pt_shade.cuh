@@ -153,6 +153,18 @@ __device__ __forceinline__ float4 cosine_sample_hemisphere(int &seed, float4 N)
     return normalize4(f4(dot4(f4(sn.x, tn.x, N.x, 0), v), dot4(f4(sn.y, tn.y, N.y, 0), v), dot4(f4(sn.z, tn.z, N.z, 0), v), 0));
 }
 
+// Shading normal of a hit (:1267-1274): interpolated vertex normals, turned towards the incoming ray. One function for the
+// shade stage and for the light cull of the connect stage, so both see the same bits.
+__device__ __forceinline__ float4 shading_normal(const DevShade *sh, float4 N, float4 d, float s, float t)
+{
+    const bool same = dot4(d, N) > 0;
+    const float4 n1 = __ldg(&sh->n1), n2 = __ldg(&sh->n2), n3 = __ldg(&sh->n3);
+    float4 Ns = normalize4((n2 * s) + (n3 * t) + (n1 * (1 - s - t)));
+    if (same) Ns = -Ns;
+    put_in_same_hemisphere(Ns, -d);
+    return normalize4(Ns);
+}
+
 // Shadow ray of one light from the hit point q (:932-938): direction = normalize(full), bound =
 // length(full) (INFINITY for a directional light) — a LENGTH handed to a parameter that the triangle
 // test compares with squared distances (F9b), reproduced as is in both modes.

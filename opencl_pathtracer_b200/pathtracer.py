@@ -112,6 +112,18 @@ class PathTracerCUDA:
                                              out["dir"].ctypes.data, out["seed_after"].ctypes.data, out["counts"].ctypes.data))
         return out
 
+    def trace_rays(self, origin, direction):
+        """Closest hits of arbitrary rays (float32 [n, 4] each) through the extend stage."""
+        o = np.ascontiguousarray(origin, np.float32)
+        d = np.ascontiguousarray(direction, np.float32)
+        n = len(o)
+        assert o.shape == (n, 4) and d.shape == (n, 4)
+        out = {"hit": np.empty(n, np.int32), "st": np.empty((n, 2), np.float32), "dist2": np.empty(n, np.float32),
+               "dir": np.empty((n, 4), np.float32), "counts": np.empty((n, 2), np.uint32)}
+        self._ck(self._lib.ptc_trace_rays(self._h, n, o.ctypes.data, d.ctypes.data, out["hit"].ctypes.data, out["st"].ctypes.data,
+                                          out["dist2"].ctypes.data, out["dir"].ctypes.data, out["counts"].ctypes.data))
+        return out
+
     def render_single(self, iteration):
         r = np.empty((self.height, self.width, 4), dtype=np.float32)
         self._ck(self._lib.ptc_render_single(self._h, iteration, r.ctypes.data))

@@ -40,6 +40,7 @@ def lib():
         L.ptref_render.argtypes = [C.POINTER(RefScene), u32, u32, u32, C.c_int, u32, u32, vp, vp, vp, vp, vp, vp, C.c_int]
         L.ptref_render_rows.argtypes = [C.POINTER(RefScene), u32, u32, u32, C.c_int, u32, u32, u32, u32, vp, vp, vp, vp, vp, vp, C.c_int]
         L.ptref_primary.argtypes = [C.POINTER(RefScene), u32, u32, C.c_int, u32, vp, vp, vp, vp, vp, vp]
+        L.ptref_trace_rays.argtypes = [C.POINTER(RefScene), u32, vp, vp, vp, vp, vp, vp, vp]
         L.ptref_rng.argtypes = [u32, u32, u32, u32, u32, C.c_int, vp, vp, vp]
         L.ptref_cosine_sample.argtypes = [C.c_int32, vp, vp, vp]
         _lib = L
@@ -98,6 +99,20 @@ def primary(scene, W, H, sampler=0, iteration=0):
     rs = ref_scene(scene)
     rc = lib().ptref_primary(C.byref(rs), W, H, sampler, iteration, out["hit"].ctypes.data, out["st"].ctypes.data,
                              out["dist2"].ctypes.data, out["dir"].ctypes.data, out["seed_after"].ctypes.data, out["counts"].ctypes.data)
+    assert rc == 0
+    return out
+
+
+def trace_rays(scene, origin, direction):
+    """Closest hits of arbitrary rays (origin, direction: float32 [n, 4]; the direction is normalised by Ray3D_Create)."""
+    o = np.ascontiguousarray(origin, np.float32)
+    d = np.ascontiguousarray(direction, np.float32)
+    n = len(o)
+    out = {"hit": np.empty(n, np.int32), "st": np.empty((n, 2), np.float32), "dist2": np.empty(n, np.float32),
+           "dir": np.empty((n, 4), np.float32), "counts": np.empty((n, 2), np.uint32)}
+    rs = ref_scene(scene)
+    rc = lib().ptref_trace_rays(C.byref(rs), n, o.ctypes.data, d.ctypes.data, out["hit"].ctypes.data, out["st"].ctypes.data,
+                                out["dist2"].ctypes.data, out["dir"].ctypes.data, out["counts"].ctypes.data)
     assert rc == 0
     return out
 

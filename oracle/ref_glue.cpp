@@ -254,6 +254,41 @@ int ptref_primary(const ptref_scene *s, uint32_t W, uint32_t H, int sampler, uin
     return 0;
 }
 
+// Ray probe: Ray3D_Create (header.cl:286-305, which normalises the direction) + one BVH_IntersectRay call (:620-702) for
+// arbitrary rays, so that traversal parity can be checked on rays that start on surfaces (the bounces), not only on
+// camera rays. Per ray: hit = BVH-order triangle index or -1; st; dist2 as Triangle_Intersects forms it; dirOut = the
+// normalised direction the traversal used; counts = (numIntersectedBBx, numIntersectedTri).
+int ptref_trace_rays(const ptref_scene *s, uint32_t n, const float *origin, const float *direction, int32_t *hit, float *st,
+                     float *dist2, float *dirOut, uint32_t *counts)
+{
+    namespace K = refk_jittered;
+    set_options(64, 64, 10, s->lightsSize);
+#pragma omp parallel for schedule(dynamic, 64)
+    for (int64_t p = 0; p < (int64_t)n; p++)
+    {
+        ocl_shim::gid[0] = 0;
+        ocl_shim::gid[1] = 0;
+        float4 o, d;
+        memcpy(&o, origin + 4 * p, 16);
+        memcpy(&d, direction + 4 * p, 16);
+        K::Ray3D r;
+        int seedValue = 1;
+        K::Ray3D_Create(&r, &o, &d, false);
+        bool h = K::BVH_IntersectRay(&seedValue, (const K::Node *)s->bvh, (const K::Triangle *)s->triangulation,
+                                     (const K::Light *)s->lights, (const K::Material *)s->materiaux, (const K::Texture *)s->textures,
+                                     (const uchar4 *)s->texturesData, (const K::Sky *)s->sky, &r);
+        hit[p] = h ? (int32_t)r.intersectedTriangleId : -1;
+        st[2 * p] = h ? r.s : 0.f;
+        st[2 * p + 1] = h ? r.t : 0.f;
+        float4 fr = r.intersectionPoint - r.origin;
+        dist2[p] = h ? K::dot(fr, fr) : INFINITY;
+        memcpy(dirOut + 4 * p, &r.direction, 16);
+        counts[2 * p] = r.numIntersectedBBx;
+        counts[2 * p + 1] = r.numIntersectedTri;
+    }
+    return 0;
+}
+
 // RNG known-answer helper: InitializeRandomSeed (header.cl:255-264) then n draws of random() (:246-253).
 int ptref_rng(uint32_t x, uint32_t y, uint32_t it, uint32_t W, uint32_t H, int n, int32_t *seed0, int32_t *seeds,
               float *us)
