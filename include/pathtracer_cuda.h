@@ -80,7 +80,7 @@ typedef struct ptc_config
     uint32_t ray_max_depth;        /* MAX_REFLECTION_NUMBER */
     uint32_t sampler;              /* ptc_sampler */
     uint32_t mode;                 /* ptc_mode */
-    uint32_t iterations_per_batch; /* samples per pixel kept in flight per wavefront pass; 0 = auto */
+    uint32_t iterations_per_batch; /* samples per pixel kept in flight per wavefront pass; 0 = auto (>= 16M paths, 112 B each) */
     uint32_t flags;                /* PTC_FLAG_* */
     uint32_t reserved;
     void *stream;                  /* cudaStream_t to launch on; NULL = the library creates its own */

@@ -274,9 +274,11 @@ int ptc_create(const ptc_config *config, ptc_ctx **out_ctx)
         }
         c->ownStream = true;
     }
-    // iterations kept in flight per wavefront pass: auto = enough for >= 2M paths
+    // iterations kept in flight per wavefront pass: auto = enough for >= 16M paths (1.9 GB of path state). Measured on the
+    // bench scene at 1080p: 1 / 2 / 4 / 8 / 16 iterations per pass = 117 / 124 / 128 / 130 / 131 Msamples/s (the tail of every
+    // persistent launch is amortised over more rays; profiles/r01_sweeps.txt)
     uint32_t b = config->iterations_per_batch;
-    if (b == 0) b = ((1u << 21) + c->nPix - 1) / c->nPix;
+    if (b == 0) b = ((1u << 24) + c->nPix - 1) / c->nPix;
     if (b > 64) b = 64;
     while ((uint64_t)b * c->nPix >= (1ull << 27) && b > 1) b--;  // staged items carry the path slot in 27 bits
     c->batchIters = b;
