@@ -203,8 +203,9 @@ PTC_API int ptc_render_single(ptc_ctx *ctx, uint32_t iteration, float *radiance)
 
 /* Host utility: the 8-wide compressed BVH that ptc_upload_scene collapses the reference BVH2 into in FAST mode
  * (opencl_pathtracer_b200/csrc/pt_wide_build.cu), exposed for inspection and structural tests. nodes = n_nodes records of
- * 80 bytes (DevNode8, csrc/pt_wide.cuh); tri_order[i] = index in the BVH-ordered triangulation of the i-th triangle
- * in wide order; depth = levels of wide nodes. Needs no CUDA device. Release with ptc_wide_bvh_free. */
+ * 80 bytes (DevNode8, csrc/pt_wide.cuh); tri_order has n_triangles = 24 * n_nodes entries: entry 24 * node + 3 * slot + k =
+ * index in the BVH-ordered triangulation of triangle k of the leaf child in `slot`, 0xffffffff where there is none;
+ * depth = levels of wide nodes. Needs no CUDA device. Release with ptc_wide_bvh_free. */
 typedef struct ptc_wide_bvh
 {
     void *nodes;

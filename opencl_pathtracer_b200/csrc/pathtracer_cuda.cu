@@ -497,7 +497,11 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
         if (wideBvh.depth + 1 > 64u) return fail(ctx, PTC_ERR_LIMIT, "wide BVH of %u levels", wideBvh.depth);
         hTris8.resize(wideBvh.triOrder.size());
 #pragma omp parallel for schedule(static)
-        for (long long i = 0; i < (long long)hTris8.size(); i++) hTris8[i] = hTris[wideBvh.triOrder[i]];
+        for (long long i = 0; i < (long long)hTris8.size(); i++)
+        {
+            if (wideBvh.triOrder[i] != kNoTriangle) hTris8[i] = hTris[wideBvh.triOrder[i]];
+            else std::memset(&hTris8[i], 0, sizeof(DevTri));  // never fetched (no bit in DevNode8::valid)
+        }
     }
 
     // ---- upload (pending renders use the old buffers: wait for them first)

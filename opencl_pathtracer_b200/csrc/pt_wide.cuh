@@ -7,22 +7,26 @@
 // ray octant, so the closest hit is the one PARITY finds except between candidates at exactly the same distance.
 //
 // Node layout (80 bytes, after Ylitie, Karras, Laine: "Efficient Incoherent Ray Traversal on GPUs Through Compressed
-// Wide BVHs", HPG 2017): child boxes are 8-bit offsets on a per-node grid p + q * 2^e; inner children are stored
-// consecutively from childBase, the triangles of leaf children consecutively from triBase (at most 3 per child slot);
-// meta[i] = 0 (empty slot), (0b001 << 5) | (24 + i) (inner child in slot i) or (unary count << 5) | offset (leaf).
+// Wide BVHs", HPG 2017): child boxes are 8-bit offsets on a per-node grid p + q * 2^e; inner children (imask) are stored
+// consecutively from childBase. Unlike the paper there is no per-child meta byte: a leaf child holds at most 3 triangles
+// and triangle k of slot s of node i is record 24 * i + 3 * s + k of a sparse triangle array (bit 3 * s + k of `valid`),
+// so the 24-bit triangle hit mask is a bit spread of the 8 slot results and needs no per-child shifts.
 #pragma once
 
 #include "pt_traverse.cuh"
 
 namespace ptc
 {
+constexpr uint32_t kTriSlots = 24;               // triangle records reserved per wide node
+constexpr uint32_t kNoTriangle = 0xffffffffu;    // unused record of the wide triangle order
+
 struct __align__(16) DevNode8
 {
     float px, py, pz;       // grid origin = lower corner of the node
     uint32_t eimask;        // bytes 0..2: IEEE biased exponents of the grid step per axis; byte 3: mask of inner children
     uint32_t childBase;     // index of the first inner child
-    uint32_t triBase;       // index (wide order) of the first triangle of the leaf children
-    uint32_t meta[2];       // 8 x 8 bit
+    uint32_t valid;         // bit 3 * slot + k: the leaf child in `slot` has a triangle k
+    uint32_t spare[2];
     uint32_t qlo[3][2];     // 8 x 8 bit per axis
     uint32_t qhi[3][2];
 };
@@ -34,7 +38,7 @@ struct WideLane
     float best;        // squared distance bound, the reference's `squaredDistance`
     float tmax;        // the same bound as a ray parameter, padded
     uint32_t gx, gy;   // node group: first child index | bits 31..24 children still to visit (front to back), bits 7..0 imask
-    uint32_t tx, ty;   // triangle group: first triangle | 24 bits of triangles still to test
+    uint32_t tx, ty;   // triangle group: first record (24 * node) | 24 bits of triangles still to test
     uint32_t octinv4;  // (7 - ray octant) in every byte
     int sp;            // stack entries, -1 = no ray
     int hitTri;
@@ -108,7 +112,8 @@ __device__ __forceinline__ void lane_node_step(WideLane &L, const SceneDev &sc, 
     const uint32_t slot = (uint32_t)(bit - 24) ^ (L.octinv4 & 7u);
     const uint32_t rest = hits & ~(1u << bit);
     const uint32_t rel = (uint32_t)__popc(hits & 0xffu & ((1u << slot) - 1u));
-    const uint4 *np = reinterpret_cast<const uint4 *>(sc.nodes8 + (L.gx + rel));
+    const uint32_t node = L.gx + rel;
+    const uint4 *np = reinterpret_cast<const uint4 *>(sc.nodes8 + node);
     const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
     if (rest > 0x00ffffffu) stk[L.sp * stride] = make_uint2(L.gx, rest);
     L.sp += rest > 0x00ffffffu ? 1 : 0;
@@ -128,15 +133,10 @@ __device__ __forceinline__ void lane_node_step(WideLane &L, const SceneDev &sc, 
     // entry planes are the low ones along axes the ray travels up, the high ones otherwise
     const bool nx = L.r.ix < 0, ny = L.r.iy < 0, nz = L.r.iz < 0;
     // words: n2 = qlo.x[0] qlo.x[1] qlo.y[0] qlo.y[1]; n3 = qlo.z[0] qlo.z[1] qhi.x[0] qhi.x[1]; n4 = qhi.y[0] qhi.y[1] qhi.z[0] qhi.z[1]
-    uint32_t hitmask = 0;
+    uint32_t slotHit = 0;  // bit s: the box in slot s is hit (empty slots may "hit": imask and valid drop them)
 #pragma unroll
     for (int h = 0; h < 2; h++)
     {
-        const uint32_t meta4 = h ? n1.w : n1.z;
-        const uint32_t isInner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-        const uint32_t innerMask4 = (isInner4 >> 4) * 0xffu;
-        const uint32_t bitIndex4 = (meta4 ^ (L.octinv4 & innerMask4)) & 0x1f1f1f1fu;
-        const uint32_t childBits4 = (meta4 >> 5) & 0x07070707u;
         const uint32_t lox = h ? n2.y : n2.x, loy = h ? n2.w : n2.z, loz = h ? n3.y : n3.x;
         const uint32_t hix = h ? n3.w : n3.z, hiy = h ? n4.y : n4.x, hiz = h ? n4.w : n4.z;
         const uint32_t ex = nx ? hix : lox, fx = nx ? lox : hix;
@@ -150,13 +150,26 @@ __device__ __forceinline__ void lane_node_step(WideLane &L, const SceneDev &sc, 
             const float tez = __fmaf_rn(q8(ez, j), adz, bzl), tfz = __fmaf_rn(q8(fz, j), adz, bzh);
             const float tEnter = fmaxf(fmaxf(tex, tey), fmaxf(tez, 0.f));
             const float tExit = fminf(fminf(tfx, tfy), fminf(tfz, L.tmax));
-            if (tEnter <= tExit) hitmask |= ((childBits4 >> (8 * j)) & 0xffu) << ((bitIndex4 >> (8 * j)) & 0xffu);
+            if (tEnter <= tExit) slotHit |= 1u << (4 * h + j);
         }
     }
+    // inner children: the bit of slot s goes to position 24 + (s ^ octinv), so that "highest bit first" is front to back
+    const uint32_t imask = n0.w >> 24;
+    uint32_t ih = slotHit & imask;
+    const uint32_t oi = L.octinv4;
+    if (oi & 1u) ih = ((ih & 0x55u) << 1) | ((ih >> 1) & 0x55u);
+    if (oi & 2u) ih = ((ih & 0x33u) << 2) | ((ih >> 2) & 0x33u);
+    if (oi & 4u) ih = ((ih & 0x0fu) << 4) | (ih >> 4);
+    // triangles: bit s -> bits 3s..3s+2 (the multiplications only add disjoint bit sets), then keep the ones that exist
+    uint32_t th = slotHit;
+    th = (th * 0x101u) & 0x0000f00fu;
+    th = (th * 0x11u) & 0x000c30c3u;
+    th = (th * 0x5u) & 0x00249249u;
+    th = (th * 7u) & n1.y;
+    L.tx = node * kTriSlots;
+    L.ty = th;
     L.gx = n1.x;
-    L.gy = (hitmask & 0xff000000u) | (n0.w >> 24);
-    L.tx = n1.y;
-    L.ty = hitmask & 0x00ffffffu;
+    L.gy = (ih << 24) | imask;
     wide_normalise(L, stk, stride);
 }
 

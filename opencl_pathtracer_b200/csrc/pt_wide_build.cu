@@ -8,8 +8,9 @@
 //      replaced by its own two children until 8 children are reached or only leaves are left;
 //   3. children are assigned to the 8 slots so that, for a ray of octant o, visiting slots by decreasing (slot ^ (7-o))
 //      is approximately front to back (greedy assignment on centroid offsets, after Ylitie et al. 2017);
-//   4. child boxes are quantised outwards to 8 bits on the node's grid; inner children get consecutive node indices,
-//      the triangles of leaf children consecutive positions in the wide triangle order.
+//   4. child boxes are quantised outwards to 8 bits on the node's grid; inner children get consecutive node indices;
+//      triangle k of the leaf child in slot s of node i is record 24 * i + 3 * s + k of the wide triangle order (a
+//      sparse array: unused records are never fetched, so they cost address space, not cache or bandwidth).
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -128,7 +129,6 @@ bool build_wide_bvh(const ptc_scene_view *s, WideBvh &out, std::string &err)
     const int root = B.convert(0);
     if (root < 0) return true;
     const std::vector<BNode> &b = B.b;
-    out.triOrder.reserve(s->triangulation_size);
     out.nodes.reserve(s->triangulation_size / 4 + 16);
 
     struct Item { int bnode; uint32_t index; uint32_t depth; };
@@ -199,10 +199,10 @@ bool build_wide_bvh(const ptc_scene_view *s, WideBvh &out, std::string &err)
             ebyte[a] = gridExponent((double)nb.hi[a] - nb.lo[a]);
             step[a] = std::ldexp(1.0, (int)ebyte[a] - 127);
         }
-        uint32_t imask = 0, nInner = 0, nTri = 0;
+        uint32_t imask = 0, nInner = 0, valid = 0;
         n.childBase = (uint32_t)out.nodes.size();
-        n.triBase = (uint32_t)out.triOrder.size();
-        uint8_t meta[8] = {0, 0, 0, 0, 0, 0, 0, 0}, qlo[3][8], qhi[3][8];
+        if (out.triOrder.size() < (size_t)(it.index + 1) * kTriSlots) out.triOrder.resize((size_t)(it.index + 1) * kTriSlots, kNoTriangle);
+        uint8_t qlo[3][8], qhi[3][8];
         std::memset(qlo, 0, sizeof(qlo));
         std::memset(qhi, 0, sizeof(qhi));
         for (int sl = 0; sl < 8; sl++)
@@ -220,18 +220,20 @@ bool build_wide_bvh(const ptc_scene_view *s, WideBvh &out, std::string &err)
             if (c.left >= 0)
             {
                 imask |= 1u << sl;
-                meta[sl] = (uint8_t)((1u << 5) | (24u + (uint32_t)sl));
                 nInner++;
             }
             else
             {
-                meta[sl] = (uint8_t)((((1u << c.count) - 1u) << 5) | nTri);
-                for (uint32_t k = 0; k < c.count; k++) out.triOrder.push_back(c.first + k);
-                nTri += c.count;
+                // triangle k of the leaf in slot sl: bit 3 * sl + k of `valid`, record it.index * 24 + 3 * sl + k
+                for (uint32_t k = 0; k < c.count; k++)
+                {
+                    valid |= 1u << (3 * sl + (int)k);
+                    out.triOrder[(size_t)it.index * kTriSlots + 3 * sl + k] = c.first + k;
+                }
             }
         }
         n.eimask = ebyte[0] | (ebyte[1] << 8) | (ebyte[2] << 16) | (imask << 24);
-        std::memcpy(n.meta, meta, 8);
+        n.valid = valid;
         for (int a = 0; a < 3; a++) { std::memcpy(n.qlo[a], qlo[a], 8); std::memcpy(n.qhi[a], qhi[a], 8); }
         out.nodes[it.index] = n;
         // inner children: consecutive nodes in slot order
@@ -240,7 +242,8 @@ bool build_wide_bvh(const ptc_scene_view *s, WideBvh &out, std::string &err)
         for (int sl = 0; sl < 8; sl++)
             if (childAt[sl] >= 0 && b[child[childAt[sl]]].left >= 0) todo.push_back({child[childAt[sl]], n.childBase + rank++, it.depth + 1u});
     }
-    if (out.triOrder.size() >= (1u << 27)) { err = "wide BVH: too many triangles"; return false; }
+    out.triOrder.resize(out.nodes.size() * kTriSlots, kNoTriangle);
+    if (out.triOrder.size() >= (1ull << 31)) { err = "wide BVH: too many nodes"; return false; }
     return true;
 }
 

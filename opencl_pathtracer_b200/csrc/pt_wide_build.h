@@ -13,7 +13,7 @@ namespace ptc
 struct WideBvh
 {
     std::vector<DevNode8> nodes;     // nodes[0] is the root
-    std::vector<uint32_t> triOrder;  // wide order -> index in the BVH-ordered triangle array
+    std::vector<uint32_t> triOrder;  // 24 records per node (slot-major, 3 per slot) -> index in the BVH-ordered triangle array, kNoTriangle = unused
     uint32_t depth = 0;              // levels of wide nodes
 };
 

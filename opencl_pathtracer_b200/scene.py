@@ -27,7 +27,7 @@ MATERIAL = np.dtype({"names": ["simpleColor", "textureName", "opacity", "texture
 
 
 # csrc/pt_wide.cuh DevNode8
-NODE8 = np.dtype([("p", "<f4", 3), ("e", "u1", 3), ("imask", "u1"), ("childBase", "<u4"), ("triBase", "<u4"), ("meta", "u1", 8),
+NODE8 = np.dtype([("p", "<f4", 3), ("e", "u1", 3), ("imask", "u1"), ("childBase", "<u4"), ("valid", "<u4"), ("spare", "<u4", 2),
                   ("qlo", "u1", (3, 8)), ("qhi", "u1", (3, 8))])
 assert NODE8.itemsize == 80
 
@@ -89,7 +89,7 @@ class Scene:
 
     def wide_bvh(self):
         """The 8-wide compressed BVH FAST mode traverses (csrc/pt_wide_build.cu): (nodes[n] as NODE8 records,
-        tri_order[nT] wide order -> BVH order, depth)."""
+        tri_order[24 n]: record 24 i + 3 slot + k -> BVH-order triangle index or 0xffffffff, depth)."""
         lib = N.cuda_lib()
         w = N.WideBvh()
         v = self.view()

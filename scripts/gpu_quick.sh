@@ -1,1 +1,2 @@
-for s in 1 2 4 8 16; do timeout 300 python scripts/profile_step.py $s fast atrium 3; done
+timeout 900 python -m pytest tests -m gpu -q -x 2>&1 | tail -3
+timeout 300 python scripts/profile_step.py 8 fast atrium 2

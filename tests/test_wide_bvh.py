@@ -12,21 +12,20 @@ def _decode(nodes, i):
     return n, lo, hi  # lo/hi: [axis, slot]
 
 
-def _children(n):
-    """(slot, kind, first, count): inner -> node index, leaf -> wide-order triangle range."""
+def _children(n, i):
+    """(slot, kind, first, count): inner -> node index, leaf -> first record of the sparse triangle order."""
     out = []
+    valid, imask = int(n["valid"]), int(n["imask"])
+    assert valid >> 24 == 0
     for s in range(8):
-        m = int(n["meta"][s])
-        if m == 0:
-            continue
-        if (m & 0x18) == 0x18 and (m >> 5) == 1:
-            assert (m & 0x1f) == 24 + s and (int(n["imask"]) >> s) & 1
-            rel = bin(int(n["imask"]) & ((1 << s) - 1)).count("1")
+        bits = (valid >> (3 * s)) & 7
+        if (imask >> s) & 1:
+            assert bits == 0
+            rel = bin(imask & ((1 << s) - 1)).count("1")
             out.append((s, "inner", int(n["childBase"]) + rel, 1))
-        else:
-            bits = m >> 5
-            assert bits in (1, 3, 7) and not (int(n["imask"]) >> s) & 1
-            out.append((s, "leaf", int(n["triBase"]) + (m & 0x1f), bin(bits).count("1")))
+        elif bits:
+            assert bits in (1, 3, 7)
+            out.append((s, "leaf", 24 * i + 3 * s, bin(bits).count("1")))
     return out
 
 
@@ -36,7 +35,8 @@ def test_wide_bvh_structure_and_boxes(scene_factory, name):
     nodes, order, depth = sc.wide_bvh()
     tris = sc.triangles()
     nT = len(tris)
-    assert sorted(order.tolist()) == list(range(nT)), "every triangle exactly once"
+    assert len(order) == 24 * len(nodes)
+    assert sorted(order[order != 0xffffffff].tolist()) == list(range(nT)), "every triangle exactly once"
     verts = np.stack([np.stack([tris[k][a] for a in "xyz"], -1) for k in ("S1", "S2", "S3")], 1).astype(np.float64)  # [tri, vertex, axis]
     seen_nodes, seen_tris, max_depth = set(), 0, 0
 
@@ -48,7 +48,7 @@ def test_wide_bvh_structure_and_boxes(scene_factory, name):
         max_depth = max(max_depth, d)
         n, lo, hi = _decode(nodes, i)
         blo, bhi = np.full(3, np.inf), np.full(3, -np.inf)
-        for s, kind, first, count in _children(n):
+        for s, kind, first, count in _children(n, i):
             if kind == "inner":
                 clo, chi = walk(first, d + 1)
             else:
@@ -116,21 +116,27 @@ def test_wide_bvh_traversal_matches_brute_force(scene_factory):
                 rel = bin(g[1] & 0xff & ((1 << slot) - 1)).count("1")
                 if rest > 0x00ffffff:
                     stack.append((g[0], rest))
-                n, blo, bhi = _decode(nodes, g[0] + rel)
+                node = g[0] + rel
+                n, blo, bhi = _decode(nodes, node)
                 visited_total += 1
-                hitmask = 0
+                slot_hit = 0
                 for s in range(8):
-                    m = int(n["meta"][s])
-                    if m == 0:
-                        continue
                     t1, t2 = (blo[:, s] - o) * inv, (bhi[:, s] - o) * inv
                     tn, tf = max(np.minimum(t1, t2).max(), 0.0), min(np.maximum(t1, t2).min(), tmax)
                     if tn <= tf:
-                        inner = (m & 0x18) == 0x18
-                        idx = ((m ^ (octinv if inner else 0)) & 0x1f)
-                        hitmask |= (m >> 5) << idx
-                g = (int(n["childBase"]), (hitmask & 0xff000000) | int(n["imask"]))
-                tg = [int(n["triBase"]), hitmask & 0x00ffffff]
+                        slot_hit |= 1 << s
+                imask = int(n["imask"])
+                ih = 0
+                for s in range(8):
+                    if (slot_hit & imask) >> s & 1:
+                        ih |= 1 << (s ^ octinv)
+                th = 0
+                for s in range(8):
+                    if slot_hit >> s & 1:
+                        th |= 7 << (3 * s)
+                th &= int(n["valid"])
+                g = (int(n["childBase"]), (ih << 24) | imask)
+                tg = [24 * node, th]
                 while tg[1]:
                     b = (tg[1] & -tg[1]).bit_length() - 1
                     tg[1] &= tg[1] - 1
