@@ -159,7 +159,7 @@ __global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas) k_trace(Sce
         {
             if (!ANY)
             {
-                st.hit[p] = f4(__int_as_float(L.hitTri), L.hs, L.ht, L.htp);
+                st.hit[p] = f4(__int_as_float(L.hit_index(sc)), L.hs, L.ht, L.htp);
                 atomicAdd(&st.nbbx[p], L.nb);
                 atomicAdd(&st.ntri[p], L.nt);
                 uint32_t flags = 0;

@@ -172,6 +172,7 @@ struct TraceLane
     __device__ __forceinline__ bool finished() const { return cur == kDone; }
     __device__ __forceinline__ bool wants_node() const { return !(cur & kLeafBit); }
     __device__ __forceinline__ bool wants_tri() const { return (cur & kLeafBit) && cur < kDone; }
+    __device__ __forceinline__ int hit_index(const SceneDev &) const { return hitTri; }
 };
 
 __device__ __forceinline__ bool lane_at_inner(const TraceLane &L) { return !(L.cur & kLeafBit); }

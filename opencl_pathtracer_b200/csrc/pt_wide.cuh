@@ -55,6 +55,8 @@ struct WideLane
     __device__ __forceinline__ bool finished() const { return sp == 0 && ty == 0u && gy <= 0x00ffffffu; }
     __device__ __forceinline__ bool wants_node() const { return sp >= 0 && ty == 0u && gy > 0x00ffffffu; }
     __device__ __forceinline__ bool wants_tri() const { return sp >= 0 && ty != 0u; }
+    // BVH-order index of the hit (what the shade stage and the reference's ids use), -1 = miss
+    __device__ __forceinline__ int hit_index(const SceneDev &sc) const { return hitTri < 0 ? -1 : (int)__ldg(&sc.tri8Index[hitTri]); }
 };
 
 __device__ __forceinline__ float finite_inverse(float inv, float d)
@@ -173,6 +175,9 @@ __device__ __forceinline__ void lane_node_step(WideLane &L, const SceneDev &sc, 
     wide_normalise(L, stk, stride);
 }
 
+// One triangle test. Nothing after the test branches: the accepted hit is kept as a record index of the wide order (hit_index
+// translates it once per ray) and the new bound follows from the hit's own ray parameter (directions are unit length over
+// the four lanes the reference normalises, so parameter and distance coincide).
 template <bool ANY>
 __device__ __forceinline__ void lane_tri_step(WideLane &L, const SceneDev &sc, const uint2 *stk, const int stride)
 {
@@ -180,17 +185,15 @@ __device__ __forceinline__ void lane_tri_step(WideLane &L, const SceneDev &sc, c
     L.ty &= L.ty - 1u;
     const uint32_t i = L.tx + (uint32_t)bit;
     L.nt++;
-    if (tri_test(sc.tris8, i, L.r, L.best, L.hs, L.ht, L.htp, L.hmat))
+    const bool acc = tri_test(sc.tris8, i, L.r, L.best, L.hs, L.ht, L.htp, L.hmat);
+    L.hitTri = acc ? (int)i : L.hitTri;
+    L.tmax = acc ? L.htp * 1.00001f : L.tmax;
+    if (ANY)
     {
-        L.hitTri = (int)__ldg(&sc.tri8Index[i]);  // back to BVH order, which the shade stage and the reference's `id`s use
-        L.tmax = bound_as_parameter(L.best);
-        if (ANY)
-        {
-            L.found = true;
-            L.gy = L.ty = 0u;
-            L.sp = 0;
-            return;
-        }
+        L.found = L.found || acc;
+        L.gy = acc ? 0u : L.gy;
+        L.ty = acc ? 0u : L.ty;
+        L.sp = acc ? 0 : L.sp;
     }
     wide_normalise(L, stk, stride);
 }
