@@ -289,6 +289,15 @@ int ptc_create(const ptc_config *config, ptc_ctx **out_ctx)
     c->lc.streamGrid = c->smCount * 8;
     c->lc.refillMin = 4;  // idle lanes that trigger a refill from the warp's staged rays (profiles/r01_sweeps.txt)
     if (const char *e = std::getenv("PTC_REFILL_MIN")) c->lc.refillMin = (uint32_t)std::max(1, std::min(32, std::atoi(e)));
+    {
+        // phase votes of k_trace, in eighths of the warp's rays: node steps while >= voteNode/8 wait for a node, triangle steps
+        // (after the first) while > voteTri/8 wait for a triangle
+        // (sweeps in profiles/r01_sweeps.txt: BVH2 walk 4 / 4; wide walk, whose lanes can park a triangle group, 5 / 3)
+        uint32_t vn = c->wide ? 5 : 4, vt = c->wide ? 3 : 4;
+        if (const char *e = std::getenv("PTC_VOTE_NODE")) vn = (uint32_t)std::max(0, std::min(8, std::atoi(e)));
+        if (const char *e = std::getenv("PTC_VOTE_TRI")) vt = (uint32_t)std::max(0, std::min(8, std::atoi(e)));
+        c->lc.refillMin |= (vn << 8) | (vt << 16);
+    }
     if (const char *e = std::getenv("PTC_CTAS_PER_SM")) c->lc.traverseGrid = c->smCount * std::max(1, std::atoi(e));
 
     cudaError_t e = cudaSuccess;
@@ -536,7 +545,7 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
     if (!std::getenv("PTC_FULL_STACK"))
     {
         ctx->lc.stackDepth = (int)std::min<uint32_t>(32u, std::max<uint32_t>(4u, maxDepth + 1));
-        if (ctx->wide) ctx->lc.stackDepth = (int)std::max<uint32_t>(2u, wideBvh.depth + 1);  // one postponed sibling group per level
+        if (ctx->wide) ctx->lc.stackDepth = (int)std::max<uint32_t>(3u, wideBvh.depth + 2);  // the parked triangle group + one sibling group per level
         if (!std::getenv("PTC_CTAS_PER_SM")) ctx->lc.traverseGrid = ctx->smCount * traverse_ctas_per_sm(ctx->fast, ctx->wide, ctx->lc.stackDepth);
     }
     ctx->sceneLoaded = true;

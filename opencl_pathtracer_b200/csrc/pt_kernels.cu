@@ -142,6 +142,8 @@ __global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas) k_trace(Sce
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt = (1u << lane) - 1u;
     const unsigned full = 0xffffffffu;
+    const int voteNode = (int)((popMin >> 8) & 0xffu), voteTri = (int)((popMin >> 16) & 0xffu);  // in eighths of the warp's rays
+    popMin &= 0xffu;
     const uint32_t count = cn->qcount[bounce];
     const uint32_t nL = ANY ? sc.nLights : 1u;
     const uint32_t total = count * nL;  // upload_scene guarantees capacity * nLights < 2^32
@@ -270,7 +272,7 @@ __global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas) k_trace(Sce
         {
             const bool wantNode = L.wants_node();
             const int nN = __popc(__ballot_sync(full, wantNode));
-            if (nN == 0 || 2 * nN < nHave) break;
+            if (nN == 0 || 8 * nN < voteNode * nHave) break;
             if (wantNode) lane_node_step<FAST>(L, sc, stk, kTraverseThreads);
         }
         // ---- triangle phase: at least one step if any lane waits for a triangle, then while they are the majority
@@ -280,7 +282,7 @@ __global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas) k_trace(Sce
             const int nT = __popc(__ballot_sync(full, wantTri));
             if (nT == 0) break;
             if (wantTri) lane_tri_step<ANY>(L, sc, stk, kTraverseThreads);
-            if (2 * nT <= nHave) break;
+            if (8 * nT <= voteTri * nHave) break;
         }
     }
     flush_work(cn, ANY ? &cn->shadowRays : &cn->extensionRays, nRays, nbSum, ntSum);

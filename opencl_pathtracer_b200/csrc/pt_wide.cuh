@@ -39,7 +39,7 @@ struct WideLane
     float tmax;        // the same bound as a ray parameter, padded
     uint32_t gx, gy;   // node group: first child index | bits 31..24 children still to visit (front to back), bits 7..0 imask
     uint32_t tx, ty;   // triangle group: first record (24 * node) | 24 bits of triangles still to test
-    uint32_t octinv4;  // (7 - ray octant) in every byte
+    uint32_t oct;      // bits 2..0: 7 - ray octant; kPostponed: a triangle group waits in the lane's slot 0 of the stack
     int sp;            // stack entries, -1 = no ray
     int hitTri;
     float hs, ht, htp;
@@ -52,9 +52,12 @@ struct WideLane
     __device__ __forceinline__ void reset() { sp = -1; gy = ty = 0; nb = nt = 0; found = false; hitTri = -1; }
     __device__ __forceinline__ bool idle() const { return sp < 0; }
     __device__ __forceinline__ void set_idle() { sp = -1; }
-    __device__ __forceinline__ bool finished() const { return sp == 0 && ty == 0u && gy <= 0x00ffffffu; }
-    __device__ __forceinline__ bool wants_node() const { return sp >= 0 && ty == 0u && gy > 0x00ffffffu; }
-    __device__ __forceinline__ bool wants_tri() const { return sp >= 0 && ty != 0u; }
+    static constexpr uint32_t kPostponed = 0x100u;
+    __device__ __forceinline__ bool finished() const { return sp == 0 && ty == 0u && gy <= 0x00ffffffu && !(oct & kPostponed); }
+    // A lane can take a node step while it still holds untested triangles: it parks that group (once) and tests it in the
+    // next triangle phase. So a lane often qualifies for both phases and follows the warp's vote instead of idling.
+    __device__ __forceinline__ bool wants_node() const { return sp >= 0 && gy > 0x00ffffffu && (ty == 0u || !(oct & kPostponed)); }
+    __device__ __forceinline__ bool wants_tri() const { return sp >= 0 && (ty != 0u || (oct & kPostponed)); }
     // BVH-order index of the hit (what the shade stage and the reference's ids use), -1 = miss
     __device__ __forceinline__ int hit_index(const SceneDev &sc) const { return hitTri < 0 ? -1 : (int)__ldg(&sc.tri8Index[hitTri]); }
 };
@@ -78,7 +81,7 @@ __device__ __forceinline__ void lane_begin(WideLane &L, const SceneDev &sc, cons
     L.best = best;
     L.tmax = bound_as_parameter(best);
     const uint32_t oct = (r.dx < 0 ? 4u : 0u) | (r.dy < 0 ? 2u : 0u) | (r.dz < 0 ? 1u : 0u);
-    L.octinv4 = (7u - oct) * 0x01010101u;
+    L.oct = 7u - oct;
     L.gx = 0u;
     L.gy = sc.nNodes8 ? 0x80000000u : 0u;  // "slot 7 ^ octinv of an imask-less group at index 0" = the root
     L.tx = L.ty = 0u;
@@ -90,13 +93,14 @@ __device__ __forceinline__ void lane_begin(WideLane &L, const SceneDev &sc, cons
     L.found = false;
 }
 
-// nothing left in the current groups: continue with the most recently postponed siblings
+// no inner child left in the current node group: continue with the most recently postponed siblings. Stack level 0 of a
+// lane is the slot of its parked triangle group, sibling groups live in levels 1..sp.
 __device__ __forceinline__ void wide_normalise(WideLane &L, const uint2 *stk, const int stride)
 {
-    const bool pop = L.ty == 0u && L.gy <= 0x00ffffffu && L.sp > 0;
+    const bool pop = L.gy <= 0x00ffffffu && L.sp > 0;
     if (pop)
     {
-        const uint2 e = stk[(L.sp - 1) * stride];
+        const uint2 e = stk[L.sp * stride];
         L.gx = e.x;
         L.gy = e.y;
     }
@@ -111,13 +115,18 @@ __device__ __forceinline__ void lane_node_step(WideLane &L, const SceneDev &sc, 
 {
     const uint32_t hits = L.gy;
     const int bit = 31 - __clz((int)hits);
-    const uint32_t slot = (uint32_t)(bit - 24) ^ (L.octinv4 & 7u);
+    const uint32_t slot = (uint32_t)(bit - 24) ^ (L.oct & 7u);
     const uint32_t rest = hits & ~(1u << bit);
     const uint32_t rel = (uint32_t)__popc(hits & 0xffu & ((1u << slot) - 1u));
     const uint32_t node = L.gx + rel;
     const uint4 *np = reinterpret_cast<const uint4 *>(sc.nodes8 + node);
     const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
-    if (rest > 0x00ffffffu) stk[L.sp * stride] = make_uint2(L.gx, rest);
+    if (L.ty != 0u)
+    {
+        stk[0] = make_uint2(L.tx, L.ty);  // park the untested triangles (wants_node: the slot is free)
+        L.oct |= WideLane::kPostponed;
+    }
+    if (rest > 0x00ffffffu) stk[(L.sp + 1) * stride] = make_uint2(L.gx, rest);
     L.sp += rest > 0x00ffffffu ? 1 : 0;
     L.nb += 8;
 
@@ -158,7 +167,7 @@ __device__ __forceinline__ void lane_node_step(WideLane &L, const SceneDev &sc, 
     // inner children: the bit of slot s goes to position 24 + (s ^ octinv), so that "highest bit first" is front to back
     const uint32_t imask = n0.w >> 24;
     uint32_t ih = slotHit & imask;
-    const uint32_t oi = L.octinv4;
+    const uint32_t oi = L.oct;
     if (oi & 1u) ih = ((ih & 0x55u) << 1) | ((ih >> 1) & 0x55u);
     if (oi & 2u) ih = ((ih & 0x33u) << 2) | ((ih >> 2) & 0x33u);
     if (oi & 4u) ih = ((ih & 0x0fu) << 4) | (ih >> 4);
@@ -181,6 +190,13 @@ __device__ __forceinline__ void lane_node_step(WideLane &L, const SceneDev &sc, 
 template <bool ANY>
 __device__ __forceinline__ void lane_tri_step(WideLane &L, const SceneDev &sc, const uint2 *stk, const int stride)
 {
+    if (L.ty == 0u)
+    {
+        const uint2 e = stk[0];  // the parked group
+        L.tx = e.x;
+        L.ty = e.y;
+        L.oct &= ~WideLane::kPostponed;
+    }
     const int bit = __ffs((int)L.ty) - 1;
     L.ty &= L.ty - 1u;
     const uint32_t i = L.tx + (uint32_t)bit;
@@ -194,6 +210,7 @@ __device__ __forceinline__ void lane_tri_step(WideLane &L, const SceneDev &sc, c
         L.gy = acc ? 0u : L.gy;
         L.ty = acc ? 0u : L.ty;
         L.sp = acc ? 0 : L.sp;
+        L.oct = acc ? (L.oct & 7u) : L.oct;
     }
     wide_normalise(L, stk, stride);
 }
