@@ -22,10 +22,20 @@ __device__ __forceinline__ float4 operator-(float4 a) { return f4(-a.x, -a.y, -a
 
 __device__ __forceinline__ float dot4(float4 a, float4 b) { return ((a.x * b.x + a.y * b.y) + a.z * b.z) + a.w * b.w; }
 __device__ __forceinline__ float length4(float4 a) { return sqrtf(dot4(a, a)); }
+// a / l where l is a length (a square root: >= 0 or NaN). A zero numerator sends the IEEE division to its slow path (FCHK
+// fails, a subroutine call), and the w lane of every direction is 0, as are lanes of the tangent frame. +-0 / l is +-0 for
+// every l > 0 and NaN otherwise; that case is answered directly and the division itself never sees the zero (a select on a
+// plain `a / l` would still evaluate it). Bit-identical results for every finite outcome.
+__device__ __forceinline__ float div_by_length(float a, float l)
+{
+    const bool z = a == 0.f;
+    const float t = (z ? 1.f : a) / l;
+    return z ? (l > 0.f ? a : __int_as_float(0x7fffffff)) : t;
+}
 __device__ __forceinline__ float4 normalize4(float4 a)
 {
     float l = length4(a);
-    return f4(a.x / l, a.y / l, a.z / l, a.w / l);
+    return f4(div_by_length(a.x, l), div_by_length(a.y, l), div_by_length(a.z, l), div_by_length(a.w, l));
 }
 __device__ __forceinline__ float4 cross3(float4 a, float4 b)
 {
@@ -49,7 +59,7 @@ __device__ __forceinline__ float clmax(float x, float y) { return x < y ? y : x;
 __device__ __forceinline__ float rng_next(int &seed)
 {
     seed = (int)((16807u * (unsigned)seed) & 0x7FFFFFFFu);
-    return (float)seed / 2147483648.0f;
+    return (float)seed * 4.656612873077392578125e-10f;  // = / 2^31 exactly (a power of two; the division's range check would fail)
 }
 
 // reference header.cl:255-264 (int arithmetic wraps; only the low 32 bits matter)
