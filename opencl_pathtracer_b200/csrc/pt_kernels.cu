@@ -290,7 +290,7 @@ __global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas) k_trace(Sce
 
 // ------------------------------------------------------------------------------------------------ shade
 template <bool FAST>
-__global__ void __launch_bounds__(kStreamThreads) k_shade(SceneDev sc, FrameParams fp, PathState st, const uint32_t *__restrict__ qin,
+__global__ void __launch_bounds__(kStreamThreads, 4) k_shade(SceneDev sc, FrameParams fp, PathState st, const uint32_t *__restrict__ qin,
                                                          uint32_t *__restrict__ qout, Counters *__restrict__ cn, int bounce)
 {
     const uint32_t count = cn->qcount[bounce];
@@ -358,11 +358,14 @@ __global__ void __launch_bounds__(kStreamThreads) k_shade(SceneDev sc, FramePara
                 float4 Nref = d, out = d;
                 float4 add = f4(0, 0, 0, 0);
                 bool inWater = (meta >> 8) & 1u;
+                // the cosine-weighted bounce of MAT_STANDART and of the diffuse branch of MAT_VARNHISHED is drawn in one place,
+                // after the per-material part, so that the lanes of both materials run it together (same draws, same order)
+                bool diffuseBounce = false;
                 if (mat.type == 0)
                 {
                     T = T * color;
                     add = L * T;
-                    out = cosine_sample_hemisphere(seed, Ns);
+                    diffuseBounce = true;
                     Nref = Ns;
                 }
                 else if (mat.type == 2)
@@ -390,8 +393,9 @@ __global__ void __launch_bounds__(kStreamThreads) k_shade(SceneDev sc, FramePara
                     add = add + L * color * T;
                     const float rF = fresnel_varnish(d, Ns);
                     if (rng_next(seed) < rF) out = d - (Ns * (2 * dot4(d, Ns)));
-                    else { out = cosine_sample_hemisphere(seed, Ns); T = T * color; }
+                    else { diffuseBounce = true; T = T * color; }
                 }
+                if (diffuseBounce) out = cosine_sample_hemisphere(seed, Ns);
                 put_in_same_hemisphere(out, Nref);
                 rad = rad + add;
                 const uint32_t refl = (meta & 0xffu) + 1u;
