@@ -106,8 +106,13 @@ __device__ __forceinline__ bool box_test(float nx, float ny, float nz, float xx,
 // zero for conformant data (upload checks S1.w == S2.w == S3.w) and omitted.
 // On acceptance hmat receives the MaterialType of the side that was hit (:568): both sides' types ride in the spare
 // lane of the record (e2.w, bits 3..0 positive side, bits 7..4 negative side).
+// order / prevHit (wide walk only): the reference keeps the LAST candidate it tests among several at exactly the same distance
+// (:543 is a strict test), and inside one leaf it tests in array order. The wide walk tests in another order, so on an
+// exact tie it keeps the candidate with the higher BVH-order index: what the reference does whenever the candidates share
+// a leaf. order = null in the BVH2 walk, whose test order is the reference's.
 __device__ __forceinline__ bool tri_test(const DevTri *__restrict__ tris, uint32_t i, const Ray &r, float &best, float &hs,
-                                         float &ht, float &htp, uint32_t &hmat)
+                                         float &ht, float &htp, uint32_t &hmat, const uint32_t *__restrict__ order = nullptr,
+                                         int prevHit = -1)
 {
     float4 n, p, e1, e2;
     ldg256(&tris[i].n, n, p);
@@ -120,6 +125,7 @@ __device__ __forceinline__ bool tri_test(const DevTri *__restrict__ tris, uint32
     const float fx = qx - r.ox, fy = qy - r.oy, fz = qz - r.oz, fw = qw - r.ow;
     const float nsd = ((fx * fx + fy * fy) + fz * fz) + fw * fw;
     if (nsd > best) return false;
+    if (order && nsd == best && prevHit >= 0 && __ldg(&order[i]) < __ldg(&order[prevHit])) return false;
     if (nsd < 0.00001f) return false;
     const float wx = qx - p.x, wy = qy - p.y, wz = qz - p.z;
     const float uv = (e1.x * e2.x + e1.y * e2.y) + e1.z * e2.z;

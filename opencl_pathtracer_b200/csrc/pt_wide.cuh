@@ -201,7 +201,7 @@ __device__ __forceinline__ void lane_tri_step(WideLane &L, const SceneDev &sc, c
     L.ty &= L.ty - 1u;
     const uint32_t i = L.tx + (uint32_t)bit;
     L.nt++;
-    const bool acc = tri_test(sc.tris8, i, L.r, L.best, L.hs, L.ht, L.htp, L.hmat);
+    const bool acc = tri_test(sc.tris8, i, L.r, L.best, L.hs, L.ht, L.htp, L.hmat, ANY ? nullptr : sc.tri8Index, L.hitTri);
     L.hitTri = acc ? (int)i : L.hitTri;
     L.tmax = acc ? L.htp * 1.00001f : L.tmax;
     if (ANY)
