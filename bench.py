@@ -142,7 +142,7 @@ def main():
     ap.add_argument("--workload", default="atrium", choices=sorted(WORKLOADS))
     ap.add_argument("--mode", default="fast", choices=["fast", "parity"])
     ap.add_argument("--spp-per-step", type=int, default=0, help="iterations per step per GPU (0 = the workload's default)")
-    ap.add_argument("--ref-rows", type=int, default=16)
+    ap.add_argument("--ref-rows", type=int, default=128)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--progressive", type=int, default=0, metavar="FRAMES",
                     help="C5: time FRAMES progressive frames (1 spp each, moving camera, RGB8 read-back) instead of the throughput run")

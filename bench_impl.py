@@ -135,24 +135,50 @@ def run_ours(args, rank, local_rank, world):
             rp.render(S, S, sync=True)
             c = rp.counters()
             rp.close()
-            ext_bytes = 64.0 * (c["ext_box_tests"] / 2 + c["ext_triangle_tests"])
-            con_bytes = 64.0 * ((c["box_tests"] - c["ext_box_tests"]) / 2 + (c["triangle_tests"] - c["ext_triangle_tests"]))
-            kern = {"k_extend": (ext_bytes, c["ms_extend"], c["launches_extend"], c["extension_rays"]),
-                    "k_connect": (con_bytes, c["ms_connect"], c["launches_connect"], c["shadow_rays"])}
+            # Algorithmic bytes per traced ray: 64 B per inner-node visit + 64 B per triangle test of the
+            # reference BVH2 walked with a correct distance cull (FAST | FLAG_BVH2), counted by the kernels themselves, per
+            # extension ray and per shadow ray. The kernel being timed may need fewer bytes (wide BVH): `fetched_bytes_per_launch`
+            # is what ITS walk asks for in its own layout (80 B per 8-wide node, 64 B per triangle record).
+            wide = args.mode == "fast"
+            if wide:
+                rb = pt.PathTracerCUDA(W, H, ray_max_depth=DEPTH, mode=pt.MODE_FAST, device=local_rank,
+                                       flags=pt.FLAG_NO_VARIANCE | pt.FLAG_BVH2, stream=stream.cuda_stream)
+                rb.upload(scene)
+                rb.render(S, S, sync=True)
+                cb = rb.counters()
+                rb.close()
+            else:
+                cb = c
+            per_ext = 64.0 * (cb["ext_box_tests"] / 2 + cb["ext_triangle_tests"]) / max(cb["extension_rays"], 1)
+            per_con = 64.0 * ((cb["box_tests"] - cb["ext_box_tests"]) / 2 + (cb["triangle_tests"] - cb["ext_triangle_tests"])) / max(cb["shadow_rays"], 1)
+            node_b, fan = (80.0, 8) if wide else (64.0, 2)
+            own_ext = node_b * c["ext_box_tests"] / fan + 64.0 * c["ext_triangle_tests"]
+            own_con = node_b * (c["box_tests"] - c["ext_box_tests"]) / fan + 64.0 * (c["triangle_tests"] - c["ext_triangle_tests"])
+            kern = {"k_extend": (per_ext * c["extension_rays"], c["ms_extend"], c["launches_extend"], c["extension_rays"], own_ext, per_ext),
+                    "k_connect": (per_con * c["shadow_rays"], c["ms_connect"], c["launches_connect"], c["shadow_rays"], own_con, per_con)}
             dom = max(kern, key=lambda k: kern[k][1])
             traffic = None
             tp = os.path.join(ROOT, "profiles", "traffic.json")
             if os.path.exists(tp):
                 with open(tp) as f:
                     traffic = json.load(f).get(args.workload, {}).get(dom)
+            # measured read bandwidths with the traversal's own load instruction: 32 MB (L2 hits) and 4 GB (HBM)
+            rm = pt.PathTracerCUDA(64, 64, mode=pt.MODE_FAST, device=local_rank, flags=pt.FLAG_NO_VARIANCE, stream=stream.cuda_stream)
+            l2_read = rm.measure_read_bandwidth(32 << 20, 200)
+            hbm_read = rm.measure_read_bandwidth(4 << 30, 3)
+            rm.close()
 
             def roofline(name):
-                b, t_ms, n, nrays = kern[name]
+                b, t_ms, n, nrays, own, per_ray = kern[name]
                 ach = b / (t_ms * 1e-3) / 1e9 if t_ms > 0 else 0.0
                 return {"kernel": name, "bound": "hbm", "achieved": ach, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": ach / peaks["hbm_gbs"],
                         "peak_kind": peak_kind + " HBM copy bandwidth (%s)" % ("working set is L2-resident: see DESIGN.md" if scene_mb < 100 else "node + triangle records exceed the L2"),
-                        "algorithmic_bytes_per_launch": b / max(n, 1), "avg_launch_ms": t_ms / max(n, 1), "launches": n,
-                        "mrays_per_s": nrays / (t_ms * 1e-3) / 1e6 if t_ms > 0 else 0.0}
+                        "algorithmic_bytes_per_launch": b / max(n, 1), "algorithmic_bytes_per_ray": per_ray,
+                        "fetched_bytes_per_launch": own / max(n, 1), "fetched_gbs": own / (t_ms * 1e-3) / 1e9 if t_ms > 0 else 0.0,
+                        "avg_launch_ms": t_ms / max(n, 1), "launches": n,
+                        "mrays_per_s": nrays / (t_ms * 1e-3) / 1e6 if t_ms > 0 else 0.0,
+                        "l2_read_gbs_measured": l2_read, "hbm_read_gbs_measured": hbm_read,
+                        "frac_of_l2_read": (own / (t_ms * 1e-3) / 1e9 / l2_read) if (t_ms > 0 and l2_read > 0) else None}
 
             roof = roofline(dom)
             roof["traffic"] = traffic
@@ -185,7 +211,7 @@ def run_ours(args, rank, local_rank, world):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
             from oracle import ptref
-            rows = (H // 2 - 32, H // 2 + 32)
+            rows = (0, H)  # the whole frame once: ~10-15 s on 16 host cores
             t0 = time.perf_counter()
             ptref.render(scene, W, H, DEPTH, 0, 0, 1, rows=rows)
             dt = time.perf_counter() - t0

@@ -218,6 +218,12 @@ typedef struct ptc_wide_bvh
 PTC_API int ptc_wide_bvh_build(const ptc_scene_view *scene, ptc_wide_bvh *out);
 PTC_API void ptc_wide_bvh_free(ptc_wide_bvh *bvh);
 
+/* Measurement utility (roofline denominators of bench.py): read-only streaming of a `bytes`-sized device buffer, `repeats`
+ * passes, with the 256-bit loads the traversal kernels use, L1 bypassed. A buffer that fits the L2 (e.g. 32 MB) gives the L2
+ * hit bandwidth the node / triangle fetches of an L2-resident scene are bounded by; a buffer far larger than the L2 gives the
+ * HBM read bandwidth. Result in GB/s (1e9 bytes). */
+PTC_API int ptc_measure_read_bandwidth(ptc_ctx *ctx, size_t bytes, uint32_t repeats, double *gb_per_s);
+
 /* Pinned host memory for read-backs inside timed regions. */
 PTC_API void *ptc_host_alloc(size_t bytes);
 PTC_API void ptc_host_free(void *p);

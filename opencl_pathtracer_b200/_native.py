@@ -68,7 +68,7 @@ class SceneInfo(C.Structure):
 PTC_SYMBOLS = ["ptc_create", "ptc_upload_scene", "ptc_set_camera", "ptc_reset_accumulation", "ptc_render", "ptc_synchronize",
                "ptc_read_image", "ptc_read_variance", "ptc_read_stats", "ptc_read_rgb8", "ptc_add_image", "ptc_read_counters",
                "ptc_get_device_buffers", "ptc_trace_primary", "ptc_trace_rays", "ptc_render_single", "ptc_host_alloc", "ptc_host_free",
-               "ptc_last_error", "ptc_version", "ptc_device_count", "ptc_destroy", "ptc_wide_bvh_build", "ptc_wide_bvh_free"]
+               "ptc_last_error", "ptc_version", "ptc_device_count", "ptc_destroy", "ptc_wide_bvh_build", "ptc_wide_bvh_free", "ptc_measure_read_bandwidth"]
 
 _cuda = None
 _host = None
@@ -109,6 +109,7 @@ def cuda_lib():
     L.ptc_trace_primary.argtypes = [vp, u32, vp, vp, vp, vp, vp, vp]
     L.ptc_trace_rays.argtypes = [vp, u32, vp, vp, vp, vp, vp, vp, vp]
     L.ptc_render_single.argtypes = [vp, u32, vp]
+    L.ptc_measure_read_bandwidth.argtypes = [vp, C.c_size_t, u32, P(C.c_double)]
     L.ptc_host_alloc.argtypes = [C.c_size_t]
     L.ptc_host_alloc.restype = vp
     L.ptc_host_free.argtypes = [vp]

@@ -199,6 +199,37 @@ void ptc_host_free(void *p)
     if (p) cudaFreeHost(p);
 }
 
+int ptc_measure_read_bandwidth(ptc_ctx *ctx, size_t bytes, uint32_t repeats, double *gb_per_s)
+{
+    if (!ctx || !gb_per_s || bytes < 32 || repeats == 0) return PTC_ERR_INVALID;
+    CK(cudaSetDevice(ctx->device));
+    DevBuf<uint4> buf;
+    DevBuf<uint32_t> sink;
+    bytes &= ~(size_t)31;
+    CK(buf.alloc(bytes / 16));
+    CK(sink.alloc(1));
+    CK(cudaMemsetAsync(buf.p, 0x5a, bytes, ctx->stream));
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    const int grid = ctx->smCount * 8;
+    launch_read_stream(ctx->stream, grid, buf.p, bytes, 2, sink.p);  // warm-up (fills the L2 when the buffer fits)
+    cudaEventRecord(e0, ctx->stream);
+    launch_read_stream(ctx->stream, grid, buf.p, bytes, repeats, sink.p);
+    cudaEventRecord(e1, ctx->stream);
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    buf.release();
+    sink.release();
+    ctx->launches += 2;
+    if (e != cudaSuccess) return fail(ctx, PTC_ERR_CUDA, "ptc_measure_read_bandwidth: %s", cudaGetErrorString(e));
+    *gb_per_s = ms > 0.f ? (double)bytes * repeats / (ms * 1e-3) / 1e9 : 0.0;
+    return PTC_OK;
+}
+
 void ptc_destroy(ptc_ctx *ctx)
 {
     if (!ctx) return;

@@ -586,7 +586,29 @@ __global__ void k_add_image(ImageDev img, uint32_t nPixels, const float4 *color,
     }
 }
 
+// Roofline denominator: read-only streaming over a buffer with the loads the traversal uses (256-bit, L1 bypassed so that a
+// buffer smaller than the L2 measures L2 hit bandwidth and a larger one HBM read bandwidth).
+__global__ void __launch_bounds__(kStreamThreads) k_read_stream(const uint4 *__restrict__ buf, size_t nVec32, uint32_t repeats, uint32_t *sink)
+{
+    uint32_t acc = 0;
+    for (uint32_t r = 0; r < repeats; r++)
+        for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nVec32; i += (size_t)gridDim.x * blockDim.x)
+        {
+            uint32_t a, b, c, d, e, f, g, h;
+            asm volatile("ld.global.cg.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                         : "=r"(a), "=r"(b), "=r"(c), "=r"(d), "=r"(e), "=r"(f), "=r"(g), "=r"(h)
+                         : "l"(reinterpret_cast<const char *>(buf) + i * 32));
+            acc ^= a ^ b ^ c ^ d ^ e ^ f ^ g ^ h;
+        }
+    if (acc == 0x9e3779b9u) *sink = acc;  // keeps the loads alive
+}
+
 // ------------------------------------------------------------------------------------------------ launchers
+void launch_read_stream(cudaStream_t s, int grid, const void *buf, size_t bytes, uint32_t repeats, uint32_t *sink)
+{
+    k_read_stream<<<grid, kStreamThreads, 0, s>>>(reinterpret_cast<const uint4 *>(buf), bytes / 32, repeats, sink);
+}
+
 static inline size_t stack_bytes(bool wide, int stackDepth)
 {
     return (size_t)stackDepth * kTraverseThreads * (wide ? sizeof(uint2) : sizeof(uint32_t)) + kStageBytes;

@@ -30,6 +30,8 @@ void launch_accumulate(cudaStream_t s, const LaunchCfg &lc, const FrameParams &f
 void launch_probe_primary(cudaStream_t s, const FrameParams &fp, const PathState &st, int32_t *hit, float2 *stOut, float *dist2,
                           float4 *dir, int32_t *seedAfter, uint2 *counts);
 void launch_probe_rays(cudaStream_t s, uint32_t n, const float4 *origin, const float4 *direction, const PathState &st);
+// roofline denominators (ptc_measure_read_bandwidth)
+void launch_read_stream(cudaStream_t s, int grid, const void *buf, size_t bytes, uint32_t repeats, uint32_t *sink);
 // display epilogue: sum / count -> clamp -> 8 bit (reference Alone/PathTracer_bitmap.cpp:259-279)
 void launch_rgb8(cudaStream_t s, const ImageDev &img, uint32_t nPixels, uint8_t *rgb);
 void launch_add_image(cudaStream_t s, const ImageDev &img, uint32_t nPixels, const float4 *color, const float *rayNb);

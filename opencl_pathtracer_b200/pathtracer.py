@@ -124,6 +124,12 @@ class PathTracerCUDA:
                                           out["dist2"].ctypes.data, out["dir"].ctypes.data, out["counts"].ctypes.data))
         return out
 
+    def measure_read_bandwidth(self, nbytes, repeats):
+        """GB/s of a read-only streaming pass over an nbytes device buffer (L2 hit bandwidth if it fits the L2, else HBM)."""
+        g = C.c_double()
+        self._ck(self._lib.ptc_measure_read_bandwidth(self._h, nbytes, repeats, C.byref(g)))
+        return g.value
+
     def render_single(self, iteration):
         r = np.empty((self.height, self.width, 4), dtype=np.float32)
         self._ck(self._lib.ptc_render_single(self._h, iteration, r.ctypes.data))
