@@ -147,6 +147,9 @@ def host_lib():
     L.pth_scene_get_info.restype = None
     L.pth_scene_get_view.argtypes = [vp, C.POINTER(SceneView)]
     L.pth_scene_get_view.restype = None
+    L.pth_scene_import.argtypes = [C.c_char_p, u32, u32, C.c_int]
+    L.pth_scene_import.restype = vp
+    L.pth_scene_export.argtypes = [vp, C.c_char_p]
     L.pth_scene_free.argtypes = [vp]
     L.pth_scene_free.restype = None
     L.pth_main.argtypes = [C.c_char_p, u32, u32, u32, u32, C.c_int, C.c_int, C.c_int, u32, C.c_int, u32, C.c_int, C.c_char_p,

@@ -56,7 +56,7 @@ def build(verbose=False, force=False):
             os.remove(o)
     host_so = os.path.join(LIB, "libpathtracer_host.so")
     host_src = [os.path.join(HOST, f) for f in ("PathTracer_BVH.cpp", "PathTracer_ProceduralImporter.cpp", "PathTracer_CUDA.cpp",
-                                                "PathTracer_Dialog.cpp", "PathTracer.cpp", "pth_capi.cpp")]
+                                                "PathTracer_Dialog.cpp", "PathTracer_FileImporter.cpp", "PathTracer.cpp", "pth_capi.cpp")]
     host_hdr = [os.path.join(HOST, f) for f in os.listdir(HOST) if f.endswith(".h")] + headers
     if force or _newer(host_so, host_src + host_hdr + [cuda_so, __file__]):
         _run(["g++"] + CXX_FLAGS + ["-shared", "-o", host_so] + host_src +

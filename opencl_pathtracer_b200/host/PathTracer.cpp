@@ -1,5 +1,6 @@
 // PathTracer.cpp — see PathTracer.h.
 #include "PathTracer.h"
+#include "PathTracer_FileImporter.h"
 
 #include <chrono>
 #include <iostream>
@@ -62,7 +63,12 @@ bool PathTracer_Main(uint image_width, uint image_height, uint numImagesToRender
             throw std::runtime_error(m.str());
         }
         if (superSampling) throw std::runtime_error("superSampling is not functional in the reference (empty X2inv.cl) and not supported");
-        if (exportScene) throw std::runtime_error("scene export (.pth) is outside the hot path and not supported");
+        if (exportScene)
+        {
+            // reference :67-71: dump the imported scene (after the BVH build has ordered the triangles) for a later run
+            PathTracer_PrintSection("EXPORTING SCENE");
+            PathTracer_Export();
+        }
 
         PathTracer_PrintSection("SETTING CUDA CONTEXT");
         start = nowMs();
@@ -212,6 +218,16 @@ void PathTracer_PrintBVHCharacteristics()
     BVHCharacteristics c = BVH_GetCharacteristics(globalVars.bvh);
     CONSOLE_LOG << "BVH : nodes " << c.nNodes << ", leafs " << c.nLeafs << ", depth " << c.minDepth << ".." << c.maxDepth << ", leaf size "
                 << c.minLeafSize << ".." << c.maxLeafSize << ENDL;
+}
+
+// reference Controleur/PathTracer.cpp:202-207 (the folder is settable instead of a build-time Windows path)
+static std::string g_sceneFolder = ".";
+void PathTracer_SetSceneFolder(const char *folder) { g_sceneFolder = folder ? folder : "."; }
+void PathTracer_Export()
+{
+    PathTracerFileImporter fileExporter(g_sceneFolder);
+    fileExporter.Initialize(globalVars);
+    fileExporter.Export();
 }
 
 void PathTracer_PrintSection(const char *section) { CONSOLE_LOG << ENDL << "**** " << section << " ****" << ENDL; }

@@ -27,6 +27,8 @@ void PathTracer_ComputeStatistics(uint numImageToRender, double loadingTime, dou
                                   double pathTracingTime, double memoryTime, double displayTime);
 void PathTracer_PrintBVHCharacteristics();
 void PathTracer_PrintSection(const char *section);
+void PathTracer_Export();                            // reference :202-207: sizes.pth / pointers.pth / textureData.pth (PathTracer_FileImporter.h)
+void PathTracer_SetSceneFolder(const char *folder);  // where PathTracer_Export writes (default "."; the reference hard-codes a folder)
 
 // New: keep the results of the last PathTracer_Main alive for callers that want the buffers (tests, the
 // Python binding). When set, PathTracer_Clear() is deferred until PathTracer_ReleaseResults().

@@ -2,11 +2,18 @@
 // (same call sequence: PathTracer_SetImporter + PathTracer_Main; parameters come from the command line
 // instead of being hard-coded, and the importer is the procedural one).
 //
-// usage: pathtracer_alone [scene] [width] [height] [numImages] [rayMaxDepth] [sampler 0|1|2] [mode 0|1] [save 0|1] [outdir]
+// usage: pathtracer_alone [scene] [width] [height] [numImages] [rayMaxDepth] [sampler 0|1|2] [mode 0|1] [save 0|1] [outdir] [exportdir]
+//   scene      a procedural scene name (cornell, gallery, atrium[:n], terrain[:n]) or file:<folder> = the .pth triple
+//              in <folder> (PathTracer_FileImporter.h, what the reference's PathTracerFileImporter reads)
+//   exportdir  if given, the imported scene is written there as sizes.pth / pointers.pth / textureData.pth before
+//              rendering (the reference's exportScene flag, Controleur/PathTracer.cpp:67-71)
 #include <cstdlib>
 #include <iostream>
 
+#include <cstring>
+
 #include "PathTracer.h"
+#include "PathTracer_FileImporter.h"
 #include "PathTracer_ProceduralImporter.h"
 
 int main(int argc, char **argv)
@@ -24,8 +31,11 @@ int main(int argc, char **argv)
     opt.readBackEvery = saveRenderedImages ? numImageToRender : 1;  // one picture at the end
     PathTracerNS::CUDA_SetOptions(opt);
 
-    PathTracerNS::PathTracer_SetImporter(new PathTracerNS::PathTracerProceduralImporter(scene));
-    bool success = PathTracerNS::PathTracer_Main(image_width, image_height, numImageToRender, saveRenderedImages, true, false, sampler,
+    const bool exportScene = argc > 10;
+    if (exportScene) PathTracerNS::PathTracer_SetSceneFolder(argv[10]);
+    if (std::strncmp(scene, "file:", 5) == 0) PathTracerNS::PathTracer_SetImporter(new PathTracerNS::PathTracerFileImporter(scene + 5));
+    else PathTracerNS::PathTracer_SetImporter(new PathTracerNS::PathTracerProceduralImporter(scene));
+    bool success = PathTracerNS::PathTracer_Main(image_width, image_height, numImageToRender, saveRenderedImages, true, exportScene, sampler,
                                                  rayMaxDepth, false, false);
     return success ? 0 : 1;
 }

@@ -5,6 +5,7 @@
 #include <string>
 
 #include "PathTracer.h"
+#include "PathTracer_FileImporter.h"
 #include "PathTracer_ProceduralImporter.h"
 #include "pathtracer_cuda.h"
 
@@ -46,6 +47,44 @@ PTH_API pth_scene *pth_scene_create(const char *name, uint32_t seed, uint32_t wi
         return nullptr;
     }
     return s;
+}
+
+// PathTracerFileImporter::Import: a scene from sizes.pth / pointers.pth / textureData.pth in `folder` (no BVH yet).
+PTH_API pth_scene *pth_scene_import(const char *folder, uint32_t width, uint32_t height, int loadSky)
+{
+    pth_scene *s = new pth_scene();
+    try
+    {
+        PathTracerFileImporter imp(folder);
+        imp.Initialize(s->gv);
+        imp.Import(width, height, loadSky != 0);
+    }
+    catch (std::exception const &e)
+    {
+        g_err = e.what();
+        GlobalVars &g = s->gv;
+        delete[] g.triangulation; delete[] g.lights; delete[] g.materiaux; delete[] g.textures; delete[] g.texturesData;
+        delete s;
+        return nullptr;
+    }
+    return s;
+}
+
+// PathTracerFileImporter::Export of the scene as it is now (after pth_scene_build_bvh: triangles in BVH order).
+PTH_API int pth_scene_export(pth_scene *s, const char *folder)
+{
+    try
+    {
+        PathTracerFileImporter exp(folder);
+        exp.Initialize(s->gv);
+        exp.Export();
+    }
+    catch (std::exception const &e)
+    {
+        g_err = e.what();
+        return 1;
+    }
+    return 0;
 }
 
 // BVH_Create of this repository (host/PathTracer_BVH.cpp). Permutes the triangles.

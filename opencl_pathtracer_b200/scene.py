@@ -51,6 +51,25 @@ class Scene:
         if build_bvh:
             self.build_bvh()
 
+    @classmethod
+    def from_files(cls, folder, width, height, load_sky=True, build_bvh=True):
+        """A scene from the reference's file triple sizes.pth / pointers.pth / textureData.pth (host/PathTracer_FileImporter.h,
+        counterpart of reference Controleur/PathTracer_FileImporter.cpp:67-146)."""
+        self = cls.__new__(cls)
+        self._lib = N.host_lib()
+        self._h = self._lib.pth_scene_import(str(folder).encode(), width, height, 1 if load_sky else 0)
+        if not self._h:
+            raise RuntimeError(self._lib.pth_last_error().decode())
+        self.name, self.width, self.height = "file:%s" % folder, width, height
+        if build_bvh:
+            self.build_bvh()
+        return self
+
+    def export(self, folder):
+        """Write the scene as it is now (triangles in BVH order once the BVH is built) — reference :15-63."""
+        if self._lib.pth_scene_export(self._h, str(folder).encode()) != 0:
+            raise RuntimeError(self._lib.pth_last_error().decode())
+
     def build_bvh(self):
         if self._lib.pth_scene_build_bvh(self._h) != 0:
             raise RuntimeError(self._lib.pth_last_error().decode())

@@ -241,3 +241,28 @@ def test_fast_bounce_like_rays(scene_factory, name, sky, flags, label):
     assert diff[regular].mean() <= 5e-3
     if flags & pt.FLAG_BVH2:
         assert diff[~regular].mean() <= 5e-3
+
+
+def test_scene_file_round_trip_renders_identically(scene_factory, tmp_path):
+    """A scene written to the reference's file triple and read back (host/PathTracer_FileImporter) renders bit-identically
+    when given the same BVH; with its own rebuilt BVH the primary hits still name the same triangles (by Triangle.id)."""
+    w, h = 128, 96
+    sc = scene_factory("gallery", w, h, True)
+    sc.export(tmp_path)
+    back = pt.Scene.from_files(tmp_path, w, h, load_sky=True, build_bvh=False)
+    back.set_bvh(sc.nodes(), sc.info.bvhSize, sc.info.bvhMaxDepth)
+    with pt.PathTracerCUDA(w, h) as a, pt.PathTracerCUDA(w, h) as b:
+        a.upload(sc)
+        b.upload(back)
+        a.render(0, 2)
+        b.render(0, 2)
+        ca, na = a.read_image()
+        cb, nb = b.read_image()
+        assert np.array_equal(ca.view(np.uint32), cb.view(np.uint32)) and np.array_equal(na, nb)
+        ids_a = sc.triangles()["id"][np.maximum(a.trace_primary(1)["hit"], 0)]
+    back.build_bvh()
+    with pt.PathTracerCUDA(w, h) as b:
+        b.upload(back)
+        hb = b.trace_primary(1)["hit"]
+        ids_b = back.triangles()["id"][np.maximum(hb, 0)]
+    assert (ids_a != ids_b).mean() <= 1e-3
