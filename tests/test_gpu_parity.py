@@ -171,6 +171,93 @@ def test_wide_bvh_hits_equal_bvh2_hits(scene_factory, name):
         assert abs(cb[..., :3].mean() / ca[..., :3].mean() - 1) <= 2e-3
 
 
+def test_rgb8_epilogue_and_add_image(scene_factory):
+    w, h = 64, 48
+    sc = scene_factory("cornell", w, h, False)
+    with pt.PathTracerCUDA(w, h) as r:
+        r.upload(sc)
+        r.render(0, 4)
+        color, nb = r.read_image()
+        rgb = r.read_rgb8()
+        exp = np.minimum(color[..., :3] * np.float32(255.0) / nb[..., None], np.float32(255.0)).astype(np.int32)
+        assert np.abs(rgb.astype(np.int32) - exp).max() <= 1
+        r.add_image(color, nb)
+        c2, n2 = r.read_image()
+        assert np.array_equal(c2, color + color) and np.array_equal(n2, nb + nb)
+
+
+def test_moving_camera_reset(scene_factory):
+    w, h = 64, 48
+    sc = scene_factory("cornell", w, h, False)
+    cam = sc.camera().copy()
+    with pt.PathTracerCUDA(w, h) as r:
+        r.upload(sc)
+        r.render(0, 1)
+        a, _ = r.read_image()
+        cam2 = cam.copy()
+        cam2[0:3] += np.float32(25.0)
+        r.set_camera(cam2)
+        r.reset()
+        r.render(0, 1)
+        b, nb = r.read_image()
+        assert (nb == 1).all() and not np.array_equal(a, b)
+        r.set_camera(cam)
+        r.reset()
+        r.render(0, 1)
+        c, _ = r.read_image()
+        assert np.array_equal(a.view(np.uint32), c.view(np.uint32))
+
+
+def test_error_paths(scene_factory):
+    with pytest.raises(pt.PathTracerError) as e:
+        pt.PathTracerCUDA(0, 10)
+    assert e.value.code == 1
+    with pt.PathTracerCUDA(32, 32) as r:
+        with pytest.raises(pt.PathTracerError) as e:
+            r.render(0, 1)
+        assert e.value.code == 4  # PTC_ERR_STATE: render before upload
+    with pytest.raises(pt.PathTracerError) as e:
+        pt.PathTracerCUDA(32, 32, ray_max_depth=1000)
+    assert e.value.code == 5
+
+
+def test_controller_drop_in(ptref, scene_factory):
+    """PathTracer_Main (C++ controller, reference call sequence) end to end vs the oracle's launch loop."""
+    w, h, spp = 80, 60, 4
+    out = pt.PathTracer_Main("cornell", w, h, spp, rayDepth=10)
+    sc = scene_factory("cornell", w, h, False)
+    ref = ptref.render(sc, w, h, 10, 0, 0, spp)
+    assert np.array_equal(out["imageRayNb"], ref["imageRayNb"])
+    bad = _rel_mismatch(out["imageColor"], ref["imageColor"]).mean()
+    assert bad <= 5e-3
+    assert out["rayDepths"].sum() == w * h * spp
+
+
+def test_gpu_against_committed_golden_vectors():
+    """Same checks against tests/golden/reference_vectors.npz (generated from the reference by tests/golden/make_golden.py),
+    so the parity claim does not depend on oracle/_ref being present on the GPU box."""
+    from golden_cases import CASES, key, load
+    g = load()
+    for name, w, h, sky, depth in CASES:
+        k = key(name)
+        sc = pt.Scene(name, w, h, load_sky=sky)
+        with pt.PathTracerCUDA(w, h, ray_max_depth=depth) as r:
+            r.upload(sc)
+            p = r.trace_primary(0)
+            rad = r.render_single(0)
+            r.render(0, 4)
+            color, nb = r.read_image()
+            d, b, t = r.read_stats()
+        for f in ("hit", "seed_after", "counts"):
+            assert np.array_equal(p[f], g[k + "_primary_" + f]), (name, f)
+        for f in ("st", "dist2", "dir"):
+            assert np.array_equal(p[f].view(np.uint32), g[k + "_primary_" + f].view(np.uint32)), (name, f)
+        assert _rel_mismatch(rad, g[k + "_radiance_it0"]).mean() <= 2e-3
+        assert np.array_equal(nb, g[k + "_acc4_imageRayNb"])
+        assert _rel_mismatch(color, g[k + "_acc4_imageColor"]).mean() <= 5e-3
+        assert np.abs(d.astype(np.int64) - g[k + "_acc4_rayDepths"].astype(np.int64)).sum() <= 4e-3 * w * h * 4 + 2
+
+
 def _surface_rays(scene, n, seed):
     """Rays like the ones a bounce shoots: origins 0.001 off random points of random triangles, random directions."""
     rng = np.random.default_rng(seed)
