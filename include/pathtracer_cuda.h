@@ -66,8 +66,12 @@ enum
     PTC_FLAG_STAGE_TIMING = 1u << 0, /* bracket every stage launch with CUDA events (ptc_read_counters) */
     PTC_FLAG_NO_VARIANCE = 1u << 1,  /* do not maintain imageV (only the dead supersampling path reads it) */
     PTC_FLAG_NO_GRAPH = 1u << 2,     /* launch stages directly instead of replaying a captured CUDA graph */
-    PTC_FLAG_BVH2 = 1u << 3          /* FAST mode: traverse the reference BVH2 itself instead of the 8-wide compressed BVH
+    PTC_FLAG_BVH2 = 1u << 3,         /* FAST mode: traverse the reference BVH2 itself instead of the 8-wide compressed BVH
                                         that ptc_upload_scene collapses it into (PARITY always walks the BVH2) */
+    PTC_FLAG_GPU_BVH = 1u << 4       /* FAST mode: ignore the caller's BVH (ptc_scene_view.bvh may be NULL / bvh_size 0, so
+                                        BVH_Create need not run at all) and build the 8-wide BVH on the device from the
+                                        triangles in the order given (csrc/pt_lbvh.cu). Hits are reported as indices into
+                                        that order. Not valid in PARITY mode or together with PTC_FLAG_BVH2. */
 };
 
 /* Replaces the `-D` build options of reference Controleur/PathTracer_OpenCL.cpp:292-314: all run-time here. */
@@ -216,6 +220,10 @@ typedef struct ptc_wide_bvh
     uint32_t reserved;
 } ptc_wide_bvh;
 PTC_API int ptc_wide_bvh_build(const ptc_scene_view *scene, ptc_wide_bvh *out);
+/* The wide BVH the context traverses (after ptc_upload_scene, FAST mode without PTC_FLAG_BVH2), read back from the device:
+ * the host-built one or, with PTC_FLAG_GPU_BVH, the one built on the device. reserved = device build time in microseconds
+ * (0 for the host build). Release with ptc_wide_bvh_free. */
+PTC_API int ptc_wide_bvh_read(ptc_ctx *ctx, ptc_wide_bvh *out);
 PTC_API void ptc_wide_bvh_free(ptc_wide_bvh *bvh);
 
 /* Measurement utility (roofline denominators of bench.py): read-only streaming of a `bytes`-sized device buffer, `repeats`

@@ -16,7 +16,7 @@ PTC_OK = 0
 PTC_ERR_INVALID, PTC_ERR_CUDA, PTC_ERR_NO_DEVICE, PTC_ERR_STATE, PTC_ERR_LIMIT, PTC_ERR_UNSUPPORTED = 1, 2, 3, 4, 5, 6
 SAMPLER_JITTERED, SAMPLER_RANDOM, SAMPLER_UNIFORM = 0, 1, 2
 MODE_PARITY, MODE_FAST = 0, 1
-FLAG_STAGE_TIMING, FLAG_NO_VARIANCE, FLAG_NO_GRAPH, FLAG_BVH2 = 1, 2, 4, 8
+FLAG_STAGE_TIMING, FLAG_NO_VARIANCE, FLAG_NO_GRAPH, FLAG_BVH2, FLAG_GPU_BVH = 1, 2, 4, 8, 16
 MAX_INTERSECTION_NUMBER = 5000
 
 
@@ -68,7 +68,7 @@ class SceneInfo(C.Structure):
 PTC_SYMBOLS = ["ptc_create", "ptc_upload_scene", "ptc_set_camera", "ptc_reset_accumulation", "ptc_render", "ptc_synchronize",
                "ptc_read_image", "ptc_read_variance", "ptc_read_stats", "ptc_read_rgb8", "ptc_add_image", "ptc_read_counters",
                "ptc_get_device_buffers", "ptc_trace_primary", "ptc_trace_rays", "ptc_render_single", "ptc_host_alloc", "ptc_host_free",
-               "ptc_last_error", "ptc_version", "ptc_device_count", "ptc_destroy", "ptc_wide_bvh_build", "ptc_wide_bvh_free", "ptc_measure_read_bandwidth"]
+               "ptc_last_error", "ptc_version", "ptc_device_count", "ptc_destroy", "ptc_wide_bvh_build", "ptc_wide_bvh_read", "ptc_wide_bvh_free", "ptc_measure_read_bandwidth"]
 
 _cuda = None
 _host = None
@@ -104,6 +104,7 @@ def cuda_lib():
     L.ptc_read_counters.argtypes = [vp, P(Counters)]
     L.ptc_get_device_buffers.argtypes = [vp, P(DeviceBuffers)]
     L.ptc_wide_bvh_build.argtypes = [P(SceneView), P(WideBvh)]
+    L.ptc_wide_bvh_read.argtypes = [vp, P(WideBvh)]
     L.ptc_wide_bvh_free.argtypes = [P(WideBvh)]
     L.ptc_wide_bvh_free.restype = None
     L.ptc_trace_primary.argtypes = [vp, u32, vp, vp, vp, vp, vp, vp]

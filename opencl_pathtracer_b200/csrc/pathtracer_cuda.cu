@@ -15,6 +15,7 @@
 #include <vector>
 
 #include "pt_launch.h"
+#include "pt_lbvh.h"
 #include "pt_wide_build.h"
 
 using namespace ptc;
@@ -47,6 +48,12 @@ struct DevBuf
         p = nullptr;
         n = 0;
     }
+    void adopt(T *ptr, size_t count)  // takes over a cudaMalloc'ed buffer
+    {
+        release();
+        p = ptr;
+        n = count;
+    }
 };
 }  // namespace
 
@@ -78,6 +85,9 @@ struct ptc_ctx
     DevBuf<DevTri> tris8;
     DevBuf<uint32_t> tri8Index;
     bool wide = false;
+    bool gpuBvh = false;      // PTC_FLAG_GPU_BVH: the wide BVH is built on the device, the caller's BVH is ignored
+    uint32_t wideDepth = 0;
+    float msGpuBuild = 0.f;
     SceneDev sc{};
     Camera cam{};
 
@@ -293,6 +303,12 @@ int ptc_create(const ptc_config *config, ptc_ctx **out_ctx)
     c->fast = config->mode == PTC_MODE_FAST;
     c->wide = c->fast && !(config->flags & PTC_FLAG_BVH2);
     if (const char *e = std::getenv("PTC_WIDE")) c->wide = c->fast && std::atoi(e) != 0;
+    c->gpuBvh = (config->flags & PTC_FLAG_GPU_BVH) != 0;
+    if (c->gpuBvh && (!c->fast || (config->flags & PTC_FLAG_BVH2) || !c->wide))
+    {
+        delete c;
+        return fail(nullptr, PTC_ERR_INVALID, "PTC_FLAG_GPU_BVH needs PTC_MODE_FAST without PTC_FLAG_BVH2 (PARITY walks the reference BVH2)");
+    }
     c->nPix = config->image_width * config->image_height;
     c->smCount = prop.multiProcessorCount;
     if (config->stream) c->stream = (cudaStream_t)config->stream;
@@ -372,7 +388,7 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
 {
     if (!ctx || !s) return PTC_ERR_INVALID;
     if (s->struct_size != sizeof(ptc_scene_view)) return fail(ctx, PTC_ERR_INVALID, "ptc_upload_scene: struct_size mismatch");
-    const uint32_t nT = s->triangulation_size, nN = s->bvh_size, nL = s->lights_size, nM = s->materiaux_size, nX = s->textures_size;
+    const uint32_t nT = s->triangulation_size, nN = ctx->gpuBvh ? 0u : s->bvh_size, nL = s->lights_size, nM = s->materiaux_size, nX = s->textures_size;
     const uint32_t nTexel = s->textures_data_size;
     if ((nT && !s->triangulation) || (nN && !s->bvh) || (nL && !s->lights) || (nM && !s->materiaux) || (nX && !s->textures) ||
         (nTexel && !s->textures_data) || !s->sky)
@@ -380,7 +396,8 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
     if (nL >= PTC_MAX_LIGHT_SIZE)  // reference PathTracer.cpp:60-65
         return fail(ctx, PTC_ERR_LIMIT, "The scene has too many lights : it has %u and should be under %u", nL, PTC_MAX_LIGHT_SIZE);
     if (nT >= kMaxTriangles) return fail(ctx, PTC_ERR_LIMIT, "too many triangles (%u, limit %u)", nT, kMaxTriangles);
-    if (nT && nN == 0) return fail(ctx, PTC_ERR_INVALID, "triangles without a BVH");
+    const bool gpuBvh = ctx->gpuBvh;
+    if (nT && nN == 0 && !gpuBvh) return fail(ctx, PTC_ERR_INVALID, "triangles without a BVH");
     if ((uint64_t)ctx->capacity * (nL ? nL : 1) >= (1ull << 32))
         return fail(ctx, PTC_ERR_LIMIT, "paths in flight (%zu) x lights (%u) exceeds 2^32: lower iterations_per_batch", ctx->capacity, nL);
     CK(cudaSetDevice(ctx->device));
@@ -389,7 +406,7 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
     std::vector<uint32_t> innerIndex(nN, 0xffffffffu);
     uint32_t nInner = 0, maxDepth = 0;
     std::vector<uint32_t> bigLeaf;
-    if (nT)
+    if (nT && !gpuBvh)
     {
         std::vector<uint8_t> seen(nN, 0);
         std::vector<std::pair<uint32_t, uint32_t>> stack;  // node, depth
@@ -432,7 +449,7 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
     };
     std::vector<DevNode> hNodes(nInner);
     uint32_t rootRef = kInvalidRef;
-    if (nT)
+    if (nT && !gpuBvh)
     {
         // zero-triangle leaves: give them an empty range that cannot alias a real big leaf
         for (uint32_t i = 0; i < nN; i++)
@@ -460,6 +477,7 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
     // ---- triangles
     std::vector<DevTri> hTris(nT);
     std::vector<DevShade> hShade(nT);
+    std::vector<float> hVerts(gpuBvh ? 9 * (size_t)nT : 0);  // device builder input: S1, S2, S3
     int badW = -1, badMat = -1;
 #pragma omp parallel for schedule(static)
     for (long long i = 0; i < (long long)nT; i++)
@@ -491,6 +509,11 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
         h.ids = make_uint4(t.materialWithPositiveNormalIndex, t.materialWithNegativeNormalIndex, t.id, 0u);
         h.pad = make_uint4(0, 0, 0, 0);
         hShade[i] = h;
+        if (gpuBvh)
+        {
+            float *v = &hVerts[9 * (size_t)i];
+            v[0] = t.S1.x; v[1] = t.S1.y; v[2] = t.S1.z; v[3] = t.S2.x; v[4] = t.S2.y; v[5] = t.S2.z; v[6] = t.S3.x; v[7] = t.S3.y; v[8] = t.S3.z;
+        }
     }
     if (badW >= 0) return fail(ctx, PTC_ERR_UNSUPPORTED, "triangle %d: S1.w, S2.w, S3.w differ (vertices must share one w lane)", badW);
     if (badMat >= 0) return fail(ctx, PTC_ERR_INVALID, "triangle %d: material index out of range", badMat);
@@ -530,7 +553,7 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
     // ---- FAST mode: the 8-wide compressed BVH (pt_wide_build.cu) and the intersection records in its order
     WideBvh wideBvh;
     std::vector<DevTri> hTris8;
-    if (ctx->wide)
+    if (ctx->wide && !gpuBvh)
     {
         std::string werr;
         if (!build_wide_bvh(s, wideBvh, werr)) return fail(ctx, PTC_ERR_INVALID, "%s", werr.c_str());
@@ -562,13 +585,39 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
     CK(up(ctx->tris8.p, hTris8.data(), sizeof(DevTri) * hTris8.size()));
     CK(up(ctx->tri8Index.p, wideBvh.triOrder.data(), sizeof(uint32_t) * wideBvh.triOrder.size()));
     CK(cudaStreamSynchronize(ctx->stream));  // host staging vectors die at return
+    uint32_t nNodes8 = (uint32_t)wideBvh.nodes.size(), wideDepth = wideBvh.depth;
+    ctx->msGpuBuild = 0.f;
+    if (gpuBvh)
+    {
+        // ---- PTC_FLAG_GPU_BVH: Morton-order LBVH + collapse on the device (pt_lbvh.cu)
+        DevBuf<float> dVerts;
+        CK(dVerts.alloc(hVerts.size()));
+        CK(up(dVerts.p, hVerts.data(), sizeof(float) * hVerts.size()));
+        DeviceWideBvh dw;
+        std::string werr;
+        const bool ok = build_wide_bvh_device(ctx->stream, dVerts.p, ctx->tris.p, nT, dw, werr);
+        dVerts.release();
+        if (!ok) return fail(ctx, PTC_ERR_CUDA, "%s", werr.c_str());
+        if (dw.depth + 2 > 64u)
+        {
+            cudaFree(dw.nodes); cudaFree(dw.tris8); cudaFree(dw.tri8Index);
+            return fail(ctx, PTC_ERR_LIMIT, "wide BVH of %u levels", dw.depth);
+        }
+        ctx->nodes8.adopt(dw.nodes, dw.nNodes);
+        ctx->tris8.adopt(dw.tris8, (size_t)dw.nNodes * kTriSlots);
+        ctx->tri8Index.adopt(dw.tri8Index, (size_t)dw.nNodes * kTriSlots);
+        nNodes8 = dw.nNodes;
+        wideDepth = dw.depth;
+        ctx->msGpuBuild = dw.msBuild;
+    }
+    ctx->wideDepth = wideDepth;
 
     SceneDev &sc = ctx->sc;
     sc.nodes = ctx->nodes.p; sc.tris = ctx->tris.p; sc.shade = ctx->shade.p; sc.materials = ctx->materials.p;
     sc.lights = ctx->lights.p; sc.textures = ctx->textures.p; sc.texels = ctx->texels.p;
     sc.bigLeafCount = bigLeaf.empty() ? nullptr : ctx->bigLeaf.p;
     sc.nodes8 = ctx->wide ? ctx->nodes8.p : nullptr; sc.tris8 = ctx->wide ? ctx->tris8.p : nullptr;
-    sc.tri8Index = ctx->wide ? ctx->tri8Index.p : nullptr; sc.nNodes8 = ctx->wide ? (uint32_t)wideBvh.nodes.size() : 0u;
+    sc.tri8Index = ctx->wide ? ctx->tri8Index.p : nullptr; sc.nNodes8 = ctx->wide ? nNodes8 : 0u;
     ctx->lc.wide = ctx->wide;
     sc.rootRef = rootRef; sc.nLights = nL; sc.nTriangles = nT; sc.sky = sky;
     ctx->cam = Camera{to4(s->camera_position), to4(s->camera_direction), to4(s->camera_right), to4(s->camera_up)};
@@ -576,7 +625,7 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
     if (!std::getenv("PTC_FULL_STACK"))
     {
         ctx->lc.stackDepth = (int)std::min<uint32_t>(32u, std::max<uint32_t>(4u, maxDepth + 1));
-        if (ctx->wide) ctx->lc.stackDepth = (int)std::max<uint32_t>(3u, wideBvh.depth + 2);  // the parked triangle group + one sibling group per level
+        if (ctx->wide) ctx->lc.stackDepth = (int)std::max<uint32_t>(3u, wideDepth + 2);  // the parked triangle group + one sibling group per level
         if (!std::getenv("PTC_CTAS_PER_SM")) ctx->lc.traverseGrid = ctx->smCount * traverse_ctas_per_sm(ctx->fast, ctx->wide, ctx->lc.stackDepth);
     }
     ctx->sceneLoaded = true;
@@ -602,6 +651,36 @@ int ptc_wide_bvh_build(const ptc_scene_view *scene, ptc_wide_bvh *out)
     }
     std::memcpy(out->nodes, w.nodes.data(), sizeof(DevNode8) * w.nodes.size());
     std::memcpy(out->tri_order, w.triOrder.data(), sizeof(uint32_t) * w.triOrder.size());
+    return PTC_OK;
+}
+
+int ptc_wide_bvh_read(ptc_ctx *ctx, ptc_wide_bvh *out)
+{
+    if (!ctx || !out) return PTC_ERR_INVALID;
+    std::memset(out, 0, sizeof(*out));
+    if (!ctx->sceneLoaded) return fail(ctx, PTC_ERR_STATE, "ptc_wide_bvh_read before ptc_upload_scene");
+    if (!ctx->wide) return fail(ctx, PTC_ERR_STATE, "ptc_wide_bvh_read: this context walks the BVH2");
+    CK(cudaSetDevice(ctx->device));
+    const size_t nNodes = ctx->nodes8.n, nRec = ctx->tri8Index.n;
+    out->n_nodes = (uint32_t)nNodes;
+    out->n_triangles = (uint32_t)nRec;
+    out->depth = ctx->wideDepth;
+    out->reserved = (uint32_t)(ctx->msGpuBuild * 1000.f);
+    out->nodes = std::malloc(std::max<size_t>(1, sizeof(DevNode8) * nNodes));
+    out->tri_order = (uint32_t *)std::malloc(std::max<size_t>(1, sizeof(uint32_t) * nRec));
+    if (!out->nodes || !out->tri_order)
+    {
+        ptc_wide_bvh_free(out);
+        return fail(ctx, PTC_ERR_INVALID, "ptc_wide_bvh_read: out of memory");
+    }
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    if (e == cudaSuccess && nNodes) e = cudaMemcpy(out->nodes, ctx->nodes8.p, sizeof(DevNode8) * nNodes, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess && nRec) e = cudaMemcpy(out->tri_order, ctx->tri8Index.p, sizeof(uint32_t) * nRec, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess)
+    {
+        ptc_wide_bvh_free(out);
+        return fail(ctx, PTC_ERR_CUDA, "ptc_wide_bvh_read: %s", cudaGetErrorString(e));
+    }
     return PTC_OK;
 }
 

@@ -50,20 +50,18 @@ PTC_HD inline double box_area(const BinNode &x)
     return 2.0 * (a * b + b * c + c * a);
 }
 
-// children must have been processed before their parent
-PTC_HD inline void collapse_costs(const BinNode *b, size_t n, const CollapseTables &t)
+// One node of the dynamic programme on values: x = the node, cl / cr = C(left, 1..7) / C(right, 1..7) (unused for a leaf).
+PTC_HD inline void collapse_costs_core(const BinNode &x, const float cl[7], const float cr[7], float c[7], uint8_t split[7], uint8_t &split8,
+                                       uint8_t &asLeaf)
 {
-    const BinNode &x = b[n];
     const double area = box_area(x);
-    float *c = t.cost + n * 7;
     if (x.left < 0)
     {
-        for (int i = 0; i < 7; i++) { c[i] = (float)(area * kTriCost); t.split[n * 7 + i] = 0; }
-        t.asLeaf[n] = 1;
-        t.split8[n] = 0;
+        for (int i = 0; i < 7; i++) { c[i] = (float)(area * kTriCost); split[i] = 0; }
+        asLeaf = 1;
+        split8 = 0;
         return;
     }
-    const float *cl = t.cost + (size_t)x.left * 7, *cr = t.cost + (size_t)x.right * 7;
     const float kInf = 3.0e38f;
     // best way to give j = 2..8 roots to the two subtrees
     float dist[9];
@@ -84,15 +82,23 @@ PTC_HD inline void collapse_costs(const BinNode *b, size_t n, const CollapseTabl
     const uint32_t cnt = x.count;
     const float leafCost = (!(cnt & kScattered) && cnt <= kLeafTriangles) ? (float)(area * cnt * kTriCost) : kInf;
     const float innerCost = dist[8] + (float)(area * kNodeCost);
-    t.split8[n] = distK[8];
-    t.asLeaf[n] = leafCost <= innerCost;
-    c[0] = t.asLeaf[n] ? leafCost : innerCost;
-    t.split[n * 7] = 0;
+    split8 = distK[8];
+    asLeaf = leafCost <= innerCost;
+    c[0] = asLeaf ? leafCost : innerCost;
+    split[0] = 0;
     for (int i = 2; i <= 7; i++)
     {
-        if (dist[i] < c[i - 2]) { c[i - 1] = dist[i]; t.split[n * 7 + i - 1] = distK[i]; }
-        else { c[i - 1] = c[i - 2]; t.split[n * 7 + i - 1] = 0; }
+        if (dist[i] < c[i - 2]) { c[i - 1] = dist[i]; split[i - 1] = distK[i]; }
+        else { c[i - 1] = c[i - 2]; split[i - 1] = 0; }
     }
+}
+
+// the same on the tables; children must have been processed before their parent
+PTC_HD inline void collapse_costs(const BinNode *b, size_t n, const CollapseTables &t)
+{
+    const BinNode &x = b[n];
+    const float *cl = x.left < 0 ? nullptr : t.cost + (size_t)x.left * 7, *cr = x.left < 0 ? nullptr : t.cost + (size_t)x.right * 7;
+    collapse_costs_core(x, cl, cr, t.cost + n * 7, t.split + n * 7, t.split8[n], t.asLeaf[n]);
 }
 
 PTC_HD inline int collapse_gather(const BinNode *b, int n, const CollapseTables &t, int child[8])

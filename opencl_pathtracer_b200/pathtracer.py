@@ -124,6 +124,19 @@ class PathTracerCUDA:
                                           out["dist2"].ctypes.data, out["dir"].ctypes.data, out["counts"].ctypes.data))
         return out
 
+    def wide_bvh(self):
+        """The wide BVH this context traverses, read back from the device: (nodes as scene.NODE8 records, tri_order[24 n],
+        depth, device build time in ms — 0 for the host-built tree)."""
+        from .scene import NODE8, _as_array
+        w = N.WideBvh()
+        self._ck(self._lib.ptc_wide_bvh_read(self._h, C.byref(w)))
+        try:
+            nodes = _as_array(w.nodes, w.n_nodes, NODE8).copy()
+            order = _as_array(w.tri_order, w.n_triangles, np.dtype("<u4")).copy()
+            return nodes, order, int(w.depth), w.reserved / 1000.0
+        finally:
+            self._lib.ptc_wide_bvh_free(C.byref(w))
+
     def measure_read_bandwidth(self, nbytes, repeats):
         """GB/s of a read-only streaming pass over an nbytes device buffer (L2 hit bandwidth if it fits the L2, else HBM)."""
         g = C.c_double()

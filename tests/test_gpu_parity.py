@@ -353,3 +353,53 @@ def test_scene_file_round_trip_renders_identically(scene_factory, tmp_path):
         hb = b.trace_primary(1)["hit"]
         ids_b = back.triangles()["id"][np.maximum(hb, 0)]
     assert (ids_a != ids_b).mean() <= 1e-3
+
+
+@pytest.mark.parametrize("name,sky,prebuilt", [("cornell", False, True), ("gallery", True, False), ("atrium:4", False, False),
+                                                ("atrium:16", False, True)])
+def test_device_built_wide_bvh(scene_factory, name, sky, prebuilt):
+    """PTC_FLAG_GPU_BVH (csrc/pt_lbvh.cu): the wide BVH built on the device from the bare triangle list — with or without a
+    BVH from the caller — has a valid structure (the checker of tests/test_wide_bvh.py on the tree read back from the device)
+    and finds the hits the host-collapsed reference BVH2 finds (differences only between candidates at the same distance)."""
+    from test_wide_bvh import check_wide_bvh
+    w, h = 256, 160
+    sc = scene_factory(name, w, h, sky) if prebuilt else pt.Scene(name, w, h, load_sky=sky, build_bvh=False)
+    ref_scene = scene_factory(name, w, h, sky)
+    with pt.PathTracerCUDA(w, h, mode=pt.MODE_FAST, flags=pt.FLAG_GPU_BVH) as g:
+        g.upload(sc)
+        nodes, order, depth, ms = g.wide_bvh()
+        print("%s: device build %.3f ms, %d nodes, depth %d, %.2f children per node" %
+              (name, ms, len(nodes), depth, (len(nodes) - 1 + (order != 0xffffffff).sum()) / max(len(nodes), 1)))
+        check_wide_bvh(nodes, order, depth, sc.triangles())
+        o, d = _surface_rays(ref_scene, 100000, 3)
+        b = g.trace_rays(o, d)
+        hg = g.trace_primary(2)
+        g.render(0, 4)
+        cg, ng = g.read_image()
+    with pt.PathTracerCUDA(w, h, mode=pt.MODE_FAST) as f:
+        f.upload(ref_scene)
+        a = f.trace_rays(o, d)
+        hf = f.trace_primary(2)
+        f.render(0, 4)
+        cf, nf = f.read_image()
+    # hit indices refer to each scene's own triangle order: compare through Triangle.id
+    ida = np.where(a["hit"] >= 0, ref_scene.triangles()["id"][np.maximum(a["hit"], 0)], -1)
+    idb = np.where(b["hit"] >= 0, sc.triangles()["id"][np.maximum(b["hit"], 0)], -1)
+    diff = ida != idb
+    tie = diff & (a["dist2"] == b["dist2"])
+    print("%s: device-built vs host-collapsed wide BVH on surface rays: %g differ, %g of them ties" % (name, diff.mean(), tie.mean()))
+    assert (diff & ~tie).sum() == 0
+    same = ~diff
+    assert np.array_equal(a["st"][same].view(np.uint32), b["st"][same].view(np.uint32))
+    pa = np.where(hf["hit"] >= 0, ref_scene.triangles()["id"][np.maximum(hf["hit"], 0)], -1)
+    pb = np.where(hg["hit"] >= 0, sc.triangles()["id"][np.maximum(hg["hit"], 0)], -1)
+    assert (pa != pb).mean() <= 1e-3
+    assert np.array_equal(ng, nf)
+    assert abs(cg[..., :3].mean() / cf[..., :3].mean() - 1) <= 5e-3
+
+
+def test_gpu_bvh_flag_needs_fast_mode():
+    with pytest.raises(pt.PathTracerError):
+        pt.PathTracerCUDA(32, 32, mode=pt.MODE_PARITY, flags=pt.FLAG_GPU_BVH)
+    with pytest.raises(pt.PathTracerError):
+        pt.PathTracerCUDA(32, 32, mode=pt.MODE_FAST, flags=pt.FLAG_GPU_BVH | pt.FLAG_BVH2)

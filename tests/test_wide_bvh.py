@@ -29,42 +29,55 @@ def _children(n, i):
     return out
 
 
-@pytest.mark.parametrize("name", ["cornell", "gallery", "atrium:8"])
-def test_wide_bvh_structure_and_boxes(scene_factory, name):
-    sc = scene_factory(name, 64, 48, load_sky=(name == "gallery"))
-    nodes, order, depth = sc.wide_bvh()
-    tris = sc.triangles()
+def check_wide_bvh(nodes, order, depth, tris):
+    """Structure of a wide BVH over `tris` (scene.TRIANGLE records in the order `order` refers to): every triangle exactly
+    once, every quantised child box contains its subtree and is at most one grid step loose, node count and depth."""
     nT = len(tris)
     assert len(order) == 24 * len(nodes)
     assert sorted(order[order != 0xffffffff].tolist()) == list(range(nT)), "every triangle exactly once"
     verts = np.stack([np.stack([tris[k][a] for a in "xyz"], -1) for k in ("S1", "S2", "S3")], 1).astype(np.float64)  # [tri, vertex, axis]
-    seen_nodes, seen_tris, max_depth = set(), 0, 0
-
-    def walk(i, d):
-        """returns the exact bounds of the subtree and checks every child box contains its subtree"""
-        nonlocal seen_tris, max_depth
-        assert i not in seen_nodes
-        seen_nodes.add(i)
-        max_depth = max(max_depth, d)
+    seen = np.zeros(len(nodes), bool)
+    seen_tris, max_depth = 0, 0
+    # iterative post-order: (node, depth, expanded)
+    bounds = {}
+    stack = [(0, 1, False)]
+    while stack:
+        i, d, expanded = stack.pop()
         n, lo, hi = _decode(nodes, i)
+        kids = _children(n, i)
+        if not expanded:
+            assert not seen[i]
+            seen[i] = True
+            max_depth = max(max_depth, d)
+            stack.append((i, d, True))
+            for s, kind, first, count in kids:
+                if kind == "inner":
+                    stack.append((first, d + 1, False))
+            continue
         blo, bhi = np.full(3, np.inf), np.full(3, -np.inf)
-        for s, kind, first, count in _children(n, i):
+        step = np.ldexp(1.0, n["e"].astype(np.int64) - 127)
+        for s, kind, first, count in kids:
             if kind == "inner":
-                clo, chi = walk(first, d + 1)
+                clo, chi = bounds.pop(first)
             else:
-                v = verts[order[first:first + count]].reshape(-1, 3)
+                idx = order[first:first + count]
+                assert (idx != 0xffffffff).all()
+                v = verts[idx].reshape(-1, 3)
                 clo, chi = v.min(0), v.max(0)
                 seen_tris += count
             assert (lo[:, s] <= clo).all() and (hi[:, s] >= chi).all(), "quantised box must contain the child"
-            # and not be looser than one grid step per side
-            step = np.ldexp(1.0, n["e"].astype(np.int64) - 127)
             assert (clo - lo[:, s] < step * 1.0001).all() and (hi[:, s] - chi < step * 1.0001).all()
             blo, bhi = np.minimum(blo, clo), np.maximum(bhi, chi)
         assert (n["p"].astype(np.float64) <= blo).all()
-        return blo, bhi
+        bounds[i] = (blo, bhi)
+    assert seen.all() and seen_tris == nT and max_depth == depth
 
-    walk(0, 1)
-    assert len(seen_nodes) == len(nodes) and seen_tris == nT and max_depth == depth
+
+@pytest.mark.parametrize("name", ["cornell", "gallery", "atrium:8"])
+def test_wide_bvh_structure_and_boxes(scene_factory, name):
+    sc = scene_factory(name, 64, 48, load_sky=(name == "gallery"))
+    nodes, order, depth = sc.wide_bvh()
+    check_wide_bvh(nodes, order, depth, sc.triangles())
 
 
 def _tri_hit(o, d, v):
