@@ -143,6 +143,8 @@ def main():
     ap.add_argument("--mode", default="fast", choices=["fast", "parity"])
     ap.add_argument("--spp-per-step", type=int, default=0, help="iterations per step per GPU (0 = the workload's default)")
     ap.add_argument("--ref-rows", type=int, default=128)
+    ap.add_argument("--bvh", choices=["host", "device"], default="host",
+                    help="FAST mode: wide BVH collapsed from the reference's host-built BVH2 (default) or built on the device (PTC_FLAG_GPU_BVH)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--progressive", type=int, default=0, metavar="FRAMES",
                     help="C5: time FRAMES progressive frames (1 spp each, moving camera, RGB8 read-back) instead of the throughput run")

@@ -32,7 +32,13 @@ def run_ours(args, rank, local_rank, world):
     S, K, WU = (args.spp_per_step or wl["spp"]), args.steps, args.warmup
     mode = pt.MODE_FAST if args.mode == "fast" else pt.MODE_PARITY
     n_pix = W * H
-    scene = pt.Scene(wl["scene"], W, H, load_sky=wl["sky"])
+    t0 = time.perf_counter()
+    scene = pt.Scene(wl["scene"], W, H, load_sky=wl["sky"], build_bvh=False)
+    t_import = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    scene.build_bvh()  # BVH_Create (the reference's host builder); the roofline / PARITY legs need it even with --bvh device
+    t_bvh = time.perf_counter() - t0
+    main_flags = pt.FLAG_NO_VARIANCE | (pt.FLAG_GPU_BVH if (args.bvh == "device" and args.mode == "fast") else 0)
     info = scene.info
     scene_mb = (info.triangulationSize * 64 + (info.bvhSize // 2) * 64) / 1e6  # DevTri + DevNode (one per inner node)
     stream = torch.cuda.Stream(device=dev)
@@ -58,8 +64,15 @@ def run_ours(args, rank, local_rank, world):
         return float(t.item())
 
     with torch.cuda.stream(stream):
-        r = pt.PathTracerCUDA(W, H, ray_max_depth=DEPTH, mode=mode, device=local_rank, flags=pt.FLAG_NO_VARIANCE, stream=stream.cuda_stream)
+        r = pt.PathTracerCUDA(W, H, ray_max_depth=DEPTH, mode=mode, device=local_rank, flags=main_flags, stream=stream.cuda_stream)
+        t0 = time.perf_counter()
         r.upload(scene)
+        t_upload = time.perf_counter() - t0
+        setup = {"import_s": t_import, "host_bvh_create_s": t_bvh, "upload_s": t_upload, "bvh": args.bvh}
+        if mode == pt.MODE_FAST:
+            wn, wo, wdepth, wms = r.wide_bvh()
+            setup.update({"wide_nodes": int(len(wn)), "wide_depth": wdepth, "device_build_ms": wms})
+            del wn, wo
         bufs = r.device_buffers()
         color = torch.as_tensor(_DevArray(bufs.image_color, n_pix * 4), device=dev)
         count = torch.as_tensor(_DevArray(bufs.image_ray_nb, n_pix), device=dev)
@@ -127,7 +140,7 @@ def run_ours(args, rank, local_rank, world):
         extra = {}
         if rank == 0:
             peaks, peak_kind = load_peaks()
-            rp = pt.PathTracerCUDA(W, H, ray_max_depth=DEPTH, mode=mode, device=local_rank, flags=pt.FLAG_NO_VARIANCE | pt.FLAG_STAGE_TIMING,
+            rp = pt.PathTracerCUDA(W, H, ray_max_depth=DEPTH, mode=mode, device=local_rank, flags=main_flags | pt.FLAG_STAGE_TIMING,
                                    stream=stream.cuda_stream)
             rp.upload(scene)
             rp.render(0, S, sync=True)
@@ -234,7 +247,7 @@ def run_ours(args, rank, local_rank, world):
                                  % (S * n_pix * 112 / 1e9, scene_mb, "inside" if scene_mb < 100 else "larger than")},
                 "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": 64, "d2h_bytes_per_step": n_pix * 20,
                         "ms_per_step": 1000.0 * e2e_s / K},
-                "gpu_launches": int(launches), "clocks": clk, "roofline": roof, "cpu_baseline": cpu, "mean_rgb": mean_rgb}
+                "gpu_launches": int(launches), "clocks": clk, "roofline": roof, "cpu_baseline": cpu, "mean_rgb": mean_rgb, "setup": setup}
         line.update(extra)
         print(json.dumps(line), flush=True)
     if world > 1:

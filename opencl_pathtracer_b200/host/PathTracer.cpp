@@ -1,6 +1,7 @@
 // PathTracer.cpp — see PathTracer.h.
 #include "PathTracer.h"
 #include "PathTracer_FileImporter.h"
+#include "pathtracer_cuda.h"
 
 #include <chrono>
 #include <iostream>
@@ -47,7 +48,9 @@ bool PathTracer_Main(uint image_width, uint image_height, uint numImagesToRender
 
         PathTracer_PrintSection("BUILDING BVH");
         start = nowMs();
-        BVH_Create(globalVars);
+        // CUDA_Options.flags & PTC_FLAG_GPU_BVH (FAST mode): the device builds its own wide BVH from the triangle list inside
+        // CUDA_InitializeMemory, so the host builder of the reference (:50, single-threaded) does not run at all
+        if (!(CUDA_GetOptions().flags & PTC_FLAG_GPU_BVH)) BVH_Create(globalVars);
         bvhBuildingTime = nowMs() - start;
 
         if (globalVars.bvhMaxDepth >= BVH_MAX_DEPTH)

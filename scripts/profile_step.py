@@ -12,9 +12,21 @@ mode = pt.MODE_PARITY if (len(sys.argv) > 2 and sys.argv[2] == "parity") else pt
 scene_name = sys.argv[3] if len(sys.argv) > 3 else "atrium"
 repeat = int(sys.argv[4]) if len(sys.argv) > 4 else 1
 W, H = 1920, 1080
-sc = pt.Scene(scene_name, W, H)
-with pt.PathTracerCUDA(W, H, mode=mode, flags=pt.FLAG_NO_VARIANCE | pt.FLAG_STAGE_TIMING, iterations_per_batch=spp) as r:
+gpu_bvh = os.environ.get("PTC_GPU_BVH") == "1"
+if scene_name.startswith("terrain"):
+    W, H = 3840, 2160
+t0 = time.perf_counter()
+sc = pt.Scene(scene_name, W, H, load_sky=scene_name.startswith("terrain"), build_bvh=not gpu_bvh)
+t_scene = time.perf_counter() - t0
+with pt.PathTracerCUDA(W, H, mode=mode, flags=pt.FLAG_NO_VARIANCE | pt.FLAG_STAGE_TIMING | (pt.FLAG_GPU_BVH if gpu_bvh else 0),
+                       iterations_per_batch=spp) as r:
+    t0 = time.perf_counter()
     r.upload(sc)
+    t_up = time.perf_counter() - t0
+    if mode == pt.MODE_FAST:
+        nodes, order, depth, ms = r.wide_bvh()
+        print("scene (import%s) %.2f s | upload %.2f s | wide BVH: %d nodes, depth %d, device build %.2f ms" %
+              ("" if gpu_bvh else " + BVH_Create", t_scene, t_up, len(nodes), depth, ms))
     r.render(0, spp, sync=True)
     r.reset()
     t0 = time.perf_counter()
