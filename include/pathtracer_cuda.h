@@ -68,10 +68,14 @@ enum
     PTC_FLAG_NO_GRAPH = 1u << 2,     /* launch stages directly instead of replaying a captured CUDA graph */
     PTC_FLAG_BVH2 = 1u << 3,         /* FAST mode: traverse the reference BVH2 itself instead of the 8-wide compressed BVH
                                         that ptc_upload_scene collapses it into (PARITY always walks the BVH2) */
-    PTC_FLAG_GPU_BVH = 1u << 4       /* FAST mode: ignore the caller's BVH (ptc_scene_view.bvh may be NULL / bvh_size 0, so
+    PTC_FLAG_GPU_BVH = 1u << 4,      /* FAST mode: ignore the caller's BVH (ptc_scene_view.bvh may be NULL / bvh_size 0, so
                                         BVH_Create need not run at all) and build the 8-wide BVH on the device from the
                                         triangles in the order given (csrc/pt_lbvh.cu). Hits are reported as indices into
                                         that order. Not valid in PARITY mode or together with PTC_FLAG_BVH2. */
+    PTC_FLAG_RUSSIAN_ROULETTE = 1u << 5 /* FAST mode: after MIN_REFLECTION_NUMBER = 5 bounces a path survives with probability
+                                        c = max throughput / (bounce - 5) and its throughput is divided by c (unbiased). The
+                                        reference has this stage disabled and commented out (Kernel/PathTracer_FullKernel_header.cl:12,
+                                        PathTracer_FullKernel.cl:1306-1314); the random streams then differ from the reference's. */
 };
 
 /* Replaces the `-D` build options of reference Controleur/PathTracer_OpenCL.cpp:292-314: all run-time here. */

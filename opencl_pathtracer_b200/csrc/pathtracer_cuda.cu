@@ -303,6 +303,11 @@ int ptc_create(const ptc_config *config, ptc_ctx **out_ctx)
     c->fast = config->mode == PTC_MODE_FAST;
     c->wide = c->fast && !(config->flags & PTC_FLAG_BVH2);
     if (const char *e = std::getenv("PTC_WIDE")) c->wide = c->fast && std::atoi(e) != 0;
+    if ((config->flags & PTC_FLAG_RUSSIAN_ROULETTE) && !c->fast)
+    {
+        delete c;
+        return fail(nullptr, PTC_ERR_INVALID, "PTC_FLAG_RUSSIAN_ROULETTE needs PTC_MODE_FAST (PARITY reproduces the reference's random streams)");
+    }
     c->gpuBvh = (config->flags & PTC_FLAG_GPU_BVH) != 0;
     if (c->gpuBvh && (!c->fast || (config->flags & PTC_FLAG_BVH2) || !c->wide))
     {

@@ -16,6 +16,7 @@
 namespace ptc
 {
 constexpr int kTraverseThreads = 128;
+constexpr uint32_t kFlagRussianRoulette = 1u << 5;  // PTC_FLAG_RUSSIAN_ROULETTE (include/pathtracer_cuda.h)
 constexpr int kStreamThreads = 256;
 
 // ------------------------------------------------------------------------------------------------ reset
@@ -407,7 +408,23 @@ __global__ void __launch_bounds__(kStreamThreads, 4) k_shade(SceneDev sc, FrameP
                 st.seed[p] = seed;
                 st.meta[p] = meta;
                 // :1294-1304 and the loop condition :1248
-                alive = !(clmax(T.x, clmax(T.y, T.z)) <= 0.001f) && refl < fp.maxDepth;
+                const float maxContribution = clmax(T.x, clmax(T.y, T.z));
+                alive = !(maxContribution <= 0.001f) && refl < fp.maxDepth;
+                // Russian roulette (opt-in, FAST only). The reference carries it disabled and commented out
+                // (:12-13, :1306-1314: coefficient maxContribution / (reflectionId - MIN_REFLECTION_NUMBER), MIN = 5), and as written
+                // there it would be biased (it keeps a path with probability 1 - c yet divides by c). Here: survive with
+                // probability c, divide the throughput by c — unbiased; one extra draw from the path's stream.
+                if (FAST && (fp.flags & kFlagRussianRoulette) && alive && refl > 5u)
+                {
+                    const float c = maxContribution / (float)(refl - 5u);
+                    if (c < 1.f)
+                    {
+                        alive = rng_next(seed) < c;
+                        T = T / c;
+                        st.thr[p] = T;
+                        st.seed[p] = seed;
+                    }
+                }
             }
         }
         // warp-aggregated append of the survivors to the next bounce's queue

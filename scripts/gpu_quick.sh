@@ -1,2 +1,2 @@
-timeout 900 python -m pytest tests -m gpu -q 2>&1 | tail -3
-timeout 600 python bench.py --bvh device --steps 4 --warmup 3 --no-cpu-baseline > gpurun_out/bench_devbvh_v9.json 2> gpurun_out/bench_devbvh_v9.err; tail -c 400 gpurun_out/bench_devbvh_v9.json; tail -3 gpurun_out/bench_devbvh_v9.err
+timeout 900 python -m pytest tests -m gpu -q -x -s -k "russian" 2>&1 | grep -v "^$" | tail -12 | cut -c1-300
+timeout 300 python scripts/profile_step.py 8 fast atrium 2

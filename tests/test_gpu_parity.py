@@ -403,3 +403,25 @@ def test_gpu_bvh_flag_needs_fast_mode():
         pt.PathTracerCUDA(32, 32, mode=pt.MODE_PARITY, flags=pt.FLAG_GPU_BVH)
     with pytest.raises(pt.PathTracerError):
         pt.PathTracerCUDA(32, 32, mode=pt.MODE_FAST, flags=pt.FLAG_GPU_BVH | pt.FLAG_BVH2)
+
+
+def test_russian_roulette_is_unbiased_and_cheaper(scene_factory):
+    """PTC_FLAG_RUSSIAN_ROULETTE (FAST, opt-in; the reference has the stage disabled): same image in expectation — the mean
+    of 64 spp agrees with the untruncated estimator — with fewer rays. No oracle exists for it: the
+    check is against this build's own FAST mode. PARITY refuses the flag."""
+    w, h, depth, spp = 160, 120, 24, 64
+    sc = scene_factory("cornell", w, h, False)
+    out = {}
+    for label, flags in (("plain", 0), ("rr", pt.FLAG_RUSSIAN_ROULETTE)):
+        with pt.PathTracerCUDA(w, h, ray_max_depth=depth, mode=pt.MODE_FAST, flags=flags) as r:
+            r.upload(sc)
+            r.render(0, spp, sync=True)
+            color, nb = r.read_image()
+            c = r.counters()
+            out[label] = (color[..., :3].astype(np.float64).sum() / nb.sum(), c["extension_rays"] + c["shadow_rays"])
+    (m0, rays0), (m1, rays1) = out["plain"], out["rr"]
+    print("Russian roulette: mean radiance %.5f vs %.5f, rays %.3g vs %.3g" % (m1, m0, rays1, rays0))
+    assert abs(m1 / m0 - 1) < 0.01
+    assert rays1 < 0.9 * rays0
+    with pytest.raises(pt.PathTracerError):
+        pt.PathTracerCUDA(32, 32, mode=pt.MODE_PARITY, flags=pt.FLAG_RUSSIAN_ROULETTE)
