@@ -425,3 +425,65 @@ def test_russian_roulette_is_unbiased_and_cheaper(scene_factory):
     assert rays1 < 0.9 * rays0
     with pytest.raises(pt.PathTracerError):
         pt.PathTracerCUDA(32, 32, mode=pt.MODE_PARITY, flags=pt.FLAG_RUSSIAN_ROULETTE)
+
+
+def _scene_with_lights(scene, tmp_path, lights):
+    """The scene re-imported from its .pth files with another light array (host/PathTracer_FileImporter)."""
+    import struct
+    from opencl_pathtracer_b200 import scene as S
+    scene.export(tmp_path)
+    i = scene.info
+    raw = (tmp_path / "sizes.pth").read_bytes()
+    counts = list(struct.unpack("<5I", raw[64:]))
+    ptr = (tmp_path / "pointers.pth").read_bytes()
+    tri_end = 336 * counts[0]
+    rest = ptr[tri_end + 64 * counts[1]:]
+    lights = np.ascontiguousarray(lights, dtype=S.LIGHT)
+    counts[1] = len(lights)
+    (tmp_path / "sizes.pth").write_bytes(raw[:64] + struct.pack("<5I", *counts))
+    (tmp_path / "pointers.pth").write_bytes(ptr[:tri_end] + lights.tobytes() + rest)
+    back = pt.Scene.from_files(tmp_path, scene.width, scene.height, load_sky=True, build_bvh=False)
+    back.set_bvh(scene.nodes(), i.bvhSize, i.bvhMaxDepth)
+    return back
+
+
+@pytest.mark.parametrize("n_lights", [0, 29])
+def test_light_count_extremes(ptref, scene_factory, tmp_path, n_lights):
+    """No light at all, and the most the reference accepts (MAX_LIGHT_SIZE - 1 = 29, Controleur/PathTracer.cpp:60-65): PARITY
+    radiance against the reference kernel, FAST against PARITY."""
+    w, h, depth = 96, 64, 5
+    base = scene_factory("gallery", w, h, True)
+    src = base.lights()
+    lights = np.zeros(n_lights, dtype=src.dtype)
+    rng = np.random.default_rng(4)
+    for k in range(n_lights):
+        lights[k] = src[k % len(src)]
+        lights[k]["power"] = src[k % len(src)]["power"] / 10
+        if int(lights[k]["type"]) != 0:
+            lights[k]["position"]["x"] += rng.uniform(-40, 40)
+            lights[k]["position"]["y"] += rng.uniform(-40, 40)
+    sc = _scene_with_lights(base, tmp_path, lights)
+    assert sc.info.lightsSize == n_lights
+    ref = ptref.render(sc, w, h, depth, 0, 2, 3)["imageColor"]
+    with pt.PathTracerCUDA(w, h, ray_max_depth=depth, mode=pt.MODE_PARITY) as p, pt.PathTracerCUDA(w, h, ray_max_depth=depth, mode=pt.MODE_FAST) as f:
+        p.upload(sc)
+        f.upload(sc)
+        got, fast = p.render_single(2), f.render_single(2)
+    assert np.isfinite(got).all()
+    bad = _rel_mismatch(got, ref).mean()
+    print("%d lights: PARITY vs reference %g of the pixels outside 1e-3; FAST vs PARITY %g" % (n_lights, bad, _rel_mismatch(fast, got).mean()))
+    assert bad <= 2e-3
+    assert _rel_mismatch(fast, got).mean() <= 5e-3
+    if n_lights == 0:
+        # only the sky can light a path: every pixel that sees geometry all the way is black
+        assert (got[..., :3] >= 0).all()
+
+
+def test_too_many_lights_is_refused(scene_factory, tmp_path):
+    base = scene_factory("cornell", 32, 32, False)
+    lights = np.repeat(base.lights()[:1], 30)
+    sc = _scene_with_lights(base, tmp_path, lights)
+    with pt.PathTracerCUDA(32, 32) as r:
+        with pytest.raises(pt.PathTracerError, match="too many lights") as e:
+            r.upload(sc)
+        assert e.value.code == 5
