@@ -17,6 +17,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
 
 import opencl_pathtracer_b200 as pt  # noqa: E402
 from oracle import ptref  # noqa: E402
+sys.path.insert(0, os.path.dirname(HERE))
+from golden_cases import surface_rays  # noqa: E402
 
 CASES = [("cornell", 64, 48, False, 10), ("gallery", 80, 60, True, 6), ("atrium:8", 64, 40, False, 5)]
 
@@ -57,6 +59,11 @@ def main():
         for k in ("hit", "st", "dist2", "dir", "seed_after", "counts"):
             out[key + "_primary_" + k] = p[k]
         out[key + "_radiance_it0"] = ptref.render(sc, w, h, depth, 0, 0, 1)["imageColor"]
+        o, d = surface_rays(sc, 4000, 21)  # rays that start on surfaces, as the bounces shoot them
+        tr = ptref.trace_rays(sc, o, d)
+        out[key + "_rays_origin"], out[key + "_rays_direction"] = o, d
+        for k in ("hit", "st", "dist2", "dir", "counts"):
+            out[key + "_rays_" + k] = tr[k]
         acc = ptref.render(sc, w, h, depth, 0, 0, 4)
         for k in ("imageColor", "imageRayNb", "rayDepths", "rayIntersectedBBx", "rayIntersectedTri"):
             out[key + "_acc4_" + k] = acc[k]

@@ -256,25 +256,19 @@ def test_gpu_against_committed_golden_vectors():
         assert np.array_equal(nb, g[k + "_acc4_imageRayNb"])
         assert _rel_mismatch(color, g[k + "_acc4_imageColor"]).mean() <= 5e-3
         assert np.abs(d.astype(np.int64) - g[k + "_acc4_rayDepths"].astype(np.int64)).sum() <= 4e-3 * w * h * 4 + 2
+        # bounce-like rays (oracle probe ptref_trace_rays): bit-exact
+        o, dd = _surface_rays(sc, 4000, 21)
+        assert np.array_equal(o, g[k + "_rays_origin"]) and np.array_equal(dd, g[k + "_rays_direction"]), "ray generator changed"
+        with pt.PathTracerCUDA(w, h, ray_max_depth=depth) as r:
+            r.upload(sc)
+            tr = r.trace_rays(o, dd)
+        for f in ("hit", "counts"):
+            assert np.array_equal(tr[f], g[k + "_rays_" + f]), (name, f)
+        for f in ("st", "dist2", "dir"):
+            assert np.array_equal(tr[f].view(np.uint32), g[k + "_rays_" + f].view(np.uint32)), (name, f)
 
 
-def _surface_rays(scene, n, seed):
-    """Rays like the ones a bounce shoots: origins 0.001 off random points of random triangles, random directions."""
-    rng = np.random.default_rng(seed)
-    t = scene.triangles()
-    k = rng.integers(0, len(t), n)
-    v = [np.stack([t[name][a][k] for a in "xyzw"], -1).astype(np.float32) for name in ("S1", "S2", "S3")]
-    u, w = rng.uniform(0, 1, n).astype(np.float32), rng.uniform(0, 1, n).astype(np.float32)
-    flip = u + w > 1
-    u[flip], w[flip] = 1 - u[flip], 1 - w[flip]
-    d = rng.normal(size=(n, 4)).astype(np.float32)
-    d[:, 3] = 0
-    d /= np.linalg.norm(d, axis=1, keepdims=True)
-    # a share of axis-parallel and grazing directions: zero components take the slow box test in the BVH2 walk
-    d[: n // 50, 1] = 0
-    d[n // 50: n // 25, 0] = 0
-    o = v[0] + u[:, None] * (v[1] - v[0]) + w[:, None] * (v[2] - v[0]) + np.float32(0.001) * d
-    return o.astype(np.float32), d.astype(np.float32)
+from golden_cases import surface_rays as _surface_rays  # noqa: E402
 
 
 @pytest.mark.parametrize("name,sky", [("cornell_specular", False), ("gallery", True), ("atrium:4", False)])

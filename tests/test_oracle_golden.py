@@ -67,6 +67,16 @@ def test_oracle_matches_golden(ptref, scene_factory, name, w, h, sky, depth):
     assert np.allclose((d * d).sum(1), 1, atol=1e-5)                     # unit directions
     hit = p["hit"] >= 0
     assert ((p["st"][hit] >= 0).all() and (p["st"][hit].sum(1) <= 1).all())  # barycentrics inside (kernel.cl:561)
+    # rays that start on surfaces (the bounces), through BVH_IntersectRay of the reference
+    from golden_cases import surface_rays
+    o, dd = surface_rays(sc, 4000, 21)
+    assert np.array_equal(o, g[k + "_rays_origin"]) and np.array_equal(dd, g[k + "_rays_direction"])
+    tr = ptref.trace_rays(sc, o, dd)
+    for f in ("hit", "counts"):
+        assert np.array_equal(tr[f], g[k + "_rays_" + f]), f
+    for f in ("st", "dist2", "dir"):
+        assert np.array_equal(tr[f].view(np.uint32), g[k + "_rays_" + f].view(np.uint32)), f
+    assert (tr["hit"] >= 0).mean() > 0.3
 
 
 def test_oracle_threads_do_not_change_result(ptref, scene_factory):
