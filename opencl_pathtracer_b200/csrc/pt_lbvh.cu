@@ -18,8 +18,10 @@
 // A Morton-order tree is a weaker partition than the reference's SAH sweep (more node visits per ray); it is offered as
 // an option (PTC_FLAG_GPU_BVH) for scenes whose set-up time matters, not as the default.
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_select.cuh>
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -110,7 +112,8 @@ __global__ void __launch_bounds__(kThreads) k_morton(const float *__restrict__ v
 }
 
 // leaf j (Morton position j) is binary node n - 1 + j
-__global__ void __launch_bounds__(kThreads) k_leaves(const float *__restrict__ verts, const uint32_t *__restrict__ perm, uint32_t n, BinNode *b)
+__global__ void __launch_bounds__(kThreads) k_leaves(const float *__restrict__ verts, const uint32_t *__restrict__ perm, uint32_t n, BinNode *b,
+                                                     CollapseTables tab)
 {
     const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= n) return;
@@ -124,8 +127,96 @@ __global__ void __launch_bounds__(kThreads) k_leaves(const float *__restrict__ v
     x.left = x.right = -1;
     x.first = j;
     x.count = 1;
-    b[(size_t)n - 1 + j] = x;
+    const size_t me = (size_t)n - 1 + j;
+    b[me] = x;
+    float c[7];
+    uint8_t sp[7], s8, leaf;
+    collapse_costs_core(x, nullptr, nullptr, c, sp, s8, leaf);
+    for (int i = 0; i < 7; i++) { tab.cost[me * 7 + i] = c[i]; tab.split[me * 7 + i] = sp[i]; }
+    tab.split8[me] = s8;
+    tab.asLeaf[me] = leaf;
 }
+
+// ---- PLOC (Meister, Bittner: "Parallel Locally-Ordered Clustering for Bounding Volume Hierarchy Construction", TVCG 2018):
+// the clusters (at first the leaves in Morton order) repeatedly merge with their nearest neighbour — nearest = smallest
+// surface area of the joint box — within a window of kPlocRadius positions, whenever the choice is mutual. Far better trees
+// than the radix tree for a few more passes over a shrinking array.
+constexpr int kPlocRadius = 16;
+constexpr uint32_t kNoCluster = 0xffffffffu;
+
+__global__ void __launch_bounds__(kThreads) k_ploc_nearest(const BinNode *__restrict__ b, const uint32_t *__restrict__ cluster, uint32_t nc,
+                                                           uint32_t *nearest)
+{
+    __shared__ float tile[kThreads + 2 * kPlocRadius][6];
+    const int base = (int)(blockIdx.x * kThreads) - kPlocRadius;
+    for (int t = threadIdx.x; t < kThreads + 2 * kPlocRadius; t += kThreads)
+    {
+        const int g = base + t;
+        if (g >= 0 && g < (int)nc)
+        {
+            const BinNode &x = b[cluster[g]];
+            for (int a = 0; a < 3; a++) { tile[t][a] = x.lo[a]; tile[t][3 + a] = x.hi[a]; }
+        }
+        else
+            for (int a = 0; a < 6; a++) tile[t][a] = a < 3 ? INFINITY : -INFINITY;
+    }
+    __syncthreads();
+    const int me = threadIdx.x + kPlocRadius;
+    const int g = base + me;
+    if (g >= (int)nc) return;
+    float best = INFINITY;
+    int bestJ = -1;
+    for (int d = -kPlocRadius; d <= kPlocRadius; d++)
+    {
+        const int j = me + d, gj = base + j;
+        if (d == 0 || gj < 0 || gj >= (int)nc) continue;
+        const float ex = fmaxf(tile[me][3], tile[j][3]) - fminf(tile[me][0], tile[j][0]);
+        const float ey = fmaxf(tile[me][4], tile[j][4]) - fminf(tile[me][1], tile[j][1]);
+        const float ez = fmaxf(tile[me][5], tile[j][5]) - fminf(tile[me][2], tile[j][2]);
+        const float area = ex * ey + ey * ez + ez * ex;  // symmetric in (me, j): both sides see the same value
+        if (area < best || bestJ < 0) { best = area; bestJ = gj; }  // ascending d: ties go to the lower index
+    }
+    nearest[g] = bestJ < 0 ? kNoCluster : (uint32_t)bestJ;
+}
+
+// mutual choices merge: the lower position keeps the new node, the higher one leaves the array
+__global__ void __launch_bounds__(kThreads) k_ploc_merge(BinNode *b, CollapseTables tab, const uint32_t *__restrict__ cluster,
+                                                         const uint32_t *__restrict__ nearest, uint32_t nc, uint32_t *out, uint32_t *nodeCounter)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nc) return;
+    const uint32_t j = nearest[i];
+    if (j == kNoCluster || nearest[j] != i)
+    {
+        out[i] = cluster[i];
+        return;
+    }
+    if (i > j)
+    {
+        out[i] = kNoCluster;
+        return;
+    }
+    const uint32_t idx = atomicAdd(nodeCounter, 1u);
+    const int l = (int)cluster[i], r = (int)cluster[j];
+    BinNode x;
+    for (int a = 0; a < 3; a++)
+    {
+        x.lo[a] = fminf(b[l].lo[a], b[r].lo[a]);
+        x.hi[a] = fmaxf(b[l].hi[a], b[r].hi[a]);
+    }
+    x.left = l;
+    x.right = r;
+    x.first = 0;
+    x.count = b[l].count + b[r].count;
+    b[idx] = x;
+    collapse_costs(b, idx, tab);  // the children are final: they were finished by earlier launches
+    out[i] = idx;
+}
+
+struct IsCluster
+{
+    __host__ __device__ bool operator()(const uint32_t &v) const { return v != 0xffffffffu; }
+};
 
 // length of the common prefix of the keys at Morton positions i and j, ties broken by the position itself; -1 outside
 __device__ __forceinline__ int delta(const uint64_t *__restrict__ keys, int n, int i, int j)
@@ -335,15 +426,65 @@ bool build_wide_bvh_device(cudaStream_t stream, const float *verts, const DevTri
     // ---- 3: binary radix tree
     LB_CK(cudaMemsetAsync(parent, 0xff, sizeof(int) * nBin, stream));
     LB_CK(cudaMemsetAsync(visits, 0, sizeof(int) * nT, stream));
-    k_leaves<<<grid, kThreads, 0, stream>>>(verts, perm, nT, b);
-    if (n > 1) k_internal<<<grid, kThreads, 0, stream>>>(keysSorted, n, b, parent);
-    // ---- 4: boxes + collapse costs
-    k_bottom_up<<<grid, kThreads, 0, stream>>>(n, b, parent, visits, tab);
-    LB_CK(cudaGetLastError());
+    k_leaves<<<grid, kThreads, 0, stream>>>(verts, perm, nT, b, tab);
+    int rootBin = 0;  // inner node 0 of the radix tree, or the only leaf (n - 1 + 0 = 0)
+    const char *which = std::getenv("PTC_GPU_BVH_BUILDER");
+    if (which && std::strcmp(which, "lbvh") == 0)
+    {
+        if (n > 1) k_internal<<<grid, kThreads, 0, stream>>>(keysSorted, n, b, parent);
+        // ---- 4: boxes + collapse costs
+        k_bottom_up<<<grid, kThreads, 0, stream>>>(n, b, parent, visits, tab);
+        LB_CK(cudaGetLastError());
+    }
+    else if (n > 1)
+    {
+        // ---- 3' + 4': PLOC; boxes and collapse costs are finished as each node is created
+        uint32_t *cl[2] = {nullptr, nullptr}, *nearest = nullptr, *merged = nullptr, *nSelected = nullptr;
+        void *selTemp = nullptr;
+        size_t selBytes = 0;
+        if (!S.alloc(cl[0], nT) || !S.alloc(cl[1], nT) || !S.alloc(nearest, nT) || !S.alloc(merged, nT) || !S.alloc(nSelected, 1))
+        {
+            err = "device BVH build: out of device memory";
+            return false;
+        }
+        LB_CK(cub::DeviceSelect::If(nullptr, selBytes, merged, cl[1], nSelected, n, IsCluster(), stream));
+        {
+            char *t = nullptr;
+            if (!S.alloc(t, selBytes)) { err = "device BVH build: out of device memory"; return false; }
+            selTemp = t;
+        }
+        // cluster[j] = leaf j; node indices 0 .. n - 2 are handed out as merges happen (counters[0] doubles as that counter here)
+        {
+            std::vector<uint32_t> init(nT);
+            for (uint32_t j = 0; j < nT; j++) init[j] = nT - 1 + j;
+            LB_CK(cudaMemcpyAsync(cl[0], init.data(), sizeof(uint32_t) * nT, cudaMemcpyHostToDevice, stream));
+            LB_CK(cudaMemsetAsync(counters, 0, sizeof(uint32_t) * 2, stream));
+            LB_CK(cudaStreamSynchronize(stream));
+        }
+        uint32_t nc = nT;
+        int cur = 0;
+        for (int pass = 0; nc > 1; pass++)
+        {
+            if (pass > 4096) { err = "device BVH build: clustering did not converge"; return false; }
+            const int g = (int)((nc + kThreads - 1) / kThreads);
+            k_ploc_nearest<<<g, kThreads, 0, stream>>>(b, cl[cur], nc, nearest);
+            k_ploc_merge<<<g, kThreads, 0, stream>>>(b, tab, cl[cur], nearest, nc, merged, counters);
+            LB_CK(cub::DeviceSelect::If(selTemp, selBytes, merged, cl[cur ^ 1], nSelected, (int)nc, IsCluster(), stream));
+            uint32_t left = 0;
+            LB_CK(cudaMemcpyAsync(&left, nSelected, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
+            LB_CK(cudaStreamSynchronize(stream));
+            if (left >= nc) { err = "device BVH build: clustering made no progress"; return false; }
+            nc = left;
+            cur ^= 1;
+        }
+        uint32_t root = 0;
+        LB_CK(cudaMemcpyAsync(&root, cl[cur], sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
+        LB_CK(cudaStreamSynchronize(stream));
+        rootBin = (int)root;
+    }
 
     // ---- 5: wide nodes, level by level. The node count is not known in advance: start with room for n / 3 nodes (the
     //         measured ratio is ~ n / 8.4) and repeat with twice as much if it did not fit.
-    const int rootBin = n > 1 ? 0 : 0;  // inner node 0, or the only leaf (n - 1 + 0 = 0)
     size_t capacity = std::max<size_t>(64, (size_t)nT / 3 + 16);
     DevNode8 *nodes = nullptr;
     uint32_t *order = nullptr;

@@ -70,11 +70,8 @@ struct Builder
         }
         n.left = l;
         n.right = r;
-        const uint32_t cl = b[l].count & ~kScattered, cr = b[r].count & ~kScattered;
-        const bool contiguous = !((b[l].count | b[r].count) & kScattered) &&
-                                (b[l].first + cl == b[r].first || b[r].first + cr == b[l].first);
-        n.first = std::min(b[l].first, b[r].first);
-        n.count = (cl + cr) | (contiguous ? 0u : kScattered);
+        n.first = 0;
+        n.count = b[l].count + b[r].count;
         b.push_back(n);
         return (int)b.size() - 1;
     }

@@ -27,10 +27,9 @@ struct BinNode  // binary tree over an ordered triangle array; leaves hold one t
 {
     float lo[3], hi[3];
     int left, right;   // -1 for leaves
-    uint32_t first;    // triangles of the subtree: positions [first, first + count) of the ordered array ...
-    uint32_t count;    // ... unless kScattered is set (then the subtree can never become a leaf child)
+    uint32_t first;    // leaves: position of the triangle in the ordered array (inner nodes: unused)
+    uint32_t count;    // triangles in the subtree
 };
-constexpr uint32_t kScattered = 0x80000000u;
 
 constexpr float kNodeCost = 1.0f;  // one wide-node visit (~250 instructions) against
 constexpr float kTriCost = 0.6f;   // one triangle test (~150); the result is flat between 0.15 and 1.2 (profiles/r01_sweeps.txt)
@@ -80,7 +79,7 @@ PTC_HD inline void collapse_costs_core(const BinNode &x, const float cl[7], cons
         distK[j] = k;
     }
     const uint32_t cnt = x.count;
-    const float leafCost = (!(cnt & kScattered) && cnt <= kLeafTriangles) ? (float)(area * cnt * kTriCost) : kInf;
+    const float leafCost = cnt <= kLeafTriangles ? (float)(area * cnt * kTriCost) : kInf;
     const float innerCost = dist[8] + (float)(area * kNodeCost);
     split8 = distK[8];
     asLeaf = leafCost <= innerCost;
@@ -215,13 +214,31 @@ PTC_HD inline bool collapse_encode(const BinNode *b, const CollapseTables &t, co
         }
         else
         {
-            // triangle k of the leaf in slot sl: bit 3 * sl + k of `valid`, record 3 * sl + k of this node
-            const uint32_t cnt = c.count & ~kScattered;
-            for (uint32_t k = 0; k < cnt && k < kLeafTriangles; k++)
+            // triangle k of the leaf in slot sl: bit 3 * sl + k of `valid`, record 3 * sl + k of this node. The (at most 3)
+            // triangles are the leaves of the binary subtree, left to right.
+            int walk[4], wp = 0;
+            uint32_t k = 0;
+            walk[wp++] = ci;
+            while (wp)
             {
-                valid |= 1u << (3 * sl + (int)k);
-                order[3 * sl + k] = perm ? perm[c.first + k] : c.first + k;
+                const BinNode &w = b[walk[--wp]];
+                if (w.left < 0)
+                {
+                    if (k < kLeafTriangles)
+                    {
+                        valid |= 1u << (3 * sl + (int)k);
+                        order[3 * sl + k] = perm ? perm[w.first] : w.first;
+                    }
+                    k++;
+                }
+                else if (wp + 2 <= 4)
+                {
+                    walk[wp++] = w.right;
+                    walk[wp++] = w.left;
+                }
+                else ok = false;
             }
+            if (k != c.count || k > kLeafTriangles) ok = false;
         }
     }
     n.eimask = ebyte[0] | (ebyte[1] << 8) | (ebyte[2] << 16) | (imask << 24);
