@@ -8,6 +8,8 @@
 //   k_shade       hit setup :1254-1275, direct light sum :901-954, Scene_ComputeRadiance :791-891,
 //                 sky :1281-1288, termination :1248, :1294-1304; ballot-compacts survivors into the next queue
 //   k_accumulate  statistics :1319-1331 and per-pixel accumulation :1333-1349
+#include <cstdlib>
+
 #include "pt_launch.h"
 #include "pt_shade.cuh"
 #include "pt_traverse.cuh"
@@ -641,6 +643,12 @@ static int occupancy_of(size_t bytes)
 
 int traverse_ctas_per_sm(bool fast, bool wide, int stackDepth)
 {
+    if (const char *e = std::getenv("PTC_CARVEOUT"))  // experiment: shared-memory carve-out in percent (what is left is L1)
+    {
+        const int v = std::atoi(e);
+        cudaFuncSetAttribute(k_trace<false, true, WideLane>, cudaFuncAttributePreferredSharedMemoryCarveout, v);
+        cudaFuncSetAttribute(k_trace<true, true, WideLane>, cudaFuncAttributePreferredSharedMemoryCarveout, v);
+    }
     const size_t bytes = stack_bytes(wide, stackDepth);
     int n, m;
     if (wide) { n = occupancy_of<false, true, WideLane>(bytes); m = occupancy_of<true, true, WideLane>(bytes); }
