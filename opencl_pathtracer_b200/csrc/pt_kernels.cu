@@ -134,6 +134,16 @@ struct StagedRays  // one per warp
 };
 constexpr size_t kStageBytes = sizeof(StagedRays) * (kTraverseThreads / 32);
 
+// connect only, one per warp: the hit point and shading normal of the 32 paths whose shadow rays are being staged, so that
+// the path state is loaded and the normal computed once per path instead of once per (path, light)
+struct PathGroup
+{
+    float4 q[32];
+    float4 ns[32];
+    uint32_t slot[32];
+};
+constexpr size_t kGroupBytes = sizeof(PathGroup) * (kTraverseThreads / 32);
+
 template <bool ANY, bool FAST, typename LaneT>
 __global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas) k_trace(SceneDev sc, PathState st, const uint32_t *__restrict__ queue,
                                                            Counters *__restrict__ cn, int bounce, uint32_t popMin, int stackDepth)
@@ -142,6 +152,7 @@ __global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas) k_trace(Sce
     extern __shared__ __align__(16) unsigned char smemRaw[];
     StackT *stk = reinterpret_cast<StackT *>(smemRaw) + threadIdx.x;
     StagedRays &stage = reinterpret_cast<StagedRays *>(smemRaw + sizeof(StackT) * stackDepth * kTraverseThreads)[threadIdx.x >> 5];
+    PathGroup &group = reinterpret_cast<PathGroup *>(smemRaw + sizeof(StackT) * stackDepth * kTraverseThreads + kStageBytes)[threadIdx.x >> 5];  // ANY only
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt = (1u << lane) - 1u;
     const unsigned full = 0xffffffffu;
@@ -149,12 +160,14 @@ __global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas) k_trace(Sce
     popMin &= 0xffu;
     const uint32_t count = cn->qcount[bounce];
     const uint32_t nL = ANY ? sc.nLights : 1u;
-    const uint32_t total = count * nL;  // upload_scene guarantees capacity * nLights < 2^32
+    const uint32_t total = ANY ? count : count * nL;  // work items drawn from the cursor: paths (connect draws groups of 32 paths)
     uint32_t *cursor = ANY ? &cn->curConnect[bounce] : &cn->curExtend[bounce];
     LaneT L;
     L.reset();
-    bool exhausted = false;
+    bool exhausted = ANY && nL == 0u;
     uint32_t qHead = 0, qCount = 0;  // staged rays [qHead, qCount) are waiting (warp-uniform)
+    uint32_t gMask = 0, gLight = 0;  // connect: lanes of the current path group that are lit, next light to stage for it
+    bool lastGroup = false;
     uint32_t p = 0, li = 0;
     uint32_t nbSum = 0, ntSum = 0, nRays = 0;
     while (true)
@@ -187,47 +200,83 @@ __global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas) k_trace(Sce
             // ---- staging: the whole warp prepares the next 32 items
             while (qHead == qCount && !exhausted)
             {
-                uint32_t base = 0;
-                if (lane == 0) base = atomicAdd(cursor, 32u);
-                base = __shfl_sync(full, base, 0);
-                if (base >= total || total - base <= 32u) exhausted = true;
-                const uint32_t k = base + lane;
-                bool valid = base < total && k < total;
                 float4 o = f4(0, 0, 0, 0), d = o;
                 float bound = INFINITY;
                 uint32_t item = 0;
-                if (valid)
+                bool valid = false;
+                if (!ANY)
                 {
-                    if (!ANY)
+                    uint32_t base = 0;
+                    if (lane == 0) base = atomicAdd(cursor, 32u);
+                    base = __shfl_sync(full, base, 0);
+                    if (base >= total || total - base <= 32u) exhausted = true;
+                    const uint32_t k = base + lane;
+                    valid = base < total && k < total;
+                    if (valid)
                     {
                         item = queue ? queue[k] : k;
                         o = st.org[item];
                         d = st.dir[item];
                     }
-                    else
+                }
+                else
+                {
+                    // a new group of 32 paths: state loads + hit point + shading normal, once per path
+                    if (gLight >= nL || gMask == 0u)
                     {
-                        // path-major: the shadow rays of one path are adjacent items (measured: light-major order is 10 % slower)
-                        const uint32_t kp = k / nL, l = k - kp * nL;
-                        const uint32_t pp = queue ? queue[kp] : kp;
-                        item = pp | (l << kLightShift);
-                        valid = !(st.occl[pp] & (kOcclUnlit | kOcclMiss));
-                        if (valid)
+                        uint32_t base = 0;
+                        if (lane == 0) base = atomicAdd(cursor, 32u);
+                        base = __shfl_sync(full, base, 0);
+                        if (base >= total)
+                        {
+                            exhausted = true;
+                            break;
+                        }
+                        lastGroup = total - base <= 32u;
+                        const uint32_t k = base + lane;
+                        bool lit = k < total;
+                        uint32_t pp = 0;
+                        if (lit)
+                        {
+                            pp = queue ? queue[k] : k;
+                            lit = !(st.occl[pp] & (kOcclUnlit | kOcclMiss));
+                        }
+                        if (lit)
                         {
                             const float4 h = st.hit[pp], po = st.org[pp], pd = st.dir[pp];
-                            const float4 q = f4(po.x + pd.x * h.w, po.y + pd.y * h.w, po.z + pd.z * h.w, po.w + pd.w * h.w);  // :538
-                            const DevLight light = sc.lights[l];
+                            group.q[lane] = f4(po.x + pd.x * h.w, po.y + pd.y * h.w, po.z + pd.z * h.w, po.w + pd.w * h.w);  // :538
                             if (FAST)
                             {
-                                // a light that sends exactly zero power towards the shading normal (:403-421: behind the surface,
-                                // outside a spot cone) adds +-0 to the pixel whether it is occluded or not: no ray
                                 const int tri = __float_as_int(h.x);
-                                const float4 Ns = shading_normal(&sc.shade[tri], __ldg(&sc.tris[tri].n), pd, h.y, h.z);
-                                valid = !(light_power_toward(light, q, Ns) == 0.0f);
+                                group.ns[lane] = shading_normal(&sc.shade[tri], __ldg(&sc.tris[tri].n), pd, h.y, h.z);
                             }
-                            shadow_setup(light, q, d, bound);
-                            o = q;
+                            group.slot[lane] = pp;
+                        }
+                        gMask = __ballot_sync(full, lit);
+                        gLight = 0;
+                        __syncwarp();
+                        if (gMask == 0u)
+                        {
+                            if (lastGroup) exhausted = true;
+                            continue;
                         }
                     }
+                    // the shadow rays of light gLight for the group (the group's rays of one light are adjacent items)
+                    const uint32_t l = gLight;
+                    valid = (gMask >> lane) & 1u;
+                    if (valid)
+                    {
+                        const float4 q = group.q[lane];
+                        const DevLight light = sc.lights[l];
+                        // FAST: a light that sends exactly zero power towards the shading normal (:403-421: behind the surface,
+                        // outside a spot cone) adds +-0 to the pixel whether it is occluded or not: no ray
+                        if (FAST) valid = !(light_power_toward(light, q, group.ns[lane]) == 0.0f);
+                        shadow_setup(light, q, d, bound);
+                        o = q;
+                        item = group.slot[lane] | (l << kLightShift);
+                    }
+                    gLight++;
+                    if (gLight >= nL && lastGroup) exhausted = true;
                 }
                 const unsigned m = __ballot_sync(full, valid);
                 if (valid)
@@ -628,9 +677,9 @@ void launch_read_stream(cudaStream_t s, int grid, const void *buf, size_t bytes,
     k_read_stream<<<grid, kStreamThreads, 0, s>>>(reinterpret_cast<const uint4 *>(buf), bytes / 32, repeats, sink);
 }
 
-static inline size_t stack_bytes(bool wide, int stackDepth)
+static inline size_t stack_bytes(bool wide, int stackDepth, bool any)
 {
-    return (size_t)stackDepth * kTraverseThreads * (wide ? sizeof(uint2) : sizeof(uint32_t)) + kStageBytes;
+    return (size_t)stackDepth * kTraverseThreads * (wide ? sizeof(uint2) : sizeof(uint32_t)) + kStageBytes + (any ? kGroupBytes : 0);
 }
 
 template <bool ANY, bool FAST, typename LaneT>
@@ -649,11 +698,11 @@ int traverse_ctas_per_sm(bool fast, bool wide, int stackDepth)
         cudaFuncSetAttribute(k_trace<false, true, WideLane>, cudaFuncAttributePreferredSharedMemoryCarveout, v);
         cudaFuncSetAttribute(k_trace<true, true, WideLane>, cudaFuncAttributePreferredSharedMemoryCarveout, v);
     }
-    const size_t bytes = stack_bytes(wide, stackDepth);
+    const size_t bytes = stack_bytes(wide, stackDepth, false), bytesAny = stack_bytes(wide, stackDepth, true);
     int n, m;
-    if (wide) { n = occupancy_of<false, true, WideLane>(bytes); m = occupancy_of<true, true, WideLane>(bytes); }
-    else if (fast) { n = occupancy_of<false, true, TraceLane>(bytes); m = occupancy_of<true, true, TraceLane>(bytes); }
-    else { n = occupancy_of<false, false, TraceLane>(bytes); m = occupancy_of<true, false, TraceLane>(bytes); }
+    if (wide) { n = occupancy_of<false, true, WideLane>(bytes); m = occupancy_of<true, true, WideLane>(bytesAny); }
+    else if (fast) { n = occupancy_of<false, true, TraceLane>(bytes); m = occupancy_of<true, true, TraceLane>(bytesAny); }
+    else { n = occupancy_of<false, false, TraceLane>(bytes); m = occupancy_of<true, false, TraceLane>(bytesAny); }
     n = n < m ? n : m;
     return n < 1 ? 1 : n;
 }
@@ -669,7 +718,7 @@ template <bool ANY>
 static void launch_trace(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const PathState &st, const uint32_t *queue,
                          Counters *cn, int bounce)
 {
-    const size_t smem = stack_bytes(lc.wide, lc.stackDepth);
+    const size_t smem = stack_bytes(lc.wide, lc.stackDepth, ANY);
     if (lc.wide) k_trace<ANY, true, WideLane><<<lc.traverseGrid, kTraverseThreads, smem, s>>>(sc, st, queue, cn, bounce, lc.refillMin, lc.stackDepth);
     else if (fast) k_trace<ANY, true, TraceLane><<<lc.traverseGrid, kTraverseThreads, smem, s>>>(sc, st, queue, cn, bounce, lc.refillMin, lc.stackDepth);
     else k_trace<ANY, false, TraceLane><<<lc.traverseGrid, kTraverseThreads, smem, s>>>(sc, st, queue, cn, bounce, lc.refillMin, lc.stackDepth);

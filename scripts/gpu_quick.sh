@@ -1,1 +1,3 @@
-for c in 50 66 75 100; do echo "CARVEOUT=$c"; PTC_CARVEOUT=$c timeout 300 python scripts/profile_step.py 8 fast atrium 2 | grep Msam | cut -c29-140; done
+timeout 900 python -m pytest tests -m gpu -q -x 2>&1 | tail -4
+timeout 300 python scripts/profile_step.py 8 fast atrium 2 | grep Msam
+timeout 300 python scripts/profile_step.py 8 parity atrium 1 | grep Msam
