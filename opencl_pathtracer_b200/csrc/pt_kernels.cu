@@ -270,7 +270,12 @@ __global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas) k_trace(Sce
                         const DevLight light = sc.lights[l];
                         // FAST: a light that sends exactly zero power towards the shading normal (:403-421: behind the surface,
                         // outside a spot cone) adds +-0 to the pixel whether it is occluded or not: no ray
-                        if (FAST) valid = !(light_power_toward(light, q, group.ns[lane]) == 0.0f);
+                        // (the light is also marked as occluded, so that the shade stage skips its term without evaluating it)
+                        if (FAST && light_power_toward(light, q, group.ns[lane]) == 0.0f)
+                        {
+                            valid = false;
+                            atomicOr(&st.occl[group.slot[lane]], 1u << l);
+                        }
                         shadow_setup(light, q, d, bound);
                         o = q;
                         item = group.slot[lane] | (l << kLightShift);
@@ -400,11 +405,14 @@ __global__ void __launch_bounds__(kStreamThreads, 4) k_shade(SceneDev sc, FrameP
                 if (!FAST || mat.type == 0 || mat.type == 3)
                     for (uint32_t li = 0; li < sc.nLights; li++)
                     {
+                        // an occluded light adds nothing (:944-949); neither does one the connect stage found to send zero power
+                        // (its term would be +-0): both carry their bit, and the term is not evaluated at all
+                        if ((occl >> li) & 1u) continue;
                         const DevLight l = sc.lights[li];
                         const float4 full = (l.type == 0) ? -l.direction : (l.position - q);
                         const float4 ldir = normalize4(full);
                         const float brdf = material_brdf(mat.type, -ldir, Ns, d);
-                        if (!((occl >> li) & 1u)) L = L + (light_power_toward(l, q, Ns) * brdf) * l.color;
+                        L = L + (light_power_toward(l, q, Ns) * brdf) * l.color;
                     }
                 // :791-891
                 float4 Nref = d, out = d;
