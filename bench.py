@@ -156,8 +156,7 @@ def main():
         run_reference(args, rank)
         return
     if args.progressive:
-        if rank == 0:
-            run_progressive(args)
+        run_progressive(args, rank, local_rank, world)
         return
     run_ours(args, rank, local_rank, world)
 

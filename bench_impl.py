@@ -254,10 +254,13 @@ def run_ours(args, rank, local_rank, world):
         dist.destroy_process_group()
 
 
-def run_progressive(args):
+def run_progressive(args, rank=0, local_rank=0, world=1):
     """BASELINE.json configs[4] (C5): progressive 1 spp/frame 1080p with a moving camera (the Maya viewport mode).
     Per frame, through the C ABI with host buffers: ptc_set_camera -> ptc_reset_accumulation -> ptc_render(1 iteration) ->
-    ptc_read_rgb8 (display epilogue on the device, 3 bytes/pixel back to the host). Reports p50 / p99 frame latency."""
+    ptc_read_rgb8 (display epilogue on the device, 3 bytes/pixel back to the host). Reports p50 / p99 frame latency.
+    On N > 1 GPUs a 1-spp frame cannot be split by iterations: every rank renders interleaved 8-row stripes
+    (ptc_set_pixel_stripes), converts them to RGB8 on the device, and one uint8 NCCL reduce composes the frame on rank 0,
+    which copies it to pinned host memory; latency = rank 0's wall clock per frame."""
     import numpy as np
     import torch
 
@@ -266,6 +269,13 @@ def run_progressive(args):
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — this benchmark has no CPU fallback")
+    import torch.distributed as dist
+    from opencl_pathtracer_b200.sharding import STRIPE_ROWS, compose_stripes, display_tensor
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    stream = torch.cuda.Stream(device=dev)
     wl = WORKLOADS[args.workload]
     W, H = wl["size"]
     scene = pt.Scene(wl["scene"], W, H, load_sky=wl["sky"])
@@ -291,19 +301,35 @@ def run_progressive(args):
     mode = pt.MODE_FAST if args.mode == "fast" else pt.MODE_PARITY
     frames, warm = args.progressive, max(3, args.warmup)
     lat = []
-    with pt.PathTracerCUDA(W, H, ray_max_depth=DEPTH, mode=mode, device=0, flags=pt.FLAG_NO_VARIANCE, iterations_per_batch=1) as r:
+    with pt.PathTracerCUDA(W, H, ray_max_depth=DEPTH, mode=mode, device=local_rank, stream=stream.cuda_stream, flags=pt.FLAG_NO_VARIANCE,
+                           iterations_per_batch=1) as r:
         r.upload(scene)
-        rgb = np.empty((H, W, 3), dtype=np.uint8)
-        c0 = None
+        if world > 1:
+            r.set_pixel_stripes(STRIPE_ROWS, rank, world)
+            frame = display_tensor(r, dev)
+            host = torch.empty(H * W * 3, dtype=torch.uint8, pin_memory=True)
+            rgb = host.numpy().reshape(H, W, 3)
+        else:
+            rgb = np.empty((H, W, 3), dtype=np.uint8)
         for f in range(warm + frames):
             if f == warm:
-                c0 = r.counters()["kernel_launches"]
+                if world > 1:
+                    dist.barrier()
+                torch.cuda.synchronize()
                 t_all = time.perf_counter()
             t0 = time.perf_counter()
             r.set_camera(rotated(np.radians(0.5) * f))
             r.reset()
             r.render(f, 1)
-            r._ck(r._lib.ptc_read_rgb8(r._h, rgb.ctypes.data))
+            if world > 1:
+                r.convert_rgb8()
+                with torch.cuda.stream(stream):
+                    compose_stripes(frame, dst=0)
+                    if rank == 0:
+                        host.copy_(frame, non_blocking=True)
+                stream.synchronize()
+            else:
+                r._ck(r._lib.ptc_read_rgb8(r._h, rgb.ctypes.data))
             if f >= warm:
                 lat.append((time.perf_counter() - t0) * 1e3)
         total = time.perf_counter() - t_all
@@ -311,13 +337,21 @@ def run_progressive(args):
         r.reset()
         r.render(0, 1, sync=True)
         per_frame = r.counters()["kernel_launches"] + 1  # + the RGB8 epilogue kernel
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank != 0:
+        return
     lat.sort()
     p50, p99 = lat[len(lat) // 2], lat[min(len(lat) - 1, int(len(lat) * 0.99))]
-    line = {"metric": "frame latency p50 (progressive 1 spp/frame, moving camera)", "value": p50, "unit": "ms", "n_gpus": 1, "steps": frames,
-            "warmup": warm, "ms_per_step": 1e3 * total / frames, "higher_is_better": False, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+    per = "ptc_set_camera + ptc_reset_accumulation + ptc_render(1) + ptc_read_rgb8" if world == 1 else \
+        "per rank: ptc_set_camera + ptc_reset_accumulation + ptc_render(1) of its 8-row stripes + ptc_convert_rgb8; uint8 NCCL reduce to rank 0; copy to pinned host"
+    line = {"metric": "frame latency p50 (progressive 1 spp/frame, moving camera)", "value": p50, "unit": "ms", "n_gpus": world, "steps": frames,
+            "warmup": warm, "ms_per_step": 1e3 * total / frames, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "p99_ms": p99, "frames_per_s": frames / total, "samples_per_s": frames * W * H / total,
             "config": {"workload": "C5: " + wl["desc"] + "; camera orbits 0.5 deg/frame, accumulation reset every frame", "image": [W, H],
-                       "ray_max_depth": DEPTH, "mode": args.mode, "per_frame": "ptc_set_camera + ptc_reset_accumulation + ptc_render(1) + ptc_read_rgb8"},
+                       "ray_max_depth": DEPTH, "mode": args.mode, "per_frame": per,
+                       "parallelism": "whole frame on one GPU" if world == 1 else "interleaved %d-row stripes x%d, one uint8 NCCL reduce per frame" % (STRIPE_ROWS, world)},
             "e2e": {"value": p50, "unit": "ms", "h2d_bytes_per_step": 64, "d2h_bytes_per_step": W * H * 3},
-            "gpu_launches": int(per_frame) * frames, "mean_rgb8": float(rgb.mean())}
+            "gpu_launches": int(per_frame) * frames * world, "mean_rgb8": float(rgb.mean())}
     print(json.dumps(line), flush=True)

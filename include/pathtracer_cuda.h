@@ -150,6 +150,7 @@ typedef struct ptc_device_buffers
     void *ray_bbx;      /* uint32[5000] */
     void *ray_tri;      /* uint32[5000] */
     void *stream;       /* cudaStream_t all of the above are written on */
+    void *rgb8;         /* uint8[3*W*H] display frame, filled by ptc_convert_rgb8 / ptc_read_rgb8 */
 } ptc_device_buffers;
 
 /* OpenCL_SetupContext: pick the device, allocate image/statistics accumulators (zeroed — the reference
@@ -173,6 +174,15 @@ PTC_API int ptc_render(ptc_ctx *ctx, uint32_t first_iteration, uint32_t n_iterat
 
 PTC_API int ptc_synchronize(ptc_ctx *ctx);
 
+/* Pixel shard for progressive rendering on several GPUs (a 1-spp frame cannot be split by iterations). The
+ * context renders only the image rows y with (y / stripe_rows) % world == rank — interleaved stripes, for load balance — of
+ * every following ptc_render; the random stream of a path depends on (x, y, iteration, W, H) alone
+ * (Kernel/PathTracer_FullKernel_header.cl:255-264), so each shard traces exactly the paths the whole-frame render traces for
+ * its rows. Accumulators of rows outside the shard stay as they are (zero after ptc_reset_accumulation), and
+ * ptc_convert_rgb8 writes 0 there, so the display frames of all shards SUM to the whole frame (one uint8 reduce over NCCL).
+ * stripe_rows = 0 returns to the whole frame. The parity probes (ptc_trace_primary, ptc_render_single) refuse a shard. */
+PTC_API int ptc_set_pixel_stripes(ptc_ctx *ctx, uint32_t stripe_rows, uint32_t rank, uint32_t world);
+
 /* clEnqueueReadBuffer of imageColor / imageRayNb (reference PathTracer_OpenCL.cpp:97-98); waits for
  * pending renders. Either pointer may be NULL. */
 PTC_API int ptc_read_image(ptc_ctx *ctx, float *image_color, float *image_ray_nb);
@@ -191,6 +201,10 @@ PTC_API int ptc_add_image(ptc_ctx *ctx, const float *image_color, const float *i
 
 PTC_API int ptc_read_counters(ptc_ctx *ctx, ptc_counters *out);
 PTC_API int ptc_get_device_buffers(ptc_ctx *ctx, ptc_device_buffers *out);
+
+/* The device half of ptc_read_rgb8: sum / count -> clamp -> RGB8 into the context's display buffer
+ * (ptc_device_buffers.rgb8), enqueued on the context's stream, no copy to the host. */
+PTC_API int ptc_convert_rgb8(ptc_ctx *ctx);
 
 /* Parity probe: generate + one closest-hit traversal for every pixel of one iteration, without touching
  * the accumulators. hit = triangle index in BVH order or -1; st = (s,t); dist2 = squared hit distance;

@@ -48,7 +48,7 @@ class Counters(C.Structure):
 
 class DeviceBuffers(C.Structure):
     _fields_ = [("image_color", C.c_void_p), ("image_ray_nb", C.c_void_p), ("image_v", C.c_void_p), ("ray_depths", C.c_void_p),
-                ("ray_bbx", C.c_void_p), ("ray_tri", C.c_void_p), ("stream", C.c_void_p)]
+                ("ray_bbx", C.c_void_p), ("ray_tri", C.c_void_p), ("stream", C.c_void_p), ("rgb8", C.c_void_p)]
 
 
 class WideBvh(C.Structure):
@@ -66,7 +66,7 @@ class SceneInfo(C.Structure):
 
 # every symbol include/pathtracer_cuda.h declares (tests check that the library exports all of them)
 PTC_SYMBOLS = ["ptc_create", "ptc_upload_scene", "ptc_set_camera", "ptc_reset_accumulation", "ptc_render", "ptc_synchronize",
-               "ptc_read_image", "ptc_read_variance", "ptc_read_stats", "ptc_read_rgb8", "ptc_add_image", "ptc_read_counters",
+               "ptc_read_image", "ptc_read_variance", "ptc_read_stats", "ptc_read_rgb8", "ptc_convert_rgb8", "ptc_set_pixel_stripes", "ptc_add_image", "ptc_read_counters",
                "ptc_get_device_buffers", "ptc_trace_primary", "ptc_trace_rays", "ptc_render_single", "ptc_host_alloc", "ptc_host_free",
                "ptc_last_error", "ptc_version", "ptc_device_count", "ptc_destroy", "ptc_wide_bvh_build", "ptc_wide_bvh_read", "ptc_wide_bvh_free", "ptc_measure_read_bandwidth"]
 
@@ -100,6 +100,8 @@ def cuda_lib():
     L.ptc_read_variance.argtypes = [vp, vp]
     L.ptc_read_stats.argtypes = [vp, vp, vp, vp]
     L.ptc_read_rgb8.argtypes = [vp, vp]
+    L.ptc_convert_rgb8.argtypes = [vp]
+    L.ptc_set_pixel_stripes.argtypes = [vp, u32, u32, u32]
     L.ptc_add_image.argtypes = [vp, vp, vp]
     L.ptc_read_counters.argtypes = [vp, P(Counters)]
     L.ptc_get_device_buffers.argtypes = [vp, P(DeviceBuffers)]

@@ -68,6 +68,7 @@ struct ptc_ctx
     std::string err;
 
     uint32_t nPix = 0, batchIters = 1;
+    uint32_t stripeRows = 0, stripeRank = 0, stripeWorld = 1, ownedPix = 0;  // pixel shard (ptc_set_pixel_stripes); 0 rows = whole frame
     size_t capacity = 0;  // path slots
     LaunchCfg lc{};
     int smCount = 0;
@@ -270,8 +271,11 @@ int ptc_reset_accumulation(ptc_ctx *ctx)
     CK(cudaMemsetAsync(ctx->rayBbx.p, 0, sizeof(uint32_t) * PTC_MAX_INTERSECTION_NUMBER, ctx->stream));
     CK(cudaMemsetAsync(ctx->rayTri.p, 0, sizeof(uint32_t) * PTC_MAX_INTERSECTION_NUMBER, ctx->stream));
     CK(cudaMemsetAsync(ctx->counters.p, 0, sizeof(Counters), ctx->stream));
-    CK(cudaStreamSynchronize(ctx->stream));
-    drainTimers(ctx);
+    if (ctx->cfg.flags & PTC_FLAG_STAGE_TIMING)  // pending stage timers must be read before their totals are cleared
+    {
+        CK(cudaStreamSynchronize(ctx->stream));
+        drainTimers(ctx);
+    }
     ctx->launches = ctx->launchesExtend = ctx->launchesConnect = 0;
     for (double &m : ctx->msStage) m = 0;
     return PTC_OK;
@@ -315,6 +319,7 @@ int ptc_create(const ptc_config *config, ptc_ctx **out_ctx)
         return fail(nullptr, PTC_ERR_INVALID, "PTC_FLAG_GPU_BVH needs PTC_MODE_FAST without PTC_FLAG_BVH2 (PARITY walks the reference BVH2)");
     }
     c->nPix = config->image_width * config->image_height;
+    c->ownedPix = c->nPix;
     c->smCount = prop.multiProcessorCount;
     if (config->stream) c->stream = (cudaStream_t)config->stream;
     else
@@ -707,9 +712,7 @@ int ptc_set_camera(ptc_ctx *ctx, const float camera[16])
 // ================================================================================================ render
 namespace
 {
-// One wavefront pass over `nIter` iterations starting at `first` (state must hold nIter * nPix slots).
-// accumulate = false leaves the per-path radiance in st.rad (parity probes). maxBounces < 0 = config depth.
-int runBatch(ptc_ctx *ctx, uint32_t first, uint32_t nIter, bool accumulate, int maxBounces)
+FrameParams frameParams(const ptc_ctx *ctx, uint32_t first, uint32_t nIter)
 {
     FrameParams fp{};
     fp.width = ctx->cfg.image_width;
@@ -719,7 +722,20 @@ int runBatch(ptc_ctx *ctx, uint32_t first, uint32_t nIter, bool accumulate, int 
     fp.firstIteration = first;
     fp.nIterations = nIter;
     fp.flags = ctx->cfg.flags;
-    const uint32_t nPaths = nIter * ctx->nPix;
+    fp.stripeRows = ctx->stripeRows;
+    fp.stripeRank = ctx->stripeRank;
+    fp.stripeWorld = ctx->stripeWorld;
+    fp.ownedPix = ctx->stripeRows ? ctx->ownedPix : ctx->nPix;
+    return fp;
+}
+
+// One wavefront pass over `nIter` iterations starting at `first` (state must hold nIter * nPix slots).
+// accumulate = false leaves the per-path radiance in st.rad (parity probes). maxBounces < 0 = config depth.
+int runBatch(ptc_ctx *ctx, uint32_t first, uint32_t nIter, bool accumulate, int maxBounces)
+{
+    const FrameParams fp = frameParams(ctx, first, nIter);
+    const uint32_t nPaths = nIter * fp.ownedPix;
+    if (nPaths == 0) return PTC_OK;  // a shard without rows
     Counters *cn = ctx->counters.p;
     cudaStream_t s = ctx->stream;
     launch_reset(s, cn, nPaths);
@@ -830,12 +846,36 @@ int ptc_read_rgb8(ptc_ctx *ctx, uint8_t *rgb)
 {
     if (!ctx || !rgb) return PTC_ERR_INVALID;
     CK(cudaSetDevice(ctx->device));
-    if (!ctx->rgb8.p) CK(ctx->rgb8.alloc((size_t)3 * ctx->nPix));
-    launch_rgb8(ctx->stream, ctx->img, ctx->nPix, ctx->rgb8.p);
-    ctx->launches++;
-    int rc = readBack(ctx, rgb, ctx->rgb8.p, (size_t)3 * ctx->nPix);
+    int rc = ptc_convert_rgb8(ctx);
+    if (rc == PTC_OK) rc = readBack(ctx, rgb, ctx->rgb8.p, (size_t)3 * ctx->nPix);
     if (rc != PTC_OK) return rc;
     return ptc_synchronize(ctx);
+}
+
+int ptc_convert_rgb8(ptc_ctx *ctx)
+{
+    if (!ctx) return PTC_ERR_INVALID;
+    CK(cudaSetDevice(ctx->device));
+    if (!ctx->rgb8.p) CK(ctx->rgb8.alloc((size_t)3 * ctx->nPix));
+    launch_rgb8(ctx->stream, ctx->img, frameParams(ctx, 0, 0), ctx->rgb8.p);
+    ctx->launches++;
+    return PTC_OK;
+}
+
+int ptc_set_pixel_stripes(ptc_ctx *ctx, uint32_t stripe_rows, uint32_t rank, uint32_t world)
+{
+    if (!ctx) return PTC_ERR_INVALID;
+    if (stripe_rows == 0)
+    {
+        ctx->stripeRows = 0; ctx->stripeRank = 0; ctx->stripeWorld = 1; ctx->ownedPix = ctx->nPix;
+        return PTC_OK;
+    }
+    if (world == 0 || rank >= world) return fail(ctx, PTC_ERR_INVALID, "ptc_set_pixel_stripes: rank %u of %u", rank, world);
+    uint32_t rows = 0;
+    for (uint32_t y = 0; y < ctx->cfg.image_height; y++) rows += (y / stripe_rows) % world == rank;
+    ctx->stripeRows = stripe_rows; ctx->stripeRank = rank; ctx->stripeWorld = world;
+    ctx->ownedPix = rows * ctx->cfg.image_width;
+    return PTC_OK;
 }
 
 int ptc_add_image(ptc_ctx *ctx, const float *image_color, const float *image_ray_nb)
@@ -901,6 +941,8 @@ int ptc_get_device_buffers(ptc_ctx *ctx, ptc_device_buffers *out)
     out->ray_bbx = ctx->rayBbx.p;
     out->ray_tri = ctx->rayTri.p;
     out->stream = ctx->stream;
+    if (!ctx->rgb8.p) CK(ctx->rgb8.alloc((size_t)3 * ctx->nPix));
+    out->rgb8 = ctx->rgb8.p;
     return PTC_OK;
 }
 
@@ -910,10 +952,9 @@ int ptc_trace_primary(ptc_ctx *ctx, uint32_t iteration, int32_t *hit, float *st,
 {
     if (!ctx) return PTC_ERR_INVALID;
     if (!ctx->sceneLoaded) return fail(ctx, PTC_ERR_STATE, "ptc_trace_primary before ptc_upload_scene");
+    if (ctx->stripeRows) return fail(ctx, PTC_ERR_STATE, "ptc_trace_primary: not available on a pixel shard (ptc_set_pixel_stripes)");
     CK(cudaSetDevice(ctx->device));
-    FrameParams fp{};
-    fp.width = ctx->cfg.image_width; fp.height = ctx->cfg.image_height; fp.maxDepth = ctx->cfg.ray_max_depth;
-    fp.sampler = ctx->cfg.sampler; fp.firstIteration = iteration; fp.nIterations = 1; fp.flags = ctx->cfg.flags;
+    const FrameParams fp = frameParams(ctx, iteration, 1);
     const uint32_t n = ctx->nPix;
     launch_reset(ctx->stream, ctx->counters.p, n);
     launch_generate(ctx->stream, ctx->lc, fp, ctx->cam, ctx->st);
@@ -967,7 +1008,7 @@ int ptc_trace_rays(ptc_ctx *ctx, uint32_t n, const float *origin, const float *d
     CK(cudaMemcpyAsync(dOrg.p, origin, sizeof(float4) * n, cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaMemcpyAsync(dDirIn.p, direction, sizeof(float4) * n, cudaMemcpyHostToDevice, ctx->stream));
     FrameParams fp{};
-    fp.width = n; fp.height = 1; fp.maxDepth = ctx->cfg.ray_max_depth; fp.nIterations = 1;
+    fp.width = n; fp.height = 1; fp.maxDepth = ctx->cfg.ray_max_depth; fp.nIterations = 1; fp.ownedPix = n;
     launch_reset(ctx->stream, ctx->counters.p, n);
     launch_probe_rays(ctx->stream, n, dOrg.p, dDirIn.p, ctx->st);
     launch_extend(ctx->stream, ctx->lc, ctx->fast, ctx->sc, ctx->st, nullptr, ctx->counters.p, 0);
@@ -990,6 +1031,7 @@ int ptc_render_single(ptc_ctx *ctx, uint32_t iteration, float *radiance)
 {
     if (!ctx || !radiance) return PTC_ERR_INVALID;
     if (!ctx->sceneLoaded) return fail(ctx, PTC_ERR_STATE, "ptc_render_single before ptc_upload_scene");
+    if (ctx->stripeRows) return fail(ctx, PTC_ERR_STATE, "ptc_render_single: not available on a pixel shard (ptc_set_pixel_stripes)");
     CK(cudaSetDevice(ctx->device));
     int rc = runBatch(ctx, iteration, 1, false, -1);
     if (rc != PTC_OK) return rc;

@@ -136,7 +136,20 @@ struct FrameParams
     uint32_t firstIteration;  // of this batch
     uint32_t nIterations;     // in this batch
     uint32_t flags;
+    // pixel shard (ptc_set_pixel_stripes): this context renders the rows y with (y / stripeRows) % stripeWorld == stripeRank;
+    // stripeRows = 0: the whole frame. ownedPix = pixels of the shard = path slots per iteration.
+    uint32_t stripeRows, stripeRank, stripeWorld;
+    uint32_t ownedPix;
 };
+
+// pixel `i` of the shard (row-major over the owned rows) -> pixel of the frame
+__device__ __forceinline__ uint32_t shard_pixel(const FrameParams &fp, uint32_t i)
+{
+    if (fp.stripeRows == 0u) return i;
+    const uint32_t oy = i / fp.width, x = i - oy * fp.width;
+    const uint32_t stripe = oy / fp.stripeRows, within = oy - stripe * fp.stripeRows;
+    return ((stripe * fp.stripeWorld + fp.stripeRank) * fp.stripeRows + within) * fp.width + x;
+}
 
 struct ImageDev
 {

@@ -34,14 +34,14 @@ __global__ void k_reset(Counters *cn, uint32_t nPaths)
 }
 
 // ------------------------------------------------------------------------------------------------ generate
-// slot k = localIteration * W*H + pixel; bounce 0 uses the identity queue (queue == nullptr).
+// slot k = localIteration * ownedPix + pixel of the shard; bounce 0 uses the identity queue (queue == nullptr).
 __global__ void __launch_bounds__(kStreamThreads) k_generate(FrameParams fp, Camera cam, PathState st)
 {
-    const uint32_t nPix = fp.width * fp.height;
+    const uint32_t nPix = fp.ownedPix;
     const uint32_t total = nPix * fp.nIterations;
     for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < total; k += gridDim.x * blockDim.x)
     {
-        const uint32_t li = k / nPix, pix = k - li * nPix;
+        const uint32_t li = k / nPix, pix = shard_pixel(fp, k - li * nPix);
         const uint32_t y = pix / fp.width, x = pix - y * fp.width;
         const uint32_t iter = fp.firstIteration + li;
         int seed = rng_init(x, y, iter, fp.width, fp.height);
@@ -555,14 +555,16 @@ __global__ void __launch_bounds__(kStreamThreads) k_accumulate(FrameParams fp, P
     for (int i = threadIdx.x; i <= kMaxBounces; i += blockDim.x) sDepth[i] = 0;
     for (uint32_t i = threadIdx.x; i < kHistBins; i += blockDim.x) sBbx[i] = sTri[i] = 0;
     __syncthreads();
-    const uint32_t nPix = fp.width * fp.height;
+    const uint32_t nPix = fp.ownedPix;
     uint32_t nPaths = 0;
     if (ORDERED)
     {
-        for (uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x; pix < nPix; pix += gridDim.x * blockDim.x)
+        for (uint32_t opix = blockIdx.x * blockDim.x + threadIdx.x; opix < nPix; opix += gridDim.x * blockDim.x)
+        {
+            const uint32_t pix = shard_pixel(fp, opix);
             for (uint32_t li = 0; li < fp.nIterations; li++)
             {
-                const uint32_t k = li * nPix + pix;
+                const uint32_t k = li * nPix + opix;
                 const float4 x = st.rad[k];
                 const uint32_t tp = target_pixel(st.sample[k], fp.width, fp.height);
                 count_path(sDepth, sBbx, sTri, st.meta[k], st.nbbx[k], st.ntri[k]);
@@ -570,6 +572,7 @@ __global__ void __launch_bounds__(kStreamThreads) k_accumulate(FrameParams fp, P
                 else add_sample_atomic(img, tp, x);
                 nPaths++;
             }
+        }
     }
     else
     {
@@ -633,14 +636,17 @@ __global__ void k_probe_rays(uint32_t n, const float4 *origin, const float4 *dir
 }
 
 // reference Alone/PathTracer_bitmap.cpp:259-279 (its test reads .x three times; a negative red marks the pixel)
-__global__ void k_rgb8(ImageDev img, uint32_t nPixels, uint8_t *rgb)
+// With a pixel shard (stripeRows != 0) the rows of other shards are written as 0, so that the frames of all shards sum to the
+// whole frame (one uint8 reduce composes it).
+__global__ void k_rgb8(ImageDev img, uint32_t nPixels, uint8_t *rgb, uint32_t width, uint32_t stripeRows, uint32_t stripeRank, uint32_t stripeWorld)
 {
     for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < nPixels; p += gridDim.x * blockDim.x)
     {
         const float4 c = img.color[p];
         const float n = img.rayNb[p];
         int r, g, b;
-        if (c.x < 0) { r = 255; g = 0; b = 0; }
+        if (stripeRows && ((p / width) / stripeRows) % stripeWorld != stripeRank) { r = g = b = 0; }
+        else if (c.x < 0) { r = 255; g = 0; b = 0; }
         else
         {
             r = (int)fminf(c.x * 255.f / n, 255.f);
@@ -770,7 +776,10 @@ void launch_probe_rays(cudaStream_t s, uint32_t n, const float4 *origin, const f
     k_probe_rays<<<1024, 256, 0, s>>>(n, origin, direction, st);
 }
 
-void launch_rgb8(cudaStream_t s, const ImageDev &img, uint32_t nPixels, uint8_t *rgb) { k_rgb8<<<1024, 256, 0, s>>>(img, nPixels, rgb); }
+void launch_rgb8(cudaStream_t s, const ImageDev &img, const FrameParams &fp, uint8_t *rgb)
+{
+    k_rgb8<<<1024, 256, 0, s>>>(img, fp.width * fp.height, rgb, fp.width, fp.stripeRows, fp.stripeRank, fp.stripeWorld);
+}
 
 void launch_add_image(cudaStream_t s, const ImageDev &img, uint32_t nPixels, const float4 *color, const float *rayNb)
 {

@@ -33,7 +33,7 @@ void launch_probe_rays(cudaStream_t s, uint32_t n, const float4 *origin, const f
 // roofline denominators (ptc_measure_read_bandwidth)
 void launch_read_stream(cudaStream_t s, int grid, const void *buf, size_t bytes, uint32_t repeats, uint32_t *sink);
 // display epilogue: sum / count -> clamp -> 8 bit (reference Alone/PathTracer_bitmap.cpp:259-279)
-void launch_rgb8(cudaStream_t s, const ImageDev &img, uint32_t nPixels, uint8_t *rgb);
+void launch_rgb8(cudaStream_t s, const ImageDev &img, const FrameParams &fp, uint8_t *rgb);
 void launch_add_image(cudaStream_t s, const ImageDev &img, uint32_t nPixels, const float4 *color, const float *rayNb);
 
 }  // namespace ptc

@@ -89,6 +89,15 @@ class PathTracerCUDA:
         self._ck(self._lib.ptc_read_rgb8(self._h, rgb.ctypes.data))
         return rgb
 
+    def convert_rgb8(self):
+        """Enqueue sum / count -> RGB8 into the device display buffer (device_buffers().rgb8); no host copy."""
+        self._ck(self._lib.ptc_convert_rgb8(self._h))
+
+    def set_pixel_stripes(self, stripe_rows, rank=0, world=1):
+        """Render only the rows y with (y // stripe_rows) % world == rank from now on (0 = whole frame).
+        See sharding.stripe_rows / sharding.compose_stripes."""
+        self._ck(self._lib.ptc_set_pixel_stripes(self._h, stripe_rows, rank, world))
+
     def add_image(self, color, ray_nb):
         color = np.ascontiguousarray(color, dtype=np.float32)
         ray_nb = np.ascontiguousarray(ray_nb, dtype=np.float32)

@@ -31,3 +31,17 @@ def surface_rays(scene, n, seed):
     d[n // 50: n // 25, 0] = 0
     o = v[0] + u[:, None] * (v[1] - v[0]) + w[:, None] * (v[2] - v[0]) + np.float32(0.001) * d
     return o.astype(np.float32), d.astype(np.float32)
+
+
+def rgb8_of(color, nb):
+    """numpy restatement of the display conversion (reference Alone/PathTracer_bitmap.cpp:259-279): sum * 255 / count clamped
+    to 255 in float32, truncated; a negative red sum marks the pixel pure red; pixels without samples are written as 0 here
+    (what ptc_convert_rgb8 does for rows outside a pixel shard)."""
+    c = color[..., :3].astype(np.float32)
+    n = nb.astype(np.float32)[..., None]
+    with np.errstate(divide="ignore", invalid="ignore"):
+        v = np.minimum(c * np.float32(255.0) / n, np.float32(255.0))
+    out = np.where(n > 0, v, 0).astype(np.int32).astype(np.uint8)
+    red = (color[..., 0] < 0) & (nb > 0)
+    out[red] = (255, 0, 0)
+    return out
