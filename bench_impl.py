@@ -304,13 +304,11 @@ def run_progressive(args, rank=0, local_rank=0, world=1):
     with pt.PathTracerCUDA(W, H, ray_max_depth=DEPTH, mode=mode, device=local_rank, stream=stream.cuda_stream, flags=pt.FLAG_NO_VARIANCE,
                            iterations_per_batch=1) as r:
         r.upload(scene)
+        host = torch.empty(H * W * 3, dtype=torch.uint8, pin_memory=True)  # the display frame lands in pinned host memory
+        rgb = host.numpy().reshape(H, W, 3)
         if world > 1:
             r.set_pixel_stripes(STRIPE_ROWS, rank, world)
             frame = display_tensor(r, dev)
-            host = torch.empty(H * W * 3, dtype=torch.uint8, pin_memory=True)
-            rgb = host.numpy().reshape(H, W, 3)
-        else:
-            rgb = np.empty((H, W, 3), dtype=np.uint8)
         for f in range(warm + frames):
             if f == warm:
                 if world > 1:

@@ -109,6 +109,21 @@ struct ptc_ctx
 
     // host-side counters
     uint64_t launches = 0, launchesExtend = 0, launchesConnect = 0;
+
+    // A launch-bound batch (progressive frames: ~34 kernels of a few microseconds each) is captured once into a CUDA graph and
+    // replayed; only the generate and accumulate nodes carry per-batch arguments (iteration numbers, camera).
+    struct BatchGraph
+    {
+        cudaGraph_t graph = nullptr;
+        cudaGraphExec_t exec = nullptr;
+        cudaGraphNode_t genNode = nullptr, accNode = nullptr;
+        cudaKernelNodeParams genParams{}, accParams{};
+        uint32_t nIter = 0, ownedPix = 0, stripeRows = 0, stripeRank = 0, stripeWorld = 0;
+        uint64_t sceneVersion = 0;
+        uint64_t launches = 0, launchesExtend = 0, launchesConnect = 0;  // per replay
+    } batchGraph;
+    uint64_t sceneVersion = 0;
+    bool useGraphs = true;
     double msStage[5] = {0, 0, 0, 0, 0};
     std::vector<StageEvent> pending;
     std::vector<cudaEvent_t> eventPool;
@@ -183,6 +198,14 @@ void drainTimers(ptc_ctx *c)
     }
     c->pending.clear();
 }
+
+void dropBatchGraph(ptc_ctx *ctx)
+{
+    auto &g = ctx->batchGraph;
+    if (g.exec) cudaGraphExecDestroy(g.exec);
+    if (g.graph) cudaGraphDestroy(g.graph);
+    g = ptc_ctx::BatchGraph{};
+}
 }  // namespace
 
 // ================================================================================================ create
@@ -247,6 +270,7 @@ void ptc_destroy(ptc_ctx *ctx)
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     drainTimers(ctx);
+    dropBatchGraph(ctx);
     for (auto e : ctx->eventPool) cudaEventDestroy(e);
     ctx->nodes.release(); ctx->tris.release(); ctx->shade.release(); ctx->materials.release(); ctx->lights.release();
     ctx->textures.release(); ctx->texels.release(); ctx->bigLeaf.release();
@@ -345,6 +369,7 @@ int ptc_create(const ptc_config *config, ptc_ctx **out_ctx)
     c->lc.traverseGrid = c->smCount * traverse_ctas_per_sm(c->fast, false, c->lc.stackDepth);
     c->lc.streamGrid = c->smCount * 8;
     c->lc.refillMin = 4;  // idle lanes that trigger a refill from the warp's staged rays (profiles/r01_sweeps.txt)
+    if (const char *e = std::getenv("PTC_GRAPHS")) c->useGraphs = std::atoi(e) != 0;
     if (const char *e = std::getenv("PTC_REFILL_MIN")) c->lc.refillMin = (uint32_t)std::max(1, std::min(32, std::atoi(e)));
     {
         // phase votes of k_trace, in eighths of the warp's rays: node steps while >= voteNode/8 wait for a node, triangle steps
@@ -639,6 +664,7 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
         if (!std::getenv("PTC_CTAS_PER_SM")) ctx->lc.traverseGrid = ctx->smCount * traverse_ctas_per_sm(ctx->fast, ctx->wide, ctx->lc.stackDepth);
     }
     ctx->sceneLoaded = true;
+    ctx->sceneVersion++;  // device pointers and launch configuration may have changed: a captured batch graph is stale
     return PTC_OK;
 }
 
@@ -777,6 +803,80 @@ int runBatch(ptc_ctx *ctx, uint32_t first, uint32_t nIter, bool accumulate, int 
     if (e != cudaSuccess) return fail(ctx, PTC_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(e));
     return PTC_OK;
 }
+// Batches of at most this many paths are launch-bound (tens of kernels of a few microseconds): replayed as one graph
+constexpr uint64_t kGraphMaxPaths = 1ull << 22;
+
+// runBatch through a CUDA graph: captured on first use of a batch shape, afterwards one cudaGraphLaunch with the generate and
+// accumulate nodes re-parameterised. Falls back to plain launches when capture is not possible.
+int runBatchGraph(ptc_ctx *ctx, uint32_t first, uint32_t nIter)
+{
+    auto &g = ctx->batchGraph;
+    const FrameParams fp = frameParams(ctx, first, nIter);
+    const bool fresh = g.exec && g.nIter == nIter && g.ownedPix == fp.ownedPix && g.stripeRows == fp.stripeRows && g.stripeRank == fp.stripeRank &&
+                       g.stripeWorld == fp.stripeWorld && g.sceneVersion == ctx->sceneVersion;
+    if (!fresh)
+    {
+        dropBatchGraph(ctx);
+        const uint64_t l0 = ctx->launches, e0 = ctx->launchesExtend, c0 = ctx->launchesConnect;
+        if (cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeRelaxed) != cudaSuccess)
+        {
+            cudaGetLastError();
+            return runBatch(ctx, first, nIter, true, -1);
+        }
+        const int rc = runBatch(ctx, first, nIter, true, -1);
+        cudaGraph_t graph = nullptr;
+        const cudaError_t ce = cudaStreamEndCapture(ctx->stream, &graph);
+        g.launches = ctx->launches - l0; g.launchesExtend = ctx->launchesExtend - e0; g.launchesConnect = ctx->launchesConnect - c0;
+        ctx->launches = l0; ctx->launchesExtend = e0; ctx->launchesConnect = c0;  // nothing ran yet
+        if (rc != PTC_OK || ce != cudaSuccess || !graph)
+        {
+            if (graph) cudaGraphDestroy(graph);
+            cudaGetLastError();
+            ctx->useGraphs = false;
+            return rc != PTC_OK ? rc : runBatch(ctx, first, nIter, true, -1);
+        }
+        g.graph = graph;
+        size_t n = 0;
+        cudaGraphGetNodes(graph, nullptr, &n);
+        std::vector<cudaGraphNode_t> nodes(n);
+        cudaGraphGetNodes(graph, nodes.data(), &n);
+        for (cudaGraphNode_t node : nodes)
+        {
+            cudaGraphNodeType t;
+            if (cudaGraphNodeGetType(node, &t) != cudaSuccess || t != cudaGraphNodeTypeKernel) continue;
+            cudaKernelNodeParams p{};
+            if (cudaGraphKernelNodeGetParams(node, &p) != cudaSuccess) continue;
+            if (p.func == generate_kernel()) { g.genNode = node; g.genParams = p; }
+            else if (p.func == accumulate_kernel(fp.sampler)) { g.accNode = node; g.accParams = p; }
+        }
+        if (!g.genNode || !g.accNode || cudaGraphInstantiate(&g.exec, graph, 0) != cudaSuccess)
+        {
+            cudaGetLastError();
+            dropBatchGraph(ctx);
+            ctx->useGraphs = false;
+            return runBatch(ctx, first, nIter, true, -1);
+        }
+        g.nIter = nIter; g.ownedPix = fp.ownedPix; g.stripeRows = fp.stripeRows; g.stripeRank = fp.stripeRank; g.stripeWorld = fp.stripeWorld;
+        g.sceneVersion = ctx->sceneVersion;
+    }
+    // per-batch arguments (the captured values are those of the capture call)
+    FrameParams fpArg = fp;
+    Camera cam = ctx->cam;
+    PathState st = ctx->st;
+    ImageDev img = ctx->img;
+    Counters *cn = ctx->counters.p;
+    void *genArgs[3] = {&fpArg, &cam, &st};
+    void *accArgs[4] = {&fpArg, &st, &img, &cn};
+    cudaKernelNodeParams gp = g.genParams, ap = g.accParams;
+    gp.kernelParams = genArgs; gp.extra = nullptr;
+    ap.kernelParams = accArgs; ap.extra = nullptr;
+    cudaError_t e = cudaGraphExecKernelNodeSetParams(g.exec, g.genNode, &gp);
+    if (e == cudaSuccess) e = cudaGraphExecKernelNodeSetParams(g.exec, g.accNode, &ap);
+    if (e == cudaSuccess) e = cudaGraphLaunch(g.exec, ctx->stream);
+    if (e != cudaSuccess) return fail(ctx, PTC_ERR_CUDA, "batch graph: %s", cudaGetErrorString(e));
+    ctx->launches += g.launches; ctx->launchesExtend += g.launchesExtend; ctx->launchesConnect += g.launchesConnect;
+    return PTC_OK;
+}
 }  // namespace
 
 int ptc_render(ptc_ctx *ctx, uint32_t first_iteration, uint32_t n_iterations)
@@ -788,7 +888,9 @@ int ptc_render(ptc_ctx *ctx, uint32_t first_iteration, uint32_t n_iterations)
     while (done < n_iterations)
     {
         const uint32_t n = std::min(ctx->batchIters, n_iterations - done);
-        int rc = runBatch(ctx, first_iteration + done, n, true, -1);
+        const uint64_t paths = (uint64_t)n * (ctx->stripeRows ? ctx->ownedPix : ctx->nPix);
+        const bool graph = ctx->useGraphs && !(ctx->cfg.flags & PTC_FLAG_STAGE_TIMING) && paths > 0 && paths <= kGraphMaxPaths;
+        int rc = graph ? runBatchGraph(ctx, first_iteration + done, n) : runBatch(ctx, first_iteration + done, n, true, -1);
         if (rc != PTC_OK) return rc;
         done += n;
     }

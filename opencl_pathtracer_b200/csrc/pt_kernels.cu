@@ -765,6 +765,14 @@ void launch_accumulate(cudaStream_t s, const LaunchCfg &lc, const FrameParams &f
     else k_accumulate<true><<<grid, kStreamThreads, 0, s>>>(fp, st, img, cn);
 }
 
+// The two kernels whose arguments change from one batch to the next (iteration numbers, camera): a captured batch graph is
+// replayed with these two nodes re-parameterised (pathtracer_cuda.cu). Argument order as in the launches above.
+const void *generate_kernel() { return reinterpret_cast<const void *>(&k_generate); }
+const void *accumulate_kernel(uint32_t sampler)
+{
+    return sampler == 1 ? reinterpret_cast<const void *>(&k_accumulate<false>) : reinterpret_cast<const void *>(&k_accumulate<true>);
+}
+
 void launch_probe_primary(cudaStream_t s, const FrameParams &fp, const PathState &st, int32_t *hit, float2 *stOut, float *dist2,
                           float4 *dir, int32_t *seedAfter, uint2 *counts)
 {

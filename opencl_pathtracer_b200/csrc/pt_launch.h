@@ -26,6 +26,9 @@ void launch_shade(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev
                   const uint32_t *qin, uint32_t *qout, Counters *cn, int bounce);
 void launch_accumulate(cudaStream_t s, const LaunchCfg &lc, const FrameParams &fp, const PathState &st, const ImageDev &img,
                        Counters *cn);
+// batch graphs: host stubs of k_generate(fp, cam, st) and k_accumulate(fp, st, img, cn), to find their nodes in a captured graph
+const void *generate_kernel();
+const void *accumulate_kernel(uint32_t sampler);
 // parity probes
 void launch_probe_primary(cudaStream_t s, const FrameParams &fp, const PathState &st, int32_t *hit, float2 *stOut, float *dist2,
                           float4 *dir, int32_t *seedAfter, uint2 *counts);
