@@ -106,6 +106,10 @@ def run_ours(args, rank, local_rank, world):
         if rank == 0:
             mean_rgb = float((color.view(-1, 4)[:, :3].sum(0) / count.sum()).mean().item())
         value = paths / (ms * 1e-3)
+        # the reference's own ray count (Controleur/PathTracer.cpp:238-243, numberOfProcessedRays): every path that ended at
+        # depth i is charged (1 + lights) * (i + 1) rays, whether or not its shadow rays were traced
+        depths = r.read_stats()[0].astype(np.float64)
+        ref_rays = sum_over_ranks(float(sum((1 + info.lightsSize) * (i + 1) * depths[i] for i in range(min(DEPTH, len(depths))))))
 
         # ---------------- e2e: reference-facing call sequence with host buffers, host wall clock
         r.reset()
@@ -240,6 +244,7 @@ def run_ours(args, rank, local_rank, world):
         line = {"metric": "samples/s", "value": value, "unit": "samples/s", "n_gpus": world, "steps": K, "warmup": WU,
                 "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "mrays_per_s": rays / (ms * 1e-3) / 1e6,
+                "mrays_per_s_reference_convention": ref_rays / (ms * 1e-3) / 1e6,
                 "config": {"workload": wl["desc"], "image": [W, H], "ray_max_depth": DEPTH, "sampler": "jittered", "mode": args.mode,
                            "spp_per_step_per_gpu": S, "triangles": int(info.triangulationSize), "bvh_nodes": int(info.bvhSize),
                            "parallelism": "iteration-range sharding x%d, one NCCL reduce of the accumulators per run" % world,
