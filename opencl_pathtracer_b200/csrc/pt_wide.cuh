@@ -53,10 +53,16 @@ struct WideLane
     __device__ __forceinline__ bool idle() const { return sp < 0; }
     __device__ __forceinline__ void set_idle() { sp = -1; }
     static constexpr uint32_t kPostponed = 0x100u;
+    // The reference's 4-lane arithmetic lets a refracted direction keep a w lane != 0 and every later origin of that path a
+    // w lane != 1. For such a ray the "distance" a triangle is accepted with is no longer the parameter at which
+    // the ray crosses the triangle's box, so which candidates survive the distance cull depends on the order of the tests. These
+    // rays never park triangles: node step, all of its triangles, next node step — an order that is a function of the ray alone
+    // (with parking it followed the warp's votes: about 40 of 2 M pixels of the bench scene changed from run to run).
+    static constexpr uint32_t kStrict = 0x200u;
     __device__ __forceinline__ bool finished() const { return sp == 0 && ty == 0u && gy <= 0x00ffffffu && !(oct & kPostponed); }
     // A lane can take a node step while it still holds untested triangles: it parks that group (once) and tests it in the
     // next triangle phase. So a lane often qualifies for both phases and follows the warp's vote instead of idling.
-    __device__ __forceinline__ bool wants_node() const { return sp >= 0 && gy > 0x00ffffffu && (ty == 0u || !(oct & kPostponed)); }
+    __device__ __forceinline__ bool wants_node() const { return sp >= 0 && gy > 0x00ffffffu && (ty == 0u || !(oct & (kPostponed | kStrict))); }
     __device__ __forceinline__ bool wants_tri() const { return sp >= 0 && (ty != 0u || (oct & kPostponed)); }
     // BVH-order index of the hit (what the shade stage and the reference's ids use), -1 = miss
     __device__ __forceinline__ int hit_index(const SceneDev &sc) const { return hitTri < 0 ? -1 : (int)__ldg(&sc.tri8Index[hitTri]); }
@@ -67,9 +73,17 @@ __device__ __forceinline__ float finite_inverse(float inv, float d)
     return fabsf(inv) < 1.0e30f ? inv : copysignf(1.0e30f, d);  // d = +-0 or denormal: a huge slope instead of inf (no 0 * inf)
 }
 
-__device__ __forceinline__ float bound_as_parameter(float best)
+// The triangle test accepts by the SQUARED DISTANCE |q - o|^2 of the hit point q = o + d * t as the reference computes it
+// (Triangle_Intersects :536-543), the boxes are culled by the ray PARAMETER. The two disagree by the rounding of q: about one
+// ulp of the coordinates, whatever t is, so for a hit very close to a far-from-zero origin the squared distances of two
+// candidates need not be ordered like their parameters. The cull bound therefore carries an absolute pad of 2^-20 of the
+// origin's coordinates besides the relative one: a candidate that the distance test could still accept is never culled,
+// whichever of the two was tested first — the hit does not depend on the order in which a warp's votes make a lane test
+// its triangles (without the pad about one ray in 10^6 did, run to run).
+__device__ __forceinline__ float cull_pad(const Ray &r) { return (fabsf(r.ox) + fabsf(r.oy) + fabsf(r.oz)) * 9.5367431640625e-7f; }
+__device__ __forceinline__ float bound_as_parameter(float t, const Ray &r)
 {
-    return sqrtf(best) * 1.00001f;  // directions are unit length; the pad keeps the cull conservative
+    return __fmaf_rn(t, 1.00001f, cull_pad(r));  // directions are unit length
 }
 
 __device__ __forceinline__ void lane_begin(WideLane &L, const SceneDev &sc, const Ray &r, float best)
@@ -79,9 +93,9 @@ __device__ __forceinline__ void lane_begin(WideLane &L, const SceneDev &sc, cons
     L.r.iy = finite_inverse(r.iy, r.dy);
     L.r.iz = finite_inverse(r.iz, r.dz);
     L.best = best;
-    L.tmax = bound_as_parameter(best);
+    L.tmax = bound_as_parameter(sqrtf(best), r);
     const uint32_t oct = (r.dx < 0 ? 4u : 0u) | (r.dy < 0 ? 2u : 0u) | (r.dz < 0 ? 1u : 0u);
-    L.oct = 7u - oct;
+    L.oct = (7u - oct) | ((r.dw == 0.f && r.ow == 1.f) ? 0u : WideLane::kStrict);
     L.gx = 0u;
     L.gy = sc.nNodes8 ? 0x80000000u : 0u;  // "slot 7 ^ octinv of an imask-less group at index 0" = the root
     L.tx = L.ty = 0u;
@@ -203,7 +217,7 @@ __device__ __forceinline__ void lane_tri_step(WideLane &L, const SceneDev &sc, c
     L.nt++;
     const bool acc = tri_test(sc.tris8, i, L.r, L.best, L.hs, L.ht, L.htp, L.hmat, ANY ? nullptr : sc.tri8Index, L.hitTri);
     L.hitTri = acc ? (int)i : L.hitTri;
-    L.tmax = acc ? L.htp * 1.00001f : L.tmax;
+    L.tmax = acc ? bound_as_parameter(L.htp, L.r) : L.tmax;
     if (ANY)
     {
         L.found = L.found || acc;
