@@ -72,10 +72,14 @@ enum
                                         BVH_Create need not run at all) and build the 8-wide BVH on the device from the
                                         triangles in the order given (csrc/pt_lbvh.cu). Hits are reported as indices into
                                         that order. Not valid in PARITY mode or together with PTC_FLAG_BVH2. */
-    PTC_FLAG_RUSSIAN_ROULETTE = 1u << 5 /* FAST mode: after MIN_REFLECTION_NUMBER = 5 bounces a path survives with probability
+    PTC_FLAG_RUSSIAN_ROULETTE = 1u << 5,/* FAST mode: after MIN_REFLECTION_NUMBER = 5 bounces a path survives with probability
                                         c = max throughput / (bounce - 5) and its throughput is divided by c (unbiased). The
                                         reference has this stage disabled and commented out (Kernel/PathTracer_FullKernel_header.cl:12,
                                         PathTracer_FullKernel.cl:1306-1314); the random streams then differ from the reference's. */
+    PTC_FLAG_TEXTURE_BILINEAR = 1u << 6 /* FAST mode: surface textures are sampled with bilinear interpolation of the four texels
+                                        around (u, v) instead of the reference's nearest texel
+                                        (Texture_GetPixelColorValue, Kernel/PathTracer_FullKernel_header.cl:430-459); same wrap
+                                        and alpha convention. The sky keeps the reference's lookup. Un-oracled. */
 };
 
 /* Replaces the `-D` build options of reference Controleur/PathTracer_OpenCL.cpp:292-314: all run-time here. */

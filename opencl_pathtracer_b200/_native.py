@@ -16,7 +16,7 @@ PTC_OK = 0
 PTC_ERR_INVALID, PTC_ERR_CUDA, PTC_ERR_NO_DEVICE, PTC_ERR_STATE, PTC_ERR_LIMIT, PTC_ERR_UNSUPPORTED = 1, 2, 3, 4, 5, 6
 SAMPLER_JITTERED, SAMPLER_RANDOM, SAMPLER_UNIFORM = 0, 1, 2
 MODE_PARITY, MODE_FAST = 0, 1
-FLAG_STAGE_TIMING, FLAG_NO_VARIANCE, FLAG_NO_GRAPH, FLAG_BVH2, FLAG_GPU_BVH, FLAG_RUSSIAN_ROULETTE = 1, 2, 4, 8, 16, 32
+FLAG_STAGE_TIMING, FLAG_NO_VARIANCE, FLAG_NO_GRAPH, FLAG_BVH2, FLAG_GPU_BVH, FLAG_RUSSIAN_ROULETTE, FLAG_TEXTURE_BILINEAR = 1, 2, 4, 8, 16, 32, 64
 MAX_INTERSECTION_NUMBER = 5000
 
 

@@ -336,6 +336,12 @@ int ptc_create(const ptc_config *config, ptc_ctx **out_ctx)
         delete c;
         return fail(nullptr, PTC_ERR_INVALID, "PTC_FLAG_RUSSIAN_ROULETTE needs PTC_MODE_FAST (PARITY reproduces the reference's random streams)");
     }
+    if ((config->flags & PTC_FLAG_TEXTURE_BILINEAR) && !c->fast)
+    {
+        delete c;
+        return fail(nullptr, PTC_ERR_INVALID, "PTC_FLAG_TEXTURE_BILINEAR needs PTC_MODE_FAST (PARITY reproduces the reference's nearest-texel lookup)");
+    }
+    if (config->flags & PTC_FLAG_NO_GRAPH) c->useGraphs = false;
     c->gpuBvh = (config->flags & PTC_FLAG_GPU_BVH) != 0;
     if (c->gpuBvh && (!c->fast || (config->flags & PTC_FLAG_BVH2) || !c->wide))
     {

@@ -19,6 +19,7 @@ namespace ptc
 {
 constexpr int kTraverseThreads = 128;
 constexpr uint32_t kFlagRussianRoulette = 1u << 5;  // PTC_FLAG_RUSSIAN_ROULETTE (include/pathtracer_cuda.h)
+constexpr uint32_t kFlagTextureBilinear = 1u << 6;  // PTC_FLAG_TEXTURE_BILINEAR
 constexpr int kStreamThreads = 256;
 
 // ------------------------------------------------------------------------------------------------ reset
@@ -393,7 +394,8 @@ __global__ void __launch_bounds__(kStreamThreads, 4) k_shade(SceneDev sc, FrameP
                     if (positive) { tu = (a.x * w0 + a.z * s) + b.x * t; tv = (a.y * w0 + a.w * s) + b.y * t; }
                     else { tu = (b.z * w0 + c.x * s) + c.z * t; tv = (b.w * w0 + c.y * s) + c.w * t; }
                     const uint4 tx = __ldg(&sc.textures[mat.textureId]);
-                    color = texture_lookup(sc, tx.x, tx.y, tx.z, tu, tv);
+                    color = (FAST && (fp.flags & kFlagTextureBilinear)) ? texture_lookup_bilinear(sc, tx.x, tx.y, tx.z, tu, tv)
+                                                                           : texture_lookup(sc, tx.x, tx.y, tx.z, tu, tv);
                 }
                 // :1267-1274 normals
                 const bool same = dot4(d, N) > 0;

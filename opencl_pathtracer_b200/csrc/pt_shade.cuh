@@ -31,6 +31,25 @@ __device__ __forceinline__ float4 texture_lookup(const SceneDev &sc, uint32_t w,
     return bgra;
 }
 
+// SURVEY.md 8(f) N4 (PTC_FLAG_TEXTURE_BILINEAR, un-oracled): the same wrap and texel grid, the four texels around the
+// continuous position blended; at texel centres it returns the nearest-texel value.
+__device__ __forceinline__ float4 texture_lookup_bilinear(const SceneDev &sc, uint32_t w, uint32_t h, uint32_t off, float u, float v)
+{
+    u = u - ((int)u) + (u < 0 ? 1 : 0);
+    v = v - ((int)v) + (v < 0 ? 1 : 0);
+    const float fx = u * (w - 1), fy = v * (h - 1);
+    const uint32_t x0 = (uint32_t)fx, y0 = (uint32_t)fy;
+    const uint32_t x1 = x0 + 1 < w ? x0 + 1 : x0, y1 = y0 + 1 < h ? y0 + 1 : y0;
+    const float ax = fx - (float)x0, ay = fy - (float)y0;
+    const uchar4 c00 = __ldg(&sc.texels[off + y0 * w + x0]), c10 = __ldg(&sc.texels[off + y0 * w + x1]);
+    const uchar4 c01 = __ldg(&sc.texels[off + y1 * w + x0]), c11 = __ldg(&sc.texels[off + y1 * w + x1]);
+    const float w00 = (1 - ax) * (1 - ay), w10 = ax * (1 - ay), w01 = (1 - ax) * ay, w11 = ax * ay;
+    float4 bgra = f4((w00 * c00.x + w10 * c10.x) + (w01 * c01.x + w11 * c11.x), (w00 * c00.y + w10 * c10.y) + (w01 * c01.y + w11 * c11.y),
+                     (w00 * c00.z + w10 * c10.z) + (w01 * c01.z + w11 * c11.z), (w00 * c00.w + w10 * c10.w) + (w01 * c01.w + w11 * c11.w)) / 255.f;
+    bgra.w = 1.f - bgra.w;
+    return bgra;
+}
+
 __device__ __forceinline__ float4 sky_color(const SceneDev &sc, float4 dir)
 {
     const float x = sc.sky.cosRot * dir.x - sc.sky.sinRot * dir.y;

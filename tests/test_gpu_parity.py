@@ -584,3 +584,28 @@ def test_full_size_properties(ptref, scene_factory):
     print("full size: FAST vs PARITY pixel mismatch fraction %g, mean ratio %g, paths that changed depth bin %g" % (bad, ratio, moved))
     # measured: 4.3e-3 of the pixels, mean ratio 0.99994, 5.5e-3 (every path that changes its depth bin is counted twice)
     assert bad <= 1e-2 and abs(ratio - 1) <= 1e-3 and moved <= 1e-2
+
+
+def test_bilinear_texture_filtering(scene_factory):
+    """PTC_FLAG_TEXTURE_BILINEAR (FAST, opt-in, un-oracled: SURVEY.md 8(f) N4). Against this build's nearest-texel FAST mode on
+    the textured scene: the same random streams, so untextured pixels are bit-identical; textured pixels change; the image mean
+    moves by well under a percent (filtering redistributes, it does not add energy); and across a checker edge the filtered
+    image has no larger steps than the unfiltered one. PARITY refuses the flag."""
+    w, h, spp = 256, 192, 8
+    sc = scene_factory("gallery", w, h, True)
+    img = {}
+    for label, flags in (("nearest", 0), ("bilinear", pt.FLAG_TEXTURE_BILINEAR)):
+        with pt.PathTracerCUDA(w, h, ray_max_depth=1, mode=pt.MODE_FAST, flags=flags) as r:
+            r.upload(sc)
+            r.render(0, spp)
+            color, nb = r.read_image()
+            img[label] = color[..., :3] / nb[..., None]
+    a, b = img["nearest"], img["bilinear"]
+    changed = (a != b).any(axis=2)
+    print("bilinear: %.1f %% of the pixels change, mean ratio %.5f" % (100 * changed.mean(), b.mean() / a.mean()))
+    assert 0.02 < changed.mean() < 0.9
+    assert abs(b.mean() / a.mean() - 1) < 5e-3
+    step = lambda x: np.abs(np.diff(x, axis=1))[changed[:, 1:] & changed[:, :-1]]
+    assert np.percentile(step(b), 99) <= np.percentile(step(a), 99) + 1e-6
+    with pytest.raises(pt.PathTracerError):
+        pt.PathTracerCUDA(32, 32, mode=pt.MODE_PARITY, flags=pt.FLAG_TEXTURE_BILINEAR)
