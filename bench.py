@@ -33,6 +33,9 @@ WORKLOADS = {
                    desc="C3: procedural atrium ~262k tris, diffuse+varnished+glass, 3 lights, 1920x1080, depth 10, jittered"),
     "cornell": dict(scene="cornell", size=(1920, 1080), sky=False, spp=8,
                     desc="C2: Cornell box 30 tris, diffuse + point light, 1920x1080, depth 10, jittered"),
+    "cornell_area": dict(scene="cornell_area", size=(1920, 1080), sky=False, spp=8,
+                         desc="C2 as BASELINE.json words it: Cornell box 30 tris, diffuse + 130x105 area light (PTC_LIGHT_AREA, an extension: "
+                              "the reference has no area lights, so no reference arm exists for this workload), 1920x1080, depth 10, jittered"),
     "terrain": dict(scene="terrain", size=(3840, 2160), sky=True, spp=1,
                     desc="C4: procedural terrain + 64x64 flattened rock instances ~10.1M tris, 16 textures 1024^2, sun + sky cube map, 3840x2160, depth 10, jittered"),
     "terrain_1080p": dict(scene="terrain", size=(1920, 1080), sky=True, spp=4,
@@ -107,6 +110,9 @@ def run_reference(args, rank):
     import opencl_pathtracer_b200 as pt
     from oracle import ptref
     wl = WORKLOADS[args.workload]
+    if args.workload == "cornell_area":
+        print(json.dumps({"impl": "reference", "unavailable": "the reference kernel has no area lights (PTC_LIGHT_AREA is an extension); use --workload cornell"}))
+        return
     W, H = wl["size"]
     scene = pt.Scene(wl["scene"], W, H, load_sky=wl["sky"])
     cores = ptref.max_threads()

@@ -208,7 +208,7 @@ def run_ours(args, rank, local_rank, world):
                                       "rays": (c["extension_rays"] + c["shadow_rays"]) / c["paths"]}
 
             # PARITY mode beside it (bit-exact arithmetic + the reference's culling quirks), 2 steps
-            if world == 1 and args.mode == "fast":
+            if world == 1 and args.mode == "fast" and args.workload != "cornell_area":  # PARITY has no area lights (an extension)
                 rq = pt.PathTracerCUDA(W, H, ray_max_depth=DEPTH, mode=pt.MODE_PARITY, device=local_rank, flags=pt.FLAG_NO_VARIANCE,
                                        stream=stream.cuda_stream)
                 rq.upload(scene)
@@ -225,7 +225,7 @@ def run_ours(args, rank, local_rank, world):
                                         "box_tests_per_path": cq["box_tests"] / cq["paths"]}
 
     cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and args.workload != "cornell_area":  # nor has the reference kernel
         try:
             from oracle import ptref
             rows = (0, H)  # the whole frame once: ~10-15 s on 16 host cores

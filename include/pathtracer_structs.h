@@ -40,7 +40,10 @@ typedef struct PTC_ALIGN(16) ptc_bounding_box
 } ptc_bounding_box;
 
 /* Controleur/PathTracer_Structs.h:24-30 */
-enum { PTC_LIGHT_DIRECTIONNAL = 0, PTC_LIGHT_POINT = 1, PTC_LIGHT_SPOT = 2, PTC_LIGHT_UNKNOWN = 3 };
+enum { PTC_LIGHT_DIRECTIONNAL = 0, PTC_LIGHT_POINT = 1, PTC_LIGHT_SPOT = 2, PTC_LIGHT_UNKNOWN = 3,
+       /* Extension (the reference has no area or emissive lights): a one-sided parallelogram emitter,
+        * FAST mode only, filled by ptc_light_make_area below. */
+       PTC_LIGHT_AREA = 4 };
 
 /* Controleur/PathTracer_Structs.h:32-41 — 64 bytes */
 typedef struct PTC_ALIGN(16) ptc_light
@@ -53,6 +56,28 @@ typedef struct PTC_ALIGN(16) ptc_light
     float cosOfOuterFallOffAngle;
     int32_t type;
 } ptc_light;
+
+/* PTC_LIGHT_AREA record: the parallelogram corner + a*eu + b*ev, (a, b) in [0,1)^2, emitting `power` x `color` as
+ * radiance towards cross(eu, ev) only. Each lit hit connects to ONE point of it, drawn from the path's own random stream
+ * (next-event estimation); the estimator is power * color * BRDF * cos(surface) * cos(light) * area / distance^2. The
+ * emitter has no geometry of its own: camera and bounce rays do not see it, exactly like the reference's point lights.
+ * Its shadow rays are bounded by the squared distance to the sampled point, i.e. every occluder in front of it counts (the
+ * reference's own light types hand a LENGTH to a squared-distance test, Kernel/PathTracer_FullKernel.cl:938-944, which both
+ * modes reproduce for them).
+ * The edge ev does not fit the 64-byte reference record beside eu, so it rides in the three lanes a positional light
+ * leaves unused (position.w, direction.w, cosOfInnerFallOffAngle); cosOfOuterFallOffAngle is reserved (the library
+ * writes the light's offset into the random stream there at upload). */
+static inline void ptc_light_make_area(ptc_light *l, const float corner[3], const float eu[3], const float ev[3],
+                                       const float rgb[3], float power)
+{
+    l->position.x = corner[0]; l->position.y = corner[1]; l->position.z = corner[2]; l->position.w = ev[0];
+    l->direction.x = eu[0]; l->direction.y = eu[1]; l->direction.z = eu[2]; l->direction.w = ev[1];
+    l->color.x = rgb[0]; l->color.y = rgb[1]; l->color.z = rgb[2]; l->color.w = 1.0f;
+    l->power = power;
+    l->cosOfInnerFallOffAngle = ev[2];
+    l->cosOfOuterFallOffAngle = 0.0f;
+    l->type = PTC_LIGHT_AREA;
+}
 
 /* Controleur/PathTracer_Structs.h:43-51 */
 enum { PTC_MAT_STANDART = 0, PTC_MAT_WATER = 1, PTC_MAT_GLASS = 2, PTC_MAT_VARNHISHED = 3, PTC_MAT_METAL = 4, PTC_MAT_UNKNOWN = 5 };

@@ -590,6 +590,22 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
     sky.cosRot = s->sky->cosRotationAngle;
     sky.sinRot = s->sky->sinRotationAngle;
     static_assert(sizeof(DevLight) == sizeof(ptc_light), "Light is uploaded as is");
+    // PTC_LIGHT_AREA (extension, include/pathtracer_structs.h): the reserved lane receives the light's offset into the path's
+    // random stream, 16807^(2k) for the k-th area light (light_resolve in pt_shade.cuh)
+    std::vector<ptc_light> hLights(s->lights, s->lights + nL);
+    uint32_t areaJump = 1u;
+    for (uint32_t i = 0; i < nL; i++)
+    {
+        if (hLights[i].type != PTC_LIGHT_AREA) continue;
+        if (!ctx->fast) return fail(ctx, PTC_ERR_UNSUPPORTED, "light %u is an area light: an extension of FAST mode, the reference has none", i);
+        const ptc_light &l = hLights[i];
+        const float cx = l.direction.y * l.cosOfInnerFallOffAngle - l.direction.z * l.direction.w;
+        const float cy = l.direction.z * l.position.w - l.direction.x * l.cosOfInnerFallOffAngle;
+        const float cz = l.direction.x * l.direction.w - l.direction.y * l.position.w;
+        if (!(cx * cx + cy * cy + cz * cz > 0.f)) return fail(ctx, PTC_ERR_INVALID, "area light %u has no area", i);
+        std::memcpy(&hLights[i].cosOfOuterFallOffAngle, &areaJump, sizeof(float));
+        areaJump *= 16807u * 16807u;
+    }
 
     // ---- FAST mode: the 8-wide compressed BVH (pt_wide_build.cu) and the intersection records in its order
     WideBvh wideBvh;
@@ -618,7 +634,7 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
     CK(up(ctx->tris.p, hTris.data(), sizeof(DevTri) * nT));
     CK(up(ctx->shade.p, hShade.data(), sizeof(DevShade) * nT));
     CK(up(ctx->materials.p, hMat.data(), sizeof(DevMaterial) * nM));
-    CK(up(ctx->lights.p, s->lights, sizeof(DevLight) * nL));
+    CK(up(ctx->lights.p, hLights.data(), sizeof(DevLight) * nL));
     CK(up(ctx->textures.p, hTex.data(), sizeof(uint4) * nX));
     CK(up(ctx->texels.p, s->textures_data, sizeof(uchar4) * nTexel));
     CK(up(ctx->bigLeaf.p, bigLeaf.data(), sizeof(uint32_t) * bigLeaf.size()));
@@ -660,7 +676,7 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
     sc.nodes8 = ctx->wide ? ctx->nodes8.p : nullptr; sc.tris8 = ctx->wide ? ctx->tris8.p : nullptr;
     sc.tri8Index = ctx->wide ? ctx->tri8Index.p : nullptr; sc.nNodes8 = ctx->wide ? nNodes8 : 0u;
     ctx->lc.wide = ctx->wide;
-    sc.rootRef = rootRef; sc.nLights = nL; sc.nTriangles = nT; sc.sky = sky;
+    sc.rootRef = rootRef; sc.nLights = nL; sc.areaJump = areaJump; sc.nTriangles = nT; sc.sky = sky;
     ctx->cam = Camera{to4(s->camera_position), to4(s->camera_direction), to4(s->camera_right), to4(s->camera_up)};
     // traversal stack: one entry per level below the root is enough (a push happens only when descending)
     if (!std::getenv("PTC_FULL_STACK"))

@@ -94,6 +94,7 @@ struct SceneDev
     uint32_t rootRef;
     uint32_t nLights;
     uint32_t nTriangles;
+    uint32_t areaJump;  // 16807^(2 * number of PTC_LIGHT_AREA lights) mod 2^32; 1 without area lights (pt_shade.cuh light_resolve)
     DevSky sky;
 };
 

@@ -145,7 +145,9 @@ struct PathGroup
 };
 constexpr size_t kGroupBytes = sizeof(PathGroup) * (kTraverseThreads / 32);
 
-template <bool ANY, bool FAST, typename LaneT>
+// FAST: 0 = PARITY, 1 = FAST, 2 = FAST for a scene with area lights (extension; connect only — scenes without one run the
+// kernels they always ran)
+template <bool ANY, int FAST, typename LaneT>
 __global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas) k_trace(SceneDev sc, PathState st, const uint32_t *__restrict__ queue,
                                                            Counters *__restrict__ cn, int bounce, uint32_t popMin, int stackDepth)
 {
@@ -268,11 +270,12 @@ __global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas) k_trace(Sce
                     if (valid)
                     {
                         const float4 q = group.q[lane];
-                        const DevLight light = sc.lights[l];
+                        DevLight light = sc.lights[l];
+                        if (FAST == 2 && light.type == 4) light = light_resolve(light, st.seed[group.slot[lane]]);
                         // FAST: a light that sends exactly zero power towards the shading normal (:403-421: behind the surface,
                         // outside a spot cone) adds +-0 to the pixel whether it is occluded or not: no ray
                         // (the light is also marked as occluded, so that the shade stage skips its term without evaluating it)
-                        if (FAST && light_power_toward(light, q, group.ns[lane]) == 0.0f)
+                        if (FAST && light_power_toward<FAST == 2>(light, q, group.ns[lane]) == 0.0f)
                         {
                             valid = false;
                             atomicOr(&st.occl[group.slot[lane]], 1u << l);
@@ -331,7 +334,7 @@ __global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas) k_trace(Sce
             const bool wantNode = L.wants_node();
             const int nN = __popc(__ballot_sync(full, wantNode));
             if (nN == 0 || 8 * nN < voteNode * nHave) break;
-            if (wantNode) lane_node_step<FAST>(L, sc, stk, kTraverseThreads);
+            if (wantNode) lane_node_step<(FAST != 0)>(L, sc, stk, kTraverseThreads);
         }
         // ---- triangle phase: at least one step if any lane waits for a triangle, then while they are the majority
         while (true)
@@ -347,7 +350,7 @@ __global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas) k_trace(Sce
 }
 
 // ------------------------------------------------------------------------------------------------ shade
-template <bool FAST>
+template <int FAST>  // as k_trace
 __global__ void __launch_bounds__(kStreamThreads, 4) k_shade(SceneDev sc, FrameParams fp, PathState st, const uint32_t *__restrict__ qin,
                                                          uint32_t *__restrict__ qout, Counters *__restrict__ cn, int bounce)
 {
@@ -410,12 +413,15 @@ __global__ void __launch_bounds__(kStreamThreads, 4) k_shade(SceneDev sc, FrameP
                         // an occluded light adds nothing (:944-949); neither does one the connect stage found to send zero power
                         // (its term would be +-0): both carry their bit, and the term is not evaluated at all
                         if ((occl >> li) & 1u) continue;
-                        const DevLight l = sc.lights[li];
+                        DevLight l = sc.lights[li];
+                        if (FAST == 2 && l.type == 4) l = light_resolve(l, seed);
                         const float4 full = (l.type == 0) ? -l.direction : (l.position - q);
                         const float4 ldir = normalize4(full);
                         const float brdf = material_brdf(mat.type, -ldir, Ns, d);
-                        L = L + (light_power_toward(l, q, Ns) * brdf) * l.color;
+                        L = L + (light_power_toward<FAST == 2>(l, q, Ns) * brdf) * l.color;
                     }
+                // area lights (extension): the stream moves past the draws their sample points took, lit hit or not
+                if (FAST == 2) seed = (int)(((unsigned)seed * sc.areaJump) & 0x7FFFFFFFu);
                 // :791-891
                 float4 Nref = d, out = d;
                 float4 add = f4(0, 0, 0, 0);
@@ -698,7 +704,7 @@ static inline size_t stack_bytes(bool wide, int stackDepth, bool any)
     return (size_t)stackDepth * kTraverseThreads * (wide ? sizeof(uint2) : sizeof(uint32_t)) + kStageBytes + (any ? kGroupBytes : 0);
 }
 
-template <bool ANY, bool FAST, typename LaneT>
+template <bool ANY, int FAST, typename LaneT>
 static int occupancy_of(size_t bytes)
 {
     int n = 0;
@@ -711,14 +717,14 @@ int traverse_ctas_per_sm(bool fast, bool wide, int stackDepth)
     if (const char *e = std::getenv("PTC_CARVEOUT"))  // experiment: shared-memory carve-out in percent (what is left is L1)
     {
         const int v = std::atoi(e);
-        cudaFuncSetAttribute(k_trace<false, true, WideLane>, cudaFuncAttributePreferredSharedMemoryCarveout, v);
-        cudaFuncSetAttribute(k_trace<true, true, WideLane>, cudaFuncAttributePreferredSharedMemoryCarveout, v);
+        cudaFuncSetAttribute(k_trace<false, 1, WideLane>, cudaFuncAttributePreferredSharedMemoryCarveout, v);
+        cudaFuncSetAttribute(k_trace<true, 1, WideLane>, cudaFuncAttributePreferredSharedMemoryCarveout, v);
     }
     const size_t bytes = stack_bytes(wide, stackDepth, false), bytesAny = stack_bytes(wide, stackDepth, true);
     int n, m;
-    if (wide) { n = occupancy_of<false, true, WideLane>(bytes); m = occupancy_of<true, true, WideLane>(bytesAny); }
-    else if (fast) { n = occupancy_of<false, true, TraceLane>(bytes); m = occupancy_of<true, true, TraceLane>(bytesAny); }
-    else { n = occupancy_of<false, false, TraceLane>(bytes); m = occupancy_of<true, false, TraceLane>(bytesAny); }
+    if (wide) { n = occupancy_of<false, 1, WideLane>(bytes); m = occupancy_of<true, 1, WideLane>(bytesAny); }
+    else if (fast) { n = occupancy_of<false, 1, TraceLane>(bytes); m = occupancy_of<true, 1, TraceLane>(bytesAny); }
+    else { n = occupancy_of<false, 0, TraceLane>(bytes); m = occupancy_of<true, 0, TraceLane>(bytesAny); }
     n = n < m ? n : m;
     return n < 1 ? 1 : n;
 }
@@ -735,9 +741,12 @@ static void launch_trace(cudaStream_t s, const LaunchCfg &lc, bool fast, const S
                          Counters *cn, int bounce)
 {
     const size_t smem = stack_bytes(lc.wide, lc.stackDepth, ANY);
-    if (lc.wide) k_trace<ANY, true, WideLane><<<lc.traverseGrid, kTraverseThreads, smem, s>>>(sc, st, queue, cn, bounce, lc.refillMin, lc.stackDepth);
-    else if (fast) k_trace<ANY, true, TraceLane><<<lc.traverseGrid, kTraverseThreads, smem, s>>>(sc, st, queue, cn, bounce, lc.refillMin, lc.stackDepth);
-    else k_trace<ANY, false, TraceLane><<<lc.traverseGrid, kTraverseThreads, smem, s>>>(sc, st, queue, cn, bounce, lc.refillMin, lc.stackDepth);
+    const bool area = ANY && sc.areaJump != 1u;  // the scene holds area lights: the connect variant that samples them
+#define PTC_TRACE(MODE, LANE) k_trace<ANY, MODE, LANE><<<lc.traverseGrid, kTraverseThreads, smem, s>>>(sc, st, queue, cn, bounce, lc.refillMin, lc.stackDepth)
+    if (lc.wide) { if (area) PTC_TRACE(ANY ? 2 : 1, WideLane); else PTC_TRACE(1, WideLane); }
+    else if (fast) { if (area) PTC_TRACE(ANY ? 2 : 1, TraceLane); else PTC_TRACE(1, TraceLane); }
+    else PTC_TRACE(0, TraceLane);
+#undef PTC_TRACE
 }
 
 void launch_extend(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const PathState &st, const uint32_t *queue,
@@ -755,8 +764,9 @@ void launch_connect(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneD
 void launch_shade(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const FrameParams &fp, const PathState &st,
                   const uint32_t *qin, uint32_t *qout, Counters *cn, int bounce)
 {
-    if (fast) k_shade<true><<<lc.streamGrid, kStreamThreads, 0, s>>>(sc, fp, st, qin, qout, cn, bounce);
-    else k_shade<false><<<lc.streamGrid, kStreamThreads, 0, s>>>(sc, fp, st, qin, qout, cn, bounce);
+    if (fast && sc.areaJump != 1u) k_shade<2><<<lc.streamGrid, kStreamThreads, 0, s>>>(sc, fp, st, qin, qout, cn, bounce);
+    else if (fast) k_shade<1><<<lc.streamGrid, kStreamThreads, 0, s>>>(sc, fp, st, qin, qout, cn, bounce);
+    else k_shade<0><<<lc.streamGrid, kStreamThreads, 0, s>>>(sc, fp, st, qin, qout, cn, bounce);
 }
 
 void launch_accumulate(cudaStream_t s, const LaunchCfg &lc, const FrameParams &fp, const PathState &st, const ImageDev &img,

@@ -109,6 +109,8 @@ __device__ __forceinline__ float material_brdf(int type, float4 incident, float4
     return 1;
 }
 
+// AREA: also evaluates a resolved PTC_LIGHT_AREA record (extension; only instantiated for scenes that hold one)
+template <bool AREA = false>
 __device__ __forceinline__ float light_power_toward(const DevLight &l, float4 p, float4 N)
 {
     if (l.type == 0) return l.power * fmaxf(dot4(-l.direction, N), 0.f);
@@ -125,7 +127,35 @@ __device__ __forceinline__ float light_power_toward(const DevLight &l, float4 p,
         if (cosAngle < l.cosOuter) return 0.0f;
         return l.power * (cosAngle - l.cosOuter) / (l.cosInner - l.cosOuter) * fmaxf(-dot4(ld, N), 0);
     }
+    if (AREA && l.type == 4)
+    {
+        // extension: one sampled point of an area light (light_resolve below): power already carries the area, direction is the
+        // emitter's normal; geometry term cos(light) * cos(surface) / distance^2
+        const float4 t = p - l.position;
+        const float4 w = normalize4(l.position - p);
+        return l.power / dot4(t, t) * fmaxf(-dot4(w, l.direction), 0.f) * fmaxf(dot4(w, N), 0.f);
+    }
     return 0.f;
+}
+
+// PTC_LIGHT_AREA (extension, FAST only; include/pathtracer_structs.h): turns the parallelogram record into the point of it
+// that this path connects to at this bounce. (a, b) are draws 2k+1 and 2k+2 of the path's stream after `seed`, k = index
+// of the light among the area lights: the stream is a multiplicative congruence (header.cl:246-253), so "skip 2k draws" is
+// one multiplication by 16807^(2k), which ptc_upload_scene stored in the reserved lane. The connect stage and the shade
+// stage both call this with the seed the path carries into the bounce and therefore see the same point; k_shade then
+// advances the stream past all area-light draws (SceneDev::areaJump).
+__device__ __forceinline__ DevLight light_resolve(DevLight l, int seed)
+{
+    if (l.type != 4) return l;
+    int s = (int)(((unsigned)seed * (unsigned)__float_as_int(l.cosOuter)) & 0x7FFFFFFFu);
+    const float a = rng_next(s), b = rng_next(s);
+    const float4 eu = f4(l.direction.x, l.direction.y, l.direction.z, 0.f), ev = f4(l.position.w, l.direction.w, l.cosInner, 0.f);
+    const float4 c = cross3(eu, ev);
+    const float area = length4(c);
+    l.position = f4(l.position.x + (a * eu.x + b * ev.x), l.position.y + (a * eu.y + b * ev.y), l.position.z + (a * eu.z + b * ev.z), 1.f);
+    l.direction = f4(c.x / area, c.y / area, c.z / area, 0.f);
+    l.power = l.power * area;
+    return l;
 }
 
 // cos/sin: the reference calls OpenCL's cos/sin (implementation-defined accuracy); the oracle build uses
@@ -192,6 +222,9 @@ __device__ __forceinline__ void shadow_setup(const DevLight &l, float4 q, float4
     const float4 full = (l.type == 0) ? -l.direction : (l.position - q);
     dir = normalize4(full);
     bound = (l.type == 0) ? INFINITY : length4(full);
+    // extension: a sampled area-light point is occluded by anything in front of it — the bound is the squared distance the
+    // triangle test compares it with (the reference's lights keep their quirk: occluders beyond sqrt(distance) are not seen)
+    if (l.type == 4) bound = dot4(full, full);
 }
 
 }  // namespace ptc

@@ -200,6 +200,20 @@ struct SceneBuilder
         l.power = power;
         lights.push_back(l);
     }
+    // PTC_LIGHT_AREA (extension of the CUDA library, include/pathtracer_structs.h ptc_light_make_area: the reference has no area
+    // lights): parallelogram corner + a eu + b ev emitting towards cross(eu, ev); ev rides in the lanes a positional light leaves unused
+    void addAreaLight(const Float4 &corner, const Float4 &eu, const Float4 &ev, float radiance, float r, float g, float b)
+    {
+        Light l;
+        std::memset((void *)&l, 0, sizeof(l));
+        l.type = (LightType)PTC_LIGHT_AREA;
+        l.color = Float4(r, g, b, 1.f);
+        l.position = Float4(corner.x, corner.y, corner.z, ev.x);
+        l.direction = Float4(eu.x, eu.y, eu.z, ev.y);
+        l.cosOfInnerFallOffAngle = ev.z;
+        l.power = radiance;
+        lights.push_back(l);
+    }
     void addDirectionalLight(const Float4 &dir, float power, float r, float g, float b)
     {
         Light l;
@@ -289,7 +303,7 @@ struct SceneBuilder
 
 // ------------------------------------------------------------------------------------------------------
 // Cornell box (classic measured data, frame permuted to z-up)
-void buildCornell(SceneBuilder &s, bool specular, uint w, uint h)
+void buildCornell(SceneBuilder &s, bool specular, uint w, uint h, bool areaLight = false)
 {
     uint white = s.addMaterial(MAT_STANDART, 0.73f, 0.73f, 0.73f);
     uint red = s.addMaterial(MAT_STANDART, 0.65f, 0.05f, 0.05f);
@@ -323,7 +337,9 @@ void buildCornell(SceneBuilder &s, bool specular, uint w, uint h)
         s.addQuad(Pc(tb[i][0], 0, tb[i][1]), Pc(tb[i][0], 330, tb[i][1]), Pc(tb[j][0], 330, tb[j][1]), Pc(tb[j][0], 0, tb[j][1]), tall, tall);
     }
     // the reference has no area light: a point light just under the ceiling
-    s.addPointLight(Pc(278, 540, 279.5), 250000.f, 1.f, 0.96f, 0.9f);
+    // "cornell_area" (BASELINE.json configs[1] names an area light): the classic 130 x 105 emitter, a hair under the ceiling
+    if (areaLight) s.addAreaLight(Pc(213, 548.7, 227), Vc(130, 0, 0), Vc(0, 0, 105), 100.f, 1.f, 0.96f, 0.9f);
+    else s.addPointLight(Pc(278, 540, 279.5), 250000.f, 1.f, 0.96f, 0.9f);
     // classic camera: (278,273,-800) looking +z, 35 mm lens on a 25 mm film; screen-right is -x
     Float4 pos = Pc(278, 273, -800);
     Float4 d = Vc(0, 0, 1), up = Vc(0, 1, 0);
@@ -535,6 +551,7 @@ void PathTracerProceduralImporter::Import(uint image_width, uint image_height, b
     uint skySize = 1;
     if (name == "cornell") buildCornell(s, false, image_width, image_height);
     else if (name == "cornell_specular") buildCornell(s, true, image_width, image_height);
+    else if (name == "cornell_area") buildCornell(s, false, image_width, image_height, true);
     else if (name == "gallery") { buildGallery(s, seed, image_width, image_height); skySize = 32; }
     else if (name == "atrium") buildAtrium(s, seed, param > 0 ? param : 1, image_width, image_height);
     else if (name == "terrain") { int g = param > 0 ? param : 64; buildTerrain(s, seed, g, image_width, image_height); skySize = g >= 64 ? 512 : 64; }

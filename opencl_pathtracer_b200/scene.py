@@ -26,6 +26,22 @@ MATERIAL = np.dtype({"names": ["simpleColor", "textureName", "opacity", "texture
                      "formats": [F4, "<u8", "<f4", "<i4", "<i4", "u1", "u1"], "offsets": [0, 16, 24, 28, 32, 36, 37], "itemsize": 48})
 
 
+LIGHT_AREA = 4  # include/pathtracer_structs.h PTC_LIGHT_AREA (extension; the reference has no area lights)
+
+
+def area_light(corner, eu, ev, rgb=(1.0, 1.0, 1.0), power=1.0):
+    """One LIGHT record holding a parallelogram emitter, packed as ptc_light_make_area (include/pathtracer_structs.h) packs
+    it: corner + a eu + b ev, emitting power * rgb as radiance towards cross(eu, ev). FAST mode only."""
+    l = np.zeros(1, dtype=LIGHT)
+    l["position"] = (corner[0], corner[1], corner[2], ev[0])
+    l["direction"] = (eu[0], eu[1], eu[2], ev[1])
+    l["color"] = (rgb[0], rgb[1], rgb[2], 1.0)
+    l["power"] = power
+    l["cosOfInnerFallOffAngle"] = ev[2]
+    l["type"] = LIGHT_AREA
+    return l[0]
+
+
 # csrc/pt_wide.cuh DevNode8
 NODE8 = np.dtype([("p", "<f4", 3), ("e", "u1", 3), ("imask", "u1"), ("childBase", "<u4"), ("valid", "<u4"), ("spare", "<u4", 2),
                   ("qlo", "u1", (3, 8)), ("qhi", "u1", (3, 8))])

@@ -5,6 +5,8 @@ for the CPU (oracle/_ref). Bars (BASELINE.json north_star):
     affected by a floating-point tie (fraction of affected pixels reported and bounded)
   * accumulated images: RMSE bound stated in each test
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -609,3 +611,101 @@ def test_bilinear_texture_filtering(scene_factory):
     assert np.percentile(step(b), 99) <= np.percentile(step(a), 99) + 1e-6
     with pytest.raises(pt.PathTracerError):
         pt.PathTracerCUDA(32, 32, mode=pt.MODE_PARITY, flags=pt.FLAG_TEXTURE_BILINEAR)
+
+
+def test_area_light_matches_quadrature(scene_factory, tmp_path):
+    """PTC_LIGHT_AREA (FAST, extension, un-oracled: SURVEY.md 8(f) N4 — BASELINE.json's Cornell configuration names an area
+    light, the reference has none). A 130 x 105 emitter under the Cornell ceiling, depth 1 (direct light only): the rendered
+    radiance of a pixel must converge to albedo / pi * integral over the emitter of V cos cos / d^2, evaluated here by a
+    16 x 16 midpoint rule whose visibility V comes from the (parity-checked) closest-hit probe. Covers lit floor, walls,
+    penumbrae and umbrae behind the boxes. Also: the emitter is one-sided, the samples are a pure function of the path's
+    stream (same bits however the iterations are split over calls), and PARITY refuses the record."""
+    w, h, spp = 160, 120, 512
+    base = scene_factory("cornell", w, h, False)
+    corner, eu, ev = np.array([214.5, 225.5, 540.0]), np.array([0.0, 105.0, 0.0]), np.array([130.0, 0.0, 0.0])  # cross(eu, ev) = -z: faces the floor
+    rgb, power = np.array([1.0, 0.96, 0.9]), 20.0
+    sc = _scene_with_lights(base, tmp_path, [pt.area_light(corner, eu, ev, rgb, power)])
+    with pt.PathTracerCUDA(w, h, ray_max_depth=1, mode=pt.MODE_FAST) as r:
+        r.upload(sc)
+        r.render(0, spp, sync=True)
+        color, nb = r.read_image()
+        img = (color[..., :3] / nb[..., None]).reshape(-1, 3).astype(np.float64)
+        prim = r.trace_primary(0)
+        # quadrature on a subset of the pixels
+        rng = np.random.default_rng(7)
+        ids2 = prim["hit"].reshape(h, w)
+        inner = np.zeros((h, w), bool)      # pixels whose whole footprint lies on one triangle (the jitter of other iterations stays on it)
+        inner[1:-1, 1:-1] = (ids2[1:-1, 1:-1] >= 0) & (ids2[1:-1, 1:-1] == ids2[:-2, 1:-1]) & (ids2[1:-1, 1:-1] == ids2[2:, 1:-1]) & \
+                            (ids2[1:-1, 1:-1] == ids2[1:-1, :-2]) & (ids2[1:-1, 1:-1] == ids2[1:-1, 2:])
+        hit_px = np.flatnonzero(inner.reshape(-1))
+        px = rng.choice(hit_px, 600, replace=False)
+        cam = sc.camera().reshape(4, 4)
+        q = cam[0][None, :3].astype(np.float64) + prim["dir"][px, :3].astype(np.float64) * np.sqrt(prim["dist2"][px].astype(np.float64))[:, None]
+        tri = sc.triangles()[prim["hit"][px]]
+        n = np.stack([tri["N"][a] for a in "xyz"], axis=1).astype(np.float64)
+        facing = (n * prim["dir"][px, :3]).sum(1) > 0
+        n[facing] *= -1
+        mat = sc.materials()[np.where(facing, tri["materialWithNegativeNormalIndex"], tri["materialWithPositiveNormalIndex"])]
+        albedo = np.stack([mat["simpleColor"][a] for a in "xyz"], axis=1).astype(np.float64)
+        g = (np.arange(16) + 0.5) / 16
+        pts = (corner[None, None] + g[:, None, None] * eu[None, None] + g[None, :, None] * ev[None, None]).reshape(-1, 3)
+        ln = np.cross(eu, ev)
+        area = np.linalg.norm(ln)
+        ln /= area
+        full = pts[None] - q[:, None]                      # [pixel, sample, 3]
+        d2 = (full ** 2).sum(2)
+        wdir = full / np.sqrt(d2)[..., None]
+        geom = np.maximum(-(wdir * ln).sum(2), 0) * np.maximum((wdir * n[:, None]).sum(2), 0) / d2
+        o4 = np.concatenate([np.repeat(q, len(pts), axis=0), np.ones((len(px) * len(pts), 1))], axis=1)
+        d4 = np.concatenate([wdir.reshape(-1, 3), np.zeros((len(px) * len(pts), 1))], axis=1)
+        sh = r.trace_rays(o4, d4)
+        vis = ~((sh["hit"] >= 0) & (sh["dist2"].astype(np.float64) < d2.reshape(-1) * (1 - 1e-4)))
+        irr = (geom * vis.reshape(geom.shape)).mean(1) * area
+        expect = albedo * (power * rgb)[None] * (irr / np.pi)[:, None]
+    got = img[px]
+    lit = irr > 0.05 * irr.max()
+    full_vis = vis.reshape(geom.shape).all(1)
+    rel = np.abs(got[:, 0] - expect[:, 0]) / np.maximum(expect[:, 0], 1e-12)
+    print("area light: %d of %d probe pixels lit, %d fully visible; sum ratio %.4f; per-pixel rel. error median %.3f, p95 %.3f (unoccluded)"
+          % (lit.sum(), len(px), (lit & full_vis).sum(), got.sum() / expect.sum(), np.median(rel[lit & full_vis]), np.percentile(rel[lit & full_vis], 95)))
+    if os.environ.get("PTC_TEST_DEBUG"):
+        ids = prim["hit"][px]
+        for t in np.unique(ids):
+            m = ids == t
+            print("  tri %3d: n=%3d N=%s got/expect %.4f (fully visible: %.4f)" % (t, m.sum(), n[m][0], got[m].sum() / max(expect[m].sum(), 1e-12),
+                  got[m & full_vis].sum() / max(expect[m & full_vis].sum(), 1e-12)))
+    assert lit.sum() > 200 and (~full_vis).sum() > 10
+    assert abs(got.sum() / expect.sum() - 1) < 0.01
+    assert np.percentile(rel[lit & full_vis], 95) < 0.10            # Monte-Carlo noise of 512 samples on the geometry term
+    away = geom.max(1) == 0                                          # surfaces above the emitter or facing away from it: exactly black
+    assert away.sum() > 20 and np.all(got[away] == 0)
+    umbra = (vis.reshape(geom.shape).sum(1) == 0) & ~away            # no quadrature point visible: at most a sliver of the emitter is
+    unoccluded = albedo[:, 0] * power * rgb[0] * geom.mean(1) * area / np.pi
+    assert np.all(got[umbra, 0] <= 0.03 * unoccluded[umbra])
+    # one-sided: the same emitter facing the ceiling lights nothing below it
+    up = _scene_with_lights(base, tmp_path, [pt.area_light(corner, ev, eu, rgb, power)])
+    with pt.PathTracerCUDA(w, h, ray_max_depth=1, mode=pt.MODE_FAST) as r:
+        r.upload(up)
+        r.render(0, 4, sync=True)
+        c_up, _ = r.read_image()
+        below = q[:, 2] < 500
+        assert np.all(c_up[..., :3].reshape(-1, 3)[px][below] == 0)
+    # a pure function of the stream: 8 iterations at once == 3 + 5 over two calls, with a point light beside the emitter and bounces
+    both = np.concatenate([base.lights(), np.array([pt.area_light(corner, eu, ev, rgb, power)], dtype=base.lights().dtype)])
+    sc2 = _scene_with_lights(base, tmp_path, both)
+    outs = []
+    for split in ((8,), (3, 5)):
+        with pt.PathTracerCUDA(w, h, ray_max_depth=6, mode=pt.MODE_FAST) as r:
+            r.upload(sc2)
+            first = 0
+            for k in split:
+                r.render(first, k, sync=True)
+                first += k
+            outs.append(r.read_image()[0].copy())
+    assert np.array_equal(outs[0], outs[1])
+    with pt.PathTracerCUDA(w, h, ray_max_depth=6, mode=pt.MODE_FAST) as r:
+        r.upload(base)
+        r.render(0, 8, sync=True)
+        assert outs[0][..., :3].sum() > r.read_image()[0][..., :3].sum()   # the emitter adds light to the point-lit box
+    with pt.PathTracerCUDA(w, h, mode=pt.MODE_PARITY) as r, pytest.raises(pt.PathTracerError):
+        r.upload(sc)
