@@ -171,6 +171,17 @@ PTC_API int ptc_set_camera(ptc_ctx *ctx, const float camera[16]);
 /* Zero imageColor / imageRayNb / imageV / the three histograms and the counters. */
 PTC_API int ptc_reset_accumulation(ptc_ctx *ctx);
 
+/* The reference's `-D SUPER_SAMPLING` build option (globalVars.superSampling, Controleur/PathTracer_OpenCL.cpp:311): from
+ * iteration 6 on Kernel_Main drops a path before tracing it when one more draw of its random stream exceeds
+ * 100 * max_rgb(imageV / n) / X2inv[(uint) n] + 0.05, n = the pixel's sample count (Kernel/PathTracer_FullKernel.cl:1152-1172,
+ * 1219-1222): pixels whose running variance is small stop receiving samples (imageRayNb then differs per pixel; the caller
+ * divides by it as always). The reference ships the table X2inv as an EMPTY file (Kernel/X2inv.cl), so its option cannot
+ * even compile; here the caller supplies it: x2inv[count] (indices beyond the end read the last entry), or x2inv = NULL
+ * for the 95 % chi-square quantiles of n = 0..count-1 degrees of freedom. count = 0 switches it off (the default).
+ * PARITY then renders one iteration per wavefront pass — the reference's sequential loop, decision for decision; FAST
+ * keeps its passes and decides on the statistics at the start of each. Needs imageV (no PTC_FLAG_NO_VARIANCE). */
+PTC_API int ptc_set_supersampling(ptc_ctx *ctx, const float *x2inv, uint32_t count);
+
 /* The body of OpenCL_RunKernel's loop for iterations [first, first+n): enqueue only, returns without
  * waiting. Iteration numbers select the random streams (header.cl:255-264), so disjoint ranges rendered
  * by different contexts / GPUs sum to exactly the paths a single run would trace. */

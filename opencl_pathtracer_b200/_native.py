@@ -65,7 +65,7 @@ class SceneInfo(C.Structure):
 
 
 # every symbol include/pathtracer_cuda.h declares (tests check that the library exports all of them)
-PTC_SYMBOLS = ["ptc_create", "ptc_upload_scene", "ptc_set_camera", "ptc_reset_accumulation", "ptc_render", "ptc_synchronize",
+PTC_SYMBOLS = ["ptc_create", "ptc_upload_scene", "ptc_set_camera", "ptc_reset_accumulation", "ptc_set_supersampling", "ptc_render", "ptc_synchronize",
                "ptc_read_image", "ptc_read_variance", "ptc_read_stats", "ptc_read_rgb8", "ptc_convert_rgb8", "ptc_set_pixel_stripes", "ptc_add_image", "ptc_read_counters",
                "ptc_get_device_buffers", "ptc_trace_primary", "ptc_trace_rays", "ptc_render_single", "ptc_host_alloc", "ptc_host_free",
                "ptc_last_error", "ptc_version", "ptc_device_count", "ptc_destroy", "ptc_wide_bvh_build", "ptc_wide_bvh_read", "ptc_wide_bvh_free", "ptc_measure_read_bandwidth"]
@@ -94,6 +94,7 @@ def cuda_lib():
     L.ptc_upload_scene.argtypes = [vp, P(SceneView)]
     L.ptc_set_camera.argtypes = [vp, P(C.c_float)]
     L.ptc_reset_accumulation.argtypes = [vp]
+    L.ptc_set_supersampling.argtypes = [vp, vp, u32]
     L.ptc_render.argtypes = [vp, u32, u32]
     L.ptc_synchronize.argtypes = [vp]
     L.ptc_read_image.argtypes = [vp, vp, vp]

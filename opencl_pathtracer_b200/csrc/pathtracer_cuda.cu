@@ -106,6 +106,8 @@ struct ptc_ctx
     DevBuf<uint32_t> rayDepths, rayBbx, rayTri;
     ImageDev img{};
     DevBuf<uint8_t> rgb8;
+    DevBuf<float> x2inv;  // ptc_set_supersampling: the chi-square table of the reference's `-D SUPER_SAMPLING` build; empty = off
+    uint32_t x2invSize = 0;
 
     // host-side counters
     uint64_t launches = 0, launchesExtend = 0, launchesConnect = 0;
@@ -302,6 +304,38 @@ int ptc_reset_accumulation(ptc_ctx *ctx)
     }
     ctx->launches = ctx->launchesExtend = ctx->launchesConnect = 0;
     for (double &m : ctx->msStage) m = 0;
+    return PTC_OK;
+}
+
+// `-D SUPER_SAMPLING` of the reference (Controleur/PathTracer_OpenCL.cpp:311; Kernel/PathTracer_FullKernel.cl:1152-1172, 1219-1222).
+int ptc_set_supersampling(ptc_ctx *ctx, const float *x2inv, uint32_t count)
+{
+    if (!ctx) return PTC_ERR_INVALID;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (count == 0)
+    {
+        ctx->x2inv.release();
+        ctx->x2invSize = 0;
+        return PTC_OK;
+    }
+    if (!ctx->imgV.p) return fail(ctx, PTC_ERR_STATE, "supersampling reads imageV: the context was created with PTC_FLAG_NO_VARIANCE");
+    std::vector<float> table(count);
+    if (x2inv) std::memcpy(table.data(), x2inv, sizeof(float) * count);
+    else
+    {
+        // 95 % quantile of the chi-square law with n degrees of freedom (Wilson-Hilferty); entry 0 is never the divisor of a
+        // finite variance (a pixel holds >= 6 samples before the criterion is first evaluated)
+        table[0] = 1.0f;
+        for (uint32_t n = 1; n < count; n++)
+        {
+            const double a = 2.0 / (9.0 * n), c = 1.0 - a + 1.6448536269514722 * std::sqrt(a);
+            table[n] = (float)(n * c * c * c);
+        }
+    }
+    CK(ctx->x2inv.alloc(count));
+    CK(cudaMemcpy(ctx->x2inv.p, table.data(), sizeof(float) * count, cudaMemcpyHostToDevice));
+    ctx->x2invSize = count;
     return PTC_OK;
 }
 
@@ -786,16 +820,23 @@ int runBatch(ptc_ctx *ctx, uint32_t first, uint32_t nIter, bool accumulate, int 
     if (nPaths == 0) return PTC_OK;  // a shard without rows
     Counters *cn = ctx->counters.p;
     cudaStream_t s = ctx->stream;
-    launch_reset(s, cn, nPaths);
+    // supersampling: the queue of bounce 0 holds the paths that survive the reference's early-out instead of being the identity
+    const bool superSampling = accumulate && ctx->x2invSize != 0 && first + nIter > 6u;
+    launch_reset(s, cn, superSampling ? 0u : nPaths);
     {
         StageTimer t(ctx, 0);
         launch_generate(s, ctx->lc, fp, ctx->cam, ctx->st);
+        if (superSampling)
+        {
+            launch_supersample(s, ctx->lc, fp, ctx->st, ctx->img, ctx->x2inv.p, ctx->x2invSize, ctx->queue[0].p, cn);
+            ctx->launches++;
+        }
     }
     ctx->launches += 2;
     const int depth = maxBounces >= 0 ? maxBounces : (int)fp.maxDepth;
     for (int b = 0; b < depth; b++)
     {
-        const uint32_t *qin = b == 0 ? nullptr : ctx->queue[b & 1].p;
+        const uint32_t *qin = b == 0 ? (superSampling ? ctx->queue[0].p : nullptr) : ctx->queue[b & 1].p;
         uint32_t *qout = ctx->queue[(b + 1) & 1].p;
         {
             StageTimer t(ctx, 1);
@@ -909,9 +950,17 @@ int ptc_render(ptc_ctx *ctx, uint32_t first_iteration, uint32_t n_iterations)
     uint32_t done = 0;
     while (done < n_iterations)
     {
-        const uint32_t n = std::min(ctx->batchIters, n_iterations - done);
+        uint32_t n = std::min(ctx->batchIters, n_iterations - done);
+        if (ctx->x2invSize)
+        {
+            // supersampling reads the accumulators of the iterations before: PARITY = the reference's sequential loop, one iteration
+            // per pass; FAST decides on the statistics at the start of a pass, and no pass straddles iteration 6, the first to decide
+            const uint32_t at = first_iteration + done;
+            if (!ctx->fast) n = 1;
+            else if (at < 6u) n = std::min(n, 6u - at);
+        }
         const uint64_t paths = (uint64_t)n * (ctx->stripeRows ? ctx->ownedPix : ctx->nPix);
-        const bool graph = ctx->useGraphs && !(ctx->cfg.flags & PTC_FLAG_STAGE_TIMING) && paths > 0 && paths <= kGraphMaxPaths;
+        const bool graph = ctx->useGraphs && !ctx->x2invSize && !(ctx->cfg.flags & PTC_FLAG_STAGE_TIMING) && paths > 0 && paths <= kGraphMaxPaths;
         int rc = graph ? runBatchGraph(ctx, first_iteration + done, n) : runBatch(ctx, first_iteration + done, n, true, -1);
         if (rc != PTC_OK) return rc;
         done += n;

@@ -519,6 +519,50 @@ __device__ __forceinline__ uint32_t target_pixel(float2 sample, uint32_t W, uint
     return (uint32_t)(py * (int)W + px);
 }
 
+// ------------------------------------------------------------------------------------------------ supersampling
+// `-D SUPER_SAMPLING` (Controleur/PathTracer_OpenCL.cpp:311): Kernel_Main :1219-1222 + superSamplingStopCriteria :1152-1172. From
+// iteration MIN_REFLECTION_NUMBER + 1 = 6 on, a path is dropped before it is traced — nothing is accumulated or counted for
+// it — when one more draw of its stream exceeds 100 * max_rgb(imageV / n) / X2inv[(uint) n] + 0.05, n = the pixel's sample
+// count so far. Runs between k_generate and the first extend: survivors are appended to the queue of bounce 0 (which is
+// the identity without supersampling), dropped paths carry kMetaSkipped for k_accumulate. The statistics read are those
+// of the start of the wavefront pass (PARITY runs one iteration per pass: the reference's sequential loop exactly).
+// x2inv: the caller's table (the reference's Kernel/X2inv.cl is an empty file); the index is clamped to its last entry.
+constexpr uint32_t kMetaSkipped = 0x80000000u;
+__global__ void __launch_bounds__(kStreamThreads) k_supersample(FrameParams fp, PathState st, ImageDev img, const float *__restrict__ x2inv,
+                                                                uint32_t x2invSize, uint32_t *__restrict__ queue0, Counters *cn)
+{
+    const uint32_t nPix = fp.ownedPix;
+    const uint32_t total = nPix * fp.nIterations;
+    const unsigned lane = threadIdx.x & 31u;
+    for (uint32_t k0 = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; k0 < total; k0 += gridDim.x * blockDim.x)
+    {
+        const uint32_t k = k0 + lane;
+        bool alive = k < total;
+        if (alive && fp.firstIteration + k / nPix > 5u)
+        {
+            int seed = st.seed[k];
+            const uint32_t pix = target_pixel(st.sample[k], fp.width, fp.height);
+            const float n = img.rayNb[pix];
+            const float4 v = img.variance[pix];
+            const float sigma2 = fmaxf(fmaxf(v.x / n, v.y / n), v.z / n);
+            uint32_t idx = (uint32_t)n;
+            idx = idx < x2invSize ? idx : x2invSize - 1u;
+            const bool stop = (double)rng_next(seed) > (double)(100.f * sigma2 / x2inv[idx]) + 0.05;
+            st.seed[k] = seed;
+            if (stop)
+            {
+                st.meta[k] = kMetaSkipped;
+                alive = false;
+            }
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, alive);
+        uint32_t base = 0;
+        if (lane == 0 && m) base = atomicAdd(&cn->qcount[0], (uint32_t)__popc(m));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (alive) queue0[base + __popc(m & ((1u << lane) - 1u))] = k;
+    }
+}
+
 // :1339-1349 on one pixel (plain read-modify-write: the caller owns the pixel)
 __device__ __forceinline__ void add_sample(const ImageDev &img, uint32_t pix, float4 x, uint32_t iteration)
 {
@@ -573,6 +617,7 @@ __global__ void __launch_bounds__(kStreamThreads) k_accumulate(FrameParams fp, P
             for (uint32_t li = 0; li < fp.nIterations; li++)
             {
                 const uint32_t k = li * nPix + opix;
+                if (st.meta[k] & kMetaSkipped) continue;  // dropped by k_supersample: the reference's work-item returned at :1221
                 const float4 x = st.rad[k];
                 const uint32_t tp = target_pixel(st.sample[k], fp.width, fp.height);
                 count_path(sDepth, sBbx, sTri, st.meta[k], st.nbbx[k], st.ntri[k]);
@@ -587,6 +632,7 @@ __global__ void __launch_bounds__(kStreamThreads) k_accumulate(FrameParams fp, P
         const uint32_t total = nPix * fp.nIterations;
         for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < total; k += gridDim.x * blockDim.x)
         {
+            if (st.meta[k] & kMetaSkipped) continue;
             count_path(sDepth, sBbx, sTri, st.meta[k], st.nbbx[k], st.ntri[k]);
             add_sample_atomic(img, target_pixel(st.sample[k], fp.width, fp.height), st.rad[k]);
             nPaths++;
@@ -734,6 +780,12 @@ void launch_reset(cudaStream_t s, Counters *cn, uint32_t nPaths) { k_reset<<<1, 
 void launch_generate(cudaStream_t s, const LaunchCfg &lc, const FrameParams &fp, const Camera &cam, const PathState &st)
 {
     k_generate<<<lc.streamGrid, kStreamThreads, 0, s>>>(fp, cam, st);
+}
+
+void launch_supersample(cudaStream_t s, const LaunchCfg &lc, const FrameParams &fp, const PathState &st, const ImageDev &img,
+                        const float *x2inv, uint32_t x2invSize, uint32_t *queue0, Counters *cn)
+{
+    k_supersample<<<lc.streamGrid, kStreamThreads, 0, s>>>(fp, st, img, x2inv, x2invSize, queue0, cn);
 }
 
 template <bool ANY>

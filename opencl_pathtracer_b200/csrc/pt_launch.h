@@ -18,6 +18,9 @@ int traverse_ctas_per_sm(bool fast, bool wide, int stackDepth);
 
 void launch_reset(cudaStream_t s, Counters *cn, uint32_t nPaths);
 void launch_generate(cudaStream_t s, const LaunchCfg &lc, const FrameParams &fp, const Camera &cam, const PathState &st);
+// `-D SUPER_SAMPLING`: drops paths by the reference's variance criterion and builds the queue of bounce 0 (launch_reset with 0 paths first)
+void launch_supersample(cudaStream_t s, const LaunchCfg &lc, const FrameParams &fp, const PathState &st, const ImageDev &img,
+                        const float *x2inv, uint32_t x2invSize, uint32_t *queue0, Counters *cn);
 void launch_extend(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const PathState &st, const uint32_t *queue,
                    Counters *cn, int bounce);
 void launch_connect(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const PathState &st, const uint32_t *queue,

@@ -65,7 +65,6 @@ bool PathTracer_Main(uint image_width, uint image_height, uint numImagesToRender
             m << "The scene has too many lights : it has " << globalVars.lightsSize << " and should be under " << MAX_LIGHT_SIZE;
             throw std::runtime_error(m.str());
         }
-        if (superSampling) throw std::runtime_error("superSampling is not functional in the reference (empty X2inv.cl) and not supported");
         if (exportScene)
         {
             // reference :67-71: dump the imported scene (after the BVH build has ordered the triangles) for a later run

@@ -54,8 +54,12 @@ void CUDA_SetupContext(GlobalVars &globalVars, Sampler sampler)
     cfg.mode = (uint32_t)g_options.mode;
     cfg.iterations_per_batch = g_options.iterationsPerBatch;
     cfg.flags = g_options.flags;
+    if (globalVars.superSampling) cfg.flags &= ~(uint32_t)PTC_FLAG_NO_VARIANCE;  // the criterion reads imageV
     globalVars.sampler = sampler;
     check(ptc_create(&cfg, &g_ctx), "CUDA_SetupContext");
+    // reference Controleur/PathTracer_OpenCL.cpp:311 `-D SUPER_SAMPLING`. Its table file Kernel/X2inv.cl is empty (the option
+    // cannot compile there); the library's own 95 % chi-square quantiles stand in, 4096 entries
+    if (globalVars.superSampling) check(ptc_set_supersampling(g_ctx, nullptr, 4096), "CUDA_SetupContext");
 }
 
 void CUDA_InitializeMemory(GlobalVars &globalVars)

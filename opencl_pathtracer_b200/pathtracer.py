@@ -52,6 +52,15 @@ class PathTracerCUDA:
     def reset(self):
         self._ck(self._lib.ptc_reset_accumulation(self._h))
 
+    def set_supersampling(self, x2inv=None, count=None):
+        """The reference's -D SUPER_SAMPLING early-out with the caller's chi-square table (None + count: the library's 95 %
+        quantiles; count 0: off)."""
+        if x2inv is None:
+            self._ck(self._lib.ptc_set_supersampling(self._h, None, 0 if count is None else count))
+        else:
+            t = np.ascontiguousarray(x2inv, dtype=np.float32)
+            self._ck(self._lib.ptc_set_supersampling(self._h, t.ctypes.data, len(t)))
+
     def render(self, first_iteration, n_iterations, sync=False):
         self._ck(self._lib.ptc_render(self._h, first_iteration, n_iterations))
         if sync:

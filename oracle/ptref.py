@@ -43,6 +43,7 @@ def lib():
         L.ptref_trace_rays.argtypes = [C.POINTER(RefScene), u32, vp, vp, vp, vp, vp, vp, vp]
         L.ptref_rng.argtypes = [u32, u32, u32, u32, u32, C.c_int, vp, vp, vp]
         L.ptref_cosine_sample.argtypes = [C.c_int32, vp, vp, vp]
+        L.ptref_x2inv.argtypes = [vp, C.c_int]
         _lib = L
     return _lib
 
@@ -90,6 +91,16 @@ def render(scene, W, H, max_depth, sampler, it_begin, it_end, nthreads=0, acc=No
                                  acc["rayIntersectedBBx"].ctypes.data, acc["rayIntersectedTri"].ctypes.data, nthreads)
     assert rc == 0
     return acc
+
+
+SAMPLER_JITTERED_SUPERSAMPLING = 3  # ref_glue.cpp: the JITTERED kernel built with -D SUPER_SAMPLING
+
+
+def x2inv():
+    """The chi-square table the SUPER_SAMPLING build of the reference kernel indexes (oracle/shim/X2inv.cl)."""
+    out = np.zeros(4096, np.float32)
+    n = lib().ptref_x2inv(out.ctypes.data, len(out))
+    return out[:n].copy()
 
 
 def primary(scene, W, H, sampler=0, iteration=0):

@@ -61,6 +61,20 @@ namespace refk_random
 #undef PATHTRACER_KERNEL
 #undef NULL
 
+// SAMPLE_JITTERED again with `-D SUPER_SAMPLING` (Controleur/PathTracer_OpenCL.cpp:311): the adaptive early-out of
+// Kernel_Main (:1219-1222, superSamplingStopCriteria :1152-1172) against the supplied X2inv.cl table
+namespace refk_jittered_ss
+{
+#include "ocl_as_cxx.h"
+#define SAMPLE_JITTERED
+#define SUPER_SAMPLING 1
+#include "PathTracer_FullKernel.cl"
+#undef SUPER_SAMPLING
+#undef SAMPLE_JITTERED
+}  // namespace refk_jittered_ss
+#undef PATHTRACER_KERNEL
+#undef NULL
+
 namespace refk_uniform
 {
 #include "ocl_as_cxx.h"
@@ -162,7 +176,8 @@ static void set_options(uint32_t W, uint32_t H, uint32_t maxDepth, uint32_t ligh
 // Launch loop: Controleur/PathTracer_OpenCL.cpp:76-107. Output buffers are accumulated into (the caller
 // zeroes them before the first call), so consecutive iteration ranges can be rendered by consecutive calls.
 // sampler: 0 JITTERED, 1 RANDOM, 2 UNIFORM (Controleur/PathTracer_Structs.h:130-135). RANDOM scatters to
-// arbitrary pixels without atomics in the reference, so it is run on one thread here.
+// arbitrary pixels without atomics in the reference, so it is run on one thread here. 3 = JITTERED built with
+// `-D SUPER_SAMPLING`. ptref_x2inv exposes the table that build reads (oracle/shim/X2inv.cl).
 int ptref_render_rows(const ptref_scene *s, uint32_t W, uint32_t H, uint32_t maxDepth, int sampler, uint32_t iterBegin,
                       uint32_t iterEnd, uint32_t rowBegin, uint32_t rowEnd, float *imageColor, float *imageRayNb, float *imageV,
                       uint32_t *rayDepths, uint32_t *bbx, uint32_t *tri, int nthreads);
@@ -197,6 +212,7 @@ int ptref_render_rows(const ptref_scene *s, uint32_t W, uint32_t H, uint32_t max
                 ocl_shim::gid[0] = x;
                 if (sampler == 0) LAUNCH(refk_jittered);
                 else if (sampler == 1) LAUNCH(refk_random);
+                else if (sampler == 3) LAUNCH(refk_jittered_ss);  // JITTERED + SUPER_SAMPLING
                 else LAUNCH(refk_uniform);
             }
         }
@@ -287,6 +303,14 @@ int ptref_trace_rays(const ptref_scene *s, uint32_t n, const float *origin, cons
         counts[2 * p + 1] = r.numIntersectedTri;
     }
     return 0;
+}
+
+// The stand-in chi-square table the SUPER_SAMPLING build indexes (the reference's Kernel/X2inv.cl is empty).
+int ptref_x2inv(float *out, int capacity)
+{
+    const int n = (int)(sizeof(refk_jittered_ss::X2inv) / sizeof(float));
+    for (int i = 0; i < n && i < capacity; i++) out[i] = refk_jittered_ss::X2inv[i];
+    return n;
 }
 
 // RNG known-answer helper: InitializeRandomSeed (header.cl:255-264) then n draws of random() (:246-253).

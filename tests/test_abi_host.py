@@ -99,3 +99,25 @@ def test_bmp_writer(tmp_path):
     if N.cuda_lib().ptc_device_count() == 0:
         r = subprocess.run([exe, "cornell", "16", "16", "1", "2", "0", "0", "1", str(tmp_path) + "/"], capture_output=True, text=True)
         assert r.returncode == 1 and "ERROR" in r.stderr
+
+
+def test_area_light_record_packing(tmp_path):
+    """PTC_LIGHT_AREA (extension): the C helper of include/pathtracer_structs.h, compiled as plain C, the Python helper and the
+    procedural importer's "cornell_area" scene pack the emitter into the 64-byte reference Light record the same way."""
+    import numpy as np
+    import opencl_pathtracer_b200 as pt
+    from opencl_pathtracer_b200 import scene as S
+    src = tmp_path / "a.c"
+    src.write_text('#include <stdio.h>\n#include "pathtracer_structs.h"\nint main(void){ptc_light l; float c[3]={227,213,548.7f},u[3]={0,130,0},v[3]={105,0,0},'
+                   'rgb[3]={1,0.96f,0.9f}; ptc_light_make_area(&l,c,u,v,rgb,100.f); fwrite(&l,sizeof l,1,stdout); return 0;}\n')
+    exe = tmp_path / "a.out"
+    subprocess.run(["gcc", "-std=c99", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    raw = subprocess.run([str(exe)], capture_output=True, check=True).stdout
+    assert len(raw) == 64
+    from_c = np.frombuffer(raw, dtype=S.LIGHT)[0]
+    from_py = pt.area_light((227, 213, 548.7), (0, 130, 0), (105, 0, 0), (1, 0.96, 0.9), 100.0)
+    assert from_c.tobytes() == from_py.tobytes()
+    sc = pt.Scene("cornell_area", 32, 24)
+    lights = sc.lights()
+    assert len(lights) == 1 and lights[0].tobytes() == from_py.tobytes()
+    assert int(lights[0]["type"]) == S.LIGHT_AREA == 4

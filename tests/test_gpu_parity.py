@@ -709,3 +709,58 @@ def test_area_light_matches_quadrature(scene_factory, tmp_path):
         assert outs[0][..., :3].sum() > r.read_image()[0][..., :3].sum()   # the emitter adds light to the point-lit box
     with pt.PathTracerCUDA(w, h, mode=pt.MODE_PARITY) as r, pytest.raises(pt.PathTracerError):
         r.upload(sc)
+
+
+def test_supersampling_matches_reference_build(ptref, scene_factory):
+    """`-D SUPER_SAMPLING` (a4: Kernel_Main :1219-1222, superSamplingStopCriteria :1152-1172). The reference ships an empty
+    X2inv.cl, so the option cannot compile there; the oracle is the reference kernel built with the option and the table of
+    oracle/shim/X2inv.cl, and the library is handed the same table. PARITY replays the sequential loop: which (pixel, iteration)
+    paths are dropped must agree with the reference except where a pixel's variance differs in the last bits (cos / sin of
+    the bounce directions, the 1e-3 radiance tolerance) — reported and bounded. FAST decides per wavefront pass on the same
+    criterion: same order of magnitude of dropped paths, same image in expectation. Without the table nothing is dropped."""
+    w, h, depth, n_it = 128, 96, 5, 30
+    sc = scene_factory("cornell", w, h, False)
+    table = ptref.x2inv()
+    ref = ptref.render(sc, w, h, depth, ptref.SAMPLER_JITTERED_SUPERSAMPLING, 0, n_it)
+    plain = ptref.render(sc, w, h, depth, 0, 0, n_it)
+    assert ref["imageRayNb"].sum() < 0.8 * plain["imageRayNb"].sum()      # the criterion does drop paths on this scene
+    with pt.PathTracerCUDA(w, h, ray_max_depth=depth, mode=pt.MODE_PARITY) as r:
+        r.upload(sc)
+        r.set_supersampling(table)
+        r.render(0, 10)
+        r.render(10, n_it - 10, sync=True)     # split over calls: the statistics carry over
+        color, nb = r.read_image()
+        depths, bbx, tri = r.read_stats()
+    differ = nb != ref["imageRayNb"]
+    print("supersampling PARITY: %d of %d paths kept (reference %d); pixels whose sample count differs: %d of %d"
+          % (nb.sum(), w * h * n_it, ref["imageRayNb"].sum(), differ.sum(), w * h))
+    assert differ.mean() < 5e-3
+    assert abs(float(nb.sum()) / float(ref["imageRayNb"].sum()) - 1) < 1e-3
+    assert abs(int(depths.sum()) - int(ref["rayDepths"].sum())) <= 8 * max(int(differ.sum()), 1)
+    assert int(depths.sum()) == int(nb.sum())                              # a dropped path is not counted anywhere
+    same = ~differ
+    a, b = color[same], ref["imageColor"][same]
+    bad = np.abs(a - b) > 1e-3 * np.maximum(np.abs(a), np.abs(b)) * np.sqrt(n_it) + 1e-5
+    assert bad.any(axis=1).mean() < 5e-3
+    # FAST: wavefront passes of several iterations, the decision reads the statistics at the start of the pass
+    with pt.PathTracerCUDA(w, h, ray_max_depth=depth, mode=pt.MODE_FAST, iterations_per_batch=4) as r:
+        r.upload(sc)
+        r.set_supersampling(None, 256)         # the library's own 95 % chi-square quantiles
+        r.render(0, n_it, sync=True)
+        cf, nf = r.read_image()
+        assert nf.min() >= 6 and nf.max() <= n_it
+        assert 0.5 < nf.sum() / nb.sum() < 2.0
+        mean_f = (cf[..., :3] / nf[..., None]).mean()
+        mean_p = (plain["imageColor"][..., :3] / plain["imageRayNb"][..., None]).mean()
+        mean_r = (ref["imageColor"][..., :3] / ref["imageRayNb"][..., None]).mean()
+        print("supersampling FAST: %d paths kept, image mean %.5f; reference with the option %.5f, without %.5f"
+              % (nf.sum(), mean_f, mean_r, mean_p))
+        # stopping on a small running variance is a biased rule (a pixel stops while its rare bright samples are still missing):
+        # the reference's own image is darker with the option than without; FAST must reproduce THAT image
+        assert abs(mean_f / mean_r - 1) < 0.03
+        r.set_supersampling(None, 0)
+        r.reset()
+        r.render(0, 8, sync=True)
+        assert np.all(r.read_image()[1] == 8)
+    with pt.PathTracerCUDA(w, h, mode=pt.MODE_FAST, flags=pt.FLAG_NO_VARIANCE) as r, pytest.raises(pt.PathTracerError):
+        r.set_supersampling(None, 64)
