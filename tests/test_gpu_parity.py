@@ -764,3 +764,27 @@ def test_supersampling_matches_reference_build(ptref, scene_factory):
         assert np.all(r.read_image()[1] == 8)
     with pt.PathTracerCUDA(w, h, mode=pt.MODE_FAST, flags=pt.FLAG_NO_VARIANCE) as r, pytest.raises(pt.PathTracerError):
         r.set_supersampling(None, 64)
+
+
+def test_supersampling_against_committed_golden(scene_factory):
+    """The same check without oracle/_ref: PARITY with the table of the golden file against tests/golden/supersampling_vectors.npz
+    (generated from the reference kernel built with `-D SUPER_SAMPLING`, tests/golden/make_golden_supersampling.py)."""
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "supersampling_vectors.npz"))
+    w, h, depth, n_it = (int(v) for v in g["case"])
+    sc = scene_factory("cornell", w, h, False)
+    with pt.PathTracerCUDA(w, h, ray_max_depth=depth, mode=pt.MODE_PARITY) as r:
+        r.upload(sc)
+        r.set_supersampling(g["x2inv"])
+        r.render(0, n_it, sync=True)
+        color, nb = r.read_image()
+        depths, bbx, tri = r.read_stats()
+    differ = nb != g["imageRayNb"]
+    print("supersampling vs golden: %d paths kept (golden %d), %d of %d pixels differ in their sample count"
+          % (nb.sum(), g["imageRayNb"].sum(), differ.sum(), w * h))
+    assert differ.mean() < 5e-3
+    if not differ.any():
+        assert np.array_equal(depths, g["rayDepths"][:len(depths)])
+        assert np.array_equal(bbx, g["rayIntersectedBBx"]) and np.array_equal(tri, g["rayIntersectedTri"])
+    a, b = color[~differ], g["imageColor"][~differ]
+    bad = np.abs(a - b) > 1e-3 * np.maximum(np.abs(a), np.abs(b)) * np.sqrt(n_it) + 1e-5
+    assert bad.any(axis=1).mean() < 5e-3

@@ -1,6 +1,7 @@
 """CPU: the oracle (reference kernel + builder compiled from /root/reference) against the committed golden vectors,
 and properties of the reference's own algorithm (its in-kernel ASSERTs) restated as tests."""
 import hashlib
+import os
 
 import numpy as np
 import pytest
@@ -101,3 +102,17 @@ def test_row_sample_is_a_subset(ptref, scene_factory):
     part = ptref.render(sc, 64, 48, 10, 0, 0, 1, rows=(10, 20))
     assert np.array_equal(part["imageColor"][10:20].view(np.uint32), full["imageColor"][10:20].view(np.uint32))
     assert part["imageRayNb"].sum() == 10 * 64
+
+
+def test_supersampling_build_matches_golden(ptref, scene_factory):
+    """The reference kernel built with `-D SUPER_SAMPLING` (Controleur/PathTracer_OpenCL.cpp:311; the table of
+    oracle/shim/X2inv.cl stands in for the reference's empty Kernel/X2inv.cl) against tests/golden/supersampling_vectors.npz:
+    bit-exact accumulators, i.e. the same paths dropped."""
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "supersampling_vectors.npz"))
+    w, h, depth, n_it = (int(v) for v in g["case"])
+    assert np.array_equal(ptref.x2inv(), g["x2inv"])
+    sc = scene_factory("cornell", w, h, False)
+    acc = ptref.render(sc, w, h, depth, ptref.SAMPLER_JITTERED_SUPERSAMPLING, 0, n_it)
+    for k in ("imageColor", "imageRayNb", "imageV", "rayDepths", "rayIntersectedBBx", "rayIntersectedTri"):
+        assert np.array_equal(acc[k], g[k]), k
+    assert g["imageRayNb"].min() >= 6 and g["imageRayNb"].sum() < 0.8 * w * h * n_it
