@@ -60,7 +60,9 @@ typedef struct PTC_ALIGN(16) ptc_light
 /* PTC_LIGHT_AREA record: the parallelogram corner + a*eu + b*ev, (a, b) in [0,1)^2, emitting `power` x `color` as
  * radiance towards cross(eu, ev) only. Each lit hit connects to ONE point of it, drawn from the path's own random stream
  * (next-event estimation); the estimator is power * color * BRDF * cos(surface) * cos(light) * area / distance^2. The
- * emitter has no geometry of its own: camera and bounce rays do not see it, exactly like the reference's point lights.
+ * emitter has no triangles of its own; camera rays and rays leaving a specular event (glass, water, the mirror branch of
+ * varnish) that cross it from its emitting side before their geometric hit end there with its radiance (it is visible and
+ * is reflected); rays leaving a diffuse vertex pass through it, since that vertex has sampled it already.
  * Its shadow rays are bounded by the squared distance to the sampled point, i.e. every occluder in front of it counts (the
  * reference's own light types hand a LENGTH to a squared-distance test, Kernel/PathTracer_FullKernel.cl:938-944, which both
  * modes reproduce for them).

@@ -123,6 +123,7 @@ __device__ __forceinline__ void flush_work(Counters *cn, unsigned long long *ray
 //   * majority vote — the warp executes node steps while at least half of its rays wait for a node, then triangle
 //     tests while those are the majority, so the two code paths are never serialised against each other.
 // The unlit / miss flags in st.occl (bits 31, 30) are written by extend and let connect drop items at staging time.
+constexpr uint32_t kMetaSpecular = 0x200u;  // st.meta bit 9 (area-light variant only): the ray was sampled by a specular event
 constexpr uint32_t kOcclUnlit = 0x80000000u, kOcclMiss = 0x40000000u, kOcclMask = 0x3fffffffu;
 constexpr uint32_t kLightShift = 27;  // staged item word: path slot | light << 27 (ptc_create keeps slots below 2^27)
 
@@ -369,7 +370,14 @@ __global__ void __launch_bounds__(kStreamThreads, 4) k_shade(SceneDev sc, FrameP
             float4 T = st.thr[p], rad = st.rad[p];
             uint32_t meta = st.meta[p];
             const int tri = __float_as_int(h.x);
-            if (tri < 0)
+            float4 emitted;
+            // area lights (extension): a camera ray or a specular chain that reaches an emitter ends there with its radiance
+            if (FAST == 2 && ((meta & 0xffu) == 0u || (meta & kMetaSpecular)) && emitter_seen(sc, o, d, tri < 0 ? INFINITY : h.w, emitted))
+            {
+                rad = rad + emitted * T;
+                st.rad[p] = rad;
+            }
+            else if (tri < 0)
             {
                 // :1281-1288 sky
                 rad = rad + sky_color(sc, d) * T;
@@ -429,6 +437,7 @@ __global__ void __launch_bounds__(kStreamThreads, 4) k_shade(SceneDev sc, FrameP
                 // the cosine-weighted bounce of MAT_STANDART and of the diffuse branch of MAT_VARNHISHED is drawn in one place,
                 // after the per-material part, so that the lanes of both materials run it together (same draws, same order)
                 bool diffuseBounce = false;
+                bool specular = mat.type == 1 || mat.type == 2;  // only read by the area-light variant
                 if (mat.type == 0)
                 {
                     T = T * color;
@@ -460,14 +469,14 @@ __global__ void __launch_bounds__(kStreamThreads, 4) k_shade(SceneDev sc, FrameP
                 {
                     add = add + L * color * T;
                     const float rF = fresnel_varnish(d, Ns);
-                    if (rng_next(seed) < rF) out = d - (Ns * (2 * dot4(d, Ns)));
+                    if (rng_next(seed) < rF) { out = d - (Ns * (2 * dot4(d, Ns))); specular = true; }
                     else { diffuseBounce = true; T = T * color; }
                 }
                 if (diffuseBounce) out = cosine_sample_hemisphere(seed, Ns);
                 put_in_same_hemisphere(out, Nref);
                 rad = rad + add;
                 const uint32_t refl = (meta & 0xffu) + 1u;
-                meta = refl | (inWater ? 0x100u : 0u);
+                meta = refl | (inWater ? 0x100u : 0u) | ((FAST == 2 && specular) ? kMetaSpecular : 0u);
                 st.org[p] = q + 0.001f * out;  // :880
                 st.dir[p] = normalize4(out);
                 st.thr[p] = T;

@@ -158,6 +158,36 @@ __device__ __forceinline__ DevLight light_resolve(DevLight l, int seed)
     return l;
 }
 
+// PTC_LIGHT_AREA emitters seen directly (extension): the nearest emitter the ray (o, d) crosses from its emitting side before
+// `tBest` (the ray parameter of the geometric hit, INFINITY on a miss). Three-lane arithmetic: a w lane the reference's quirks
+// may have left in o or d plays no part here. Used for camera rays and after specular bounces only — a diffuse
+// vertex has already sampled the emitter itself (next-event estimation), so its bounce ray passes through it.
+__device__ __forceinline__ bool emitter_seen(const SceneDev &sc, float4 o, float4 d, float tBest, float4 &radiance)
+{
+    bool seen = false;
+    for (uint32_t li = 0; li < sc.nLights; li++)
+    {
+        const DevLight l = sc.lights[li];
+        if (l.type != 4) continue;
+        const float4 eu = f4(l.direction.x, l.direction.y, l.direction.z, 0.f), ev = f4(l.position.w, l.direction.w, l.cosInner, 0.f);
+        const float4 n = cross3(eu, ev);
+        const float denom = (n.x * d.x + n.y * d.y) + n.z * d.z;
+        if (!(denom < 0.f)) continue;  // one-sided
+        const float4 c = f4(l.position.x - o.x, l.position.y - o.y, l.position.z - o.z, 0.f);
+        const float t = ((n.x * c.x + n.y * c.y) + n.z * c.z) / denom;
+        if (!(t > 0.001f) || !(t < tBest)) continue;
+        const float4 p = f4(d.x * t - c.x, d.y * t - c.y, d.z * t - c.z, 0.f);
+        const float nn = (n.x * n.x + n.y * n.y) + n.z * n.z;
+        const float4 pa = cross3(p, ev), pb = cross3(eu, p);
+        const float a = ((pa.x * n.x + pa.y * n.y) + pa.z * n.z) / nn, b = ((pb.x * n.x + pb.y * n.y) + pb.z * n.z) / nn;
+        if (a < 0.f || a > 1.f || b < 0.f || b > 1.f) continue;
+        tBest = t;
+        radiance = l.color * l.power;
+        seen = true;
+    }
+    return seen;
+}
+
 // cos/sin: the reference calls OpenCL's cos/sin (implementation-defined accuracy); the oracle build uses
 // glibc cosf/sinf (< 1 ulp). They are evaluated in double here and rounded once, which yields the
 // correctly rounded float and therefore agrees with the oracle in all but a ~1e-7 fraction of calls.

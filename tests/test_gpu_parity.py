@@ -618,7 +618,8 @@ def test_area_light_matches_quadrature(scene_factory, tmp_path):
     light, the reference has none). A 130 x 105 emitter under the Cornell ceiling, depth 1 (direct light only): the rendered
     radiance of a pixel must converge to albedo / pi * integral over the emitter of V cos cos / d^2, evaluated here by a
     16 x 16 midpoint rule whose visibility V comes from the (parity-checked) closest-hit probe. Covers lit floor, walls,
-    penumbrae and umbrae behind the boxes. Also: the emitter is one-sided, the samples are a pure function of the path's
+    penumbrae and umbrae behind the boxes. Camera rays that cross the emitter from below show its radiance (emitters are seen
+    directly by camera rays and through specular chains; diffuse vertices sample them). Also: the emitter is one-sided, the samples are a pure function of the path's
     stream (same bits however the iterations are split over calls), and PARITY refuses the record."""
     w, h, spp = 160, 120, 512
     base = scene_factory("cornell", w, h, False)
@@ -637,6 +638,28 @@ def test_area_light_matches_quadrature(scene_factory, tmp_path):
         inner = np.zeros((h, w), bool)      # pixels whose whole footprint lies on one triangle (the jitter of other iterations stays on it)
         inner[1:-1, 1:-1] = (ids2[1:-1, 1:-1] >= 0) & (ids2[1:-1, 1:-1] == ids2[:-2, 1:-1]) & (ids2[1:-1, 1:-1] == ids2[2:, 1:-1]) & \
                             (ids2[1:-1, 1:-1] == ids2[1:-1, :-2]) & (ids2[1:-1, 1:-1] == ids2[1:-1, 2:])
+        # pixels whose camera ray crosses the emitter (from below) before it reaches geometry show the emitter itself
+        cam_o = sc.camera().reshape(4, 4)[0, :3].astype(np.float64)
+        dirs = prim["dir"][:, :3].astype(np.float64)
+        en = np.cross(eu, ev)
+        den = dirs @ en
+        with np.errstate(divide="ignore", invalid="ignore"):
+            te = ((corner - cam_o) @ en) / den
+            pe = cam_o[None] + dirs * te[:, None] - corner[None]
+            ea = np.cross(pe, ev[None]) @ en / (en @ en)
+            eb = np.cross(eu[None], pe) @ en / (en @ en)
+        t_geo = np.where(prim["hit"] >= 0, np.sqrt(prim["dist2"].astype(np.float64)), np.inf)
+        sees = (den < 0) & (te > 0) & (te < t_geo) & (ea > 0.02) & (ea < 0.98) & (eb > 0.02) & (eb < 0.98)
+        r1 = r.render_single(0).reshape(-1, 4)
+        assert sees.sum() > 20
+        assert np.allclose(r1[sees, :3], (power * rgb)[None].astype(np.float32), rtol=1e-6)
+        near = (den < 0) & (te > 0) & (te < t_geo) & (ea > -0.05) & (ea < 1.05) & (eb > -0.05) & (eb < 1.05)
+        near = near.reshape(h, w)
+        grown = near.copy()                   # + the 8 neighbours: the other iterations' jitter stays inside the pixel
+        for dy in (-1, 0, 1):
+            for dx in (-1, 0, 1):
+                grown[max(dy, 0):h + min(dy, 0), max(dx, 0):w + min(dx, 0)] |= near[max(-dy, 0):h + min(-dy, 0), max(-dx, 0):w + min(-dx, 0)]
+        inner &= ~grown
         hit_px = np.flatnonzero(inner.reshape(-1))
         px = rng.choice(hit_px, 600, replace=False)
         cam = sc.camera().reshape(4, 4)
