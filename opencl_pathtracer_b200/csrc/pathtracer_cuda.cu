@@ -82,7 +82,7 @@ struct ptc_ctx
     DevBuf<uint4> textures;
     DevBuf<uchar4> texels;
     DevBuf<uint32_t> bigLeaf;
-    DevBuf<DevNode8> nodes8;  // FAST + wide BVH only
+    DevBuf<DevNode8P> nodes8;  // FAST + wide BVH only; padded records, see pt_wide.cuh
     DevBuf<DevTri> tris8;
     DevBuf<uint32_t> tri8Index;
     bool wide = false;
@@ -672,7 +672,9 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
     CK(up(ctx->textures.p, hTex.data(), sizeof(uint4) * nX));
     CK(up(ctx->texels.p, s->textures_data, sizeof(uchar4) * nTexel));
     CK(up(ctx->bigLeaf.p, bigLeaf.data(), sizeof(uint32_t) * bigLeaf.size()));
-    CK(up(ctx->nodes8.p, wideBvh.nodes.data(), sizeof(DevNode8) * wideBvh.nodes.size()));
+    if (!wideBvh.nodes.empty())
+        CK(cudaMemcpy2DAsync(ctx->nodes8.p, sizeof(DevNode8P), wideBvh.nodes.data(), sizeof(DevNode8), sizeof(DevNode8), wideBvh.nodes.size(),
+                             cudaMemcpyHostToDevice, ctx->stream));
     CK(up(ctx->tris8.p, hTris8.data(), sizeof(DevTri) * hTris8.size()));
     CK(up(ctx->tri8Index.p, wideBvh.triOrder.data(), sizeof(uint32_t) * wideBvh.triOrder.size()));
     CK(cudaStreamSynchronize(ctx->stream));  // host staging vectors die at return
@@ -694,7 +696,19 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
             cudaFree(dw.nodes); cudaFree(dw.tris8); cudaFree(dw.tri8Index);
             return fail(ctx, PTC_ERR_LIMIT, "wide BVH of %u levels", dw.depth);
         }
-        ctx->nodes8.adopt(dw.nodes, dw.nNodes);
+        {
+            // the device builder emits 80-byte records: re-pitch them to the padded layout the traversal reads
+            cudaError_t e = ctx->nodes8.alloc(dw.nNodes);
+            if (e == cudaSuccess && dw.nNodes)
+                e = cudaMemcpy2DAsync(ctx->nodes8.p, sizeof(DevNode8P), dw.nodes, sizeof(DevNode8), sizeof(DevNode8), dw.nNodes, cudaMemcpyDeviceToDevice, ctx->stream);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+            cudaFree(dw.nodes);
+            if (e != cudaSuccess)
+            {
+                cudaFree(dw.tris8); cudaFree(dw.tri8Index);
+                return fail(ctx, PTC_ERR_CUDA, "wide BVH re-pitch: %s", cudaGetErrorString(e));
+            }
+        }
         ctx->tris8.adopt(dw.tris8, (size_t)dw.nNodes * kTriSlots);
         ctx->tri8Index.adopt(dw.tri8Index, (size_t)dw.nNodes * kTriSlots);
         nNodes8 = dw.nNodes;
@@ -766,7 +780,7 @@ int ptc_wide_bvh_read(ptc_ctx *ctx, ptc_wide_bvh *out)
         return fail(ctx, PTC_ERR_INVALID, "ptc_wide_bvh_read: out of memory");
     }
     cudaError_t e = cudaStreamSynchronize(ctx->stream);
-    if (e == cudaSuccess && nNodes) e = cudaMemcpy(out->nodes, ctx->nodes8.p, sizeof(DevNode8) * nNodes, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess && nNodes) e = cudaMemcpy2D(out->nodes, sizeof(DevNode8), ctx->nodes8.p, sizeof(DevNode8P), sizeof(DevNode8), nNodes, cudaMemcpyDeviceToHost);
     if (e == cudaSuccess && nRec) e = cudaMemcpy(out->tri_order, ctx->tri8Index.p, sizeof(uint32_t) * nRec, cudaMemcpyDeviceToHost);
     if (e != cudaSuccess)
     {

@@ -87,7 +87,7 @@ struct SceneDev
     const uchar4 *texels;
     const uint32_t *bigLeafCount;  // may be null
     // FAST mode with the wide BVH (pt_wide.cuh); null / 0 otherwise
-    const struct DevNode8 *nodes8;
+    const struct DevNode8P *nodes8;  // 96-byte padded records (pt_wide.cuh)
     const DevTri *tris8;           // the intersection records again, in wide order
     const uint32_t *tri8Index;     // wide order -> BVH order
     uint32_t nNodes8;

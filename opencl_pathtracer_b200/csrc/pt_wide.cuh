@@ -32,6 +32,17 @@ struct __align__(16) DevNode8
 };
 static_assert(sizeof(DevNode8) == 80, "DevNode8");
 
+// The node as the traversal kernels see it: padded to 96 bytes so that every record is 32-byte aligned and is fetched by
+// three 256-bit loads (LDG.E.256) instead of five 128-bit ones — per warp of incoherent rays 96 instead of 160 L1 wavefronts
+// per node visit. The builders, the inspection ABI (ptc_wide_bvh) and the tests keep the 80-byte record; ptc_upload_scene
+// copies with a pitch.
+struct __align__(32) DevNode8P
+{
+    DevNode8 n;
+    uint32_t pad[4];
+};
+static_assert(sizeof(DevNode8P) == 96, "DevNode8P");
+
 struct WideLane
 {
     Ray r;             // ix, iy, iz clamped to finite values
@@ -133,8 +144,11 @@ __device__ __forceinline__ void lane_node_step(WideLane &L, const SceneDev &sc, 
     const uint32_t rest = hits & ~(1u << bit);
     const uint32_t rel = (uint32_t)__popc(hits & 0xffu & ((1u << slot) - 1u));
     const uint32_t node = L.gx + rel;
-    const uint4 *np = reinterpret_cast<const uint4 *>(sc.nodes8 + node);
-    const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+    const char *np = reinterpret_cast<const char *>(sc.nodes8 + node);
+    uint4 n0, n1, n2, n3, n4, n5;
+    ldg256(np, reinterpret_cast<float4 &>(n0), reinterpret_cast<float4 &>(n1));
+    ldg256(np + 32, reinterpret_cast<float4 &>(n2), reinterpret_cast<float4 &>(n3));
+    ldg256(np + 64, reinterpret_cast<float4 &>(n4), reinterpret_cast<float4 &>(n5));  // n5 = padding
     if (L.ty != 0u)
     {
         stk[0] = make_uint2(L.tx, L.ty);  // park the untested triangles (wants_node: the slot is free)
