@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_DIR = os.path.join(_HERE, "_lib")
+LIB_DIR = os.environ.get("PTC_LIB_DIR") or os.path.join(_HERE, "_lib")  # PTC_LIB_DIR: A/B builds of the kernels (scripts/build_variant.sh)
 
 PTC_OK = 0
 PTC_ERR_INVALID, PTC_ERR_CUDA, PTC_ERR_NO_DEVICE, PTC_ERR_STATE, PTC_ERR_LIMIT, PTC_ERR_UNSUPPORTED = 1, 2, 3, 4, 5, 6
