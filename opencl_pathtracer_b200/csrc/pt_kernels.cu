@@ -17,7 +17,10 @@
 
 namespace ptc
 {
-constexpr int kTraverseThreads = 128;
+#ifndef PTC_TRAVERSE_THREADS
+#define PTC_TRAVERSE_THREADS 128  // A/B: scripts/build_variant.sh t64 -DPTC_TRAVERSE_THREADS=64
+#endif
+constexpr int kTraverseThreads = PTC_TRAVERSE_THREADS;
 constexpr uint32_t kFlagRussianRoulette = 1u << 5;  // PTC_FLAG_RUSSIAN_ROULETTE (include/pathtracer_cuda.h)
 constexpr uint32_t kFlagTextureBilinear = 1u << 6;  // PTC_FLAG_TEXTURE_BILINEAR
 constexpr int kStreamThreads = 256;
@@ -149,7 +152,7 @@ constexpr size_t kGroupBytes = sizeof(PathGroup) * (kTraverseThreads / 32);
 // FAST: 0 = PARITY, 1 = FAST, 2 = FAST for a scene with area lights (extension; connect only — scenes without one run the
 // kernels they always ran)
 template <bool ANY, int FAST, typename LaneT>
-__global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas) k_trace(SceneDev sc, PathState st, const uint32_t *__restrict__ queue,
+__global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas * 128 / kTraverseThreads) k_trace(SceneDev sc, PathState st, const uint32_t *__restrict__ queue,
                                                            Counters *__restrict__ cn, int bounce, uint32_t popMin, int stackDepth)
 {
     typedef typename LaneT::StackT StackT;

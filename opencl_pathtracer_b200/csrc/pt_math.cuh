@@ -50,14 +50,6 @@ __device__ __forceinline__ void ldg256(const void *p, float4 &a, float4 &b)
                  : "l"(p));
 }
 
-// the same without allocating the line in L1 (triangle records: touched once per ray)
-__device__ __forceinline__ void ldg256_noalloc(const void *p, float4 &a, float4 &b)
-{
-    asm volatile("ld.global.nc.L1::no_allocate.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
-                 : "l"(p));
-}
-
 // OpenCL max(x, y) = (x < y) ? y : x  — NOT fmaxf (differs on NaN)
 __device__ __forceinline__ float clmax(float x, float y) { return x < y ? y : x; }
 

@@ -115,9 +115,8 @@ __device__ __forceinline__ bool tri_test(const DevTri *__restrict__ tris, uint32
                                          int prevHit = -1)
 {
     float4 n, p, e1, e2;
-    // not allocated in L1: a triangle record is touched once per ray, the upper tree levels again and again
-    ldg256_noalloc(&tris[i].n, n, p);
-    ldg256_noalloc(&tris[i].e1, e1, e2);
+    ldg256(&tris[i].n, n, p);
+    ldg256(&tris[i].e1, e1, e2);
     const float nd = ((n.x * r.dx + n.y * r.dy) + n.z * r.dz) + n.w * r.dw;
     if ((nd > -0.00001f) && (nd < 0.00001f)) return false;
     const float no = ((n.x * r.ox + n.y * r.oy) + n.z * r.oz) + n.w * r.ow;
