@@ -319,7 +319,9 @@ __global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas * 128 / kTra
                     r.ox = o.x; r.oy = o.y; r.oz = o.z; r.ow = o.w;
                     r.dx = d.x; r.dy = d.y; r.dz = d.z; r.dw = d.w;
                     r.ix = ib.x; r.iy = ib.y; r.iz = ib.z;
-                    lane_begin(L, sc, r, ib.w);
+                    // extend: the bound is INFINITY for every ray (a literal here, so that the wide lane's sqrtf(bound) folds away: the IEEE
+                    // square root of infinity is a subroutine call, which every extension ray took — 2.1 M calls per launch, ncu v14)
+                    lane_begin(L, sc, r, ANY ? ib.w : INFINITY);
                 }
                 qHead = min(qHead + nIdle, qCount);
                 __syncwarp();

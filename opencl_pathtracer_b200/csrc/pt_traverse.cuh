@@ -120,7 +120,13 @@ __device__ __forceinline__ bool tri_test(const DevTri *__restrict__ tris, uint32
     const float nd = ((n.x * r.dx + n.y * r.dy) + n.z * r.dz) + n.w * r.dw;
     if ((nd > -0.00001f) && (nd < 0.00001f)) return false;
     const float no = ((n.x * r.ox + n.y * r.oy) + n.z * r.oz) + n.w * r.ow;
-    const float tp = (p.w - no) / nd;
+    // A shadow ray starts ON the triangle it was shot from: p.w - no is then a small multiple of an ulp and very often exactly 0.
+    // 0 / nd = +-0 puts q on the origin, the squared distance is 0 and the reference's self-hit guard (:545, `< 0.00001f` below)
+    // rejects the candidate — the same answer without the IEEE division, whose zero-numerator case is a subroutine call that 2 of a
+    // warp's lanes took in 64 % of connect's triangle steps (ncu v14).
+    const float num = p.w - no;
+    if (num == 0.f) return false;
+    const float tp = num / nd;
     const float qx = r.ox + r.dx * tp, qy = r.oy + r.dy * tp, qz = r.oz + r.dz * tp, qw = r.ow + r.dw * tp;
     const float fx = qx - r.ox, fy = qy - r.oy, fz = qz - r.oz, fw = qw - r.ow;
     const float nsd = ((fx * fx + fy * fy) + fz * fz) + fw * fw;

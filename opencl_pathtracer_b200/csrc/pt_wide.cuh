@@ -104,7 +104,9 @@ __device__ __forceinline__ void lane_begin(WideLane &L, const SceneDev &sc, cons
     L.r.iy = finite_inverse(r.iy, r.dy);
     L.r.iz = finite_inverse(r.iz, r.dz);
     L.best = best;
-    L.tmax = bound_as_parameter(sqrtf(best), r);
+    // an unbounded ray (every extension ray, shadow rays of directional lights) skips the IEEE square root: sqrtf(INFINITY) is a
+    // subroutine call, not an instruction
+    L.tmax = best < 3.0e38f ? bound_as_parameter(sqrtf(best), r) : INFINITY;
     const uint32_t oct = (r.dx < 0 ? 4u : 0u) | (r.dy < 0 ? 2u : 0u) | (r.dz < 0 ? 1u : 0u);
     L.oct = (7u - oct) | ((r.dw == 0.f && r.ow == 1.f) ? 0u : WideLane::kStrict);
     L.gx = 0u;
