@@ -18,6 +18,16 @@ namespace ptc
 constexpr float kPi = 3.14159265f;  // PATH_PI
 constexpr float kPiInv = 0.31830988618f;
 
+// x / 255.f of convert_float4(uchar4) / 255 (header.cl:455). The IEEE division with a zero numerator is a subroutine call, not the
+// inline sequence — and a black texel is common (every sky face without a sky, `loadSky=false`, is the texel (0,0,0,0): ncu v14 showed
+// 4 such calls per missed ray, 3.8 % of k_shade's instructions). A zero lane divides 1 instead and answers +0, which is what 0 / 255 is.
+__device__ __forceinline__ float over255(float x)
+{
+    const bool z = x == 0.f;
+    const float q = (z ? 1.f : x) / 255.f;
+    return z ? 0.f : q;
+}
+
 // nearest texel, wrap by truncation, alpha inverted
 __device__ __forceinline__ float4 texture_lookup(const SceneDev &sc, uint32_t w, uint32_t h, uint32_t off, float u, float v)
 {
@@ -26,7 +36,7 @@ __device__ __forceinline__ float4 texture_lookup(const SceneDev &sc, uint32_t w,
     const uint32_t x = (uint32_t)(u * (w - 1));
     const uint32_t y = (uint32_t)(v * (h - 1));
     const uchar4 c = __ldg(&sc.texels[off + y * w + x]);
-    float4 bgra = f4((float)c.x, (float)c.y, (float)c.z, (float)c.w) / 255.f;
+    float4 bgra = f4(over255((float)c.x), over255((float)c.y), over255((float)c.z), over255((float)c.w));
     bgra.w = 1.f - bgra.w;
     return bgra;
 }
@@ -44,8 +54,8 @@ __device__ __forceinline__ float4 texture_lookup_bilinear(const SceneDev &sc, ui
     const uchar4 c00 = __ldg(&sc.texels[off + y0 * w + x0]), c10 = __ldg(&sc.texels[off + y0 * w + x1]);
     const uchar4 c01 = __ldg(&sc.texels[off + y1 * w + x0]), c11 = __ldg(&sc.texels[off + y1 * w + x1]);
     const float w00 = (1 - ax) * (1 - ay), w10 = ax * (1 - ay), w01 = (1 - ax) * ay, w11 = ax * ay;
-    float4 bgra = f4((w00 * c00.x + w10 * c10.x) + (w01 * c01.x + w11 * c11.x), (w00 * c00.y + w10 * c10.y) + (w01 * c01.y + w11 * c11.y),
-                     (w00 * c00.z + w10 * c10.z) + (w01 * c01.z + w11 * c11.z), (w00 * c00.w + w10 * c10.w) + (w01 * c01.w + w11 * c11.w)) / 255.f;
+    float4 bgra = f4(over255((w00 * c00.x + w10 * c10.x) + (w01 * c01.x + w11 * c11.x)), over255((w00 * c00.y + w10 * c10.y) + (w01 * c01.y + w11 * c11.y)),
+                     over255((w00 * c00.z + w10 * c10.z) + (w01 * c01.z + w11 * c11.z)), over255((w00 * c00.w + w10 * c10.w) + (w01 * c01.w + w11 * c11.w)));
     bgra.w = 1.f - bgra.w;
     return bgra;
 }
