@@ -1,5 +1,5 @@
 set -x
-TAG=${1:-v14}
+TAG=${1:-v15}
 mkdir -p gpurun_out
 timeout 1200 python -m pytest tests -m gpu -x -q 2>&1 | tail -4
 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2

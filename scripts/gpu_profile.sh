@@ -1,6 +1,6 @@
 # One gpurun call: launch list of the bench command + ncu --set full of k_trace (extend + connect) and k_shade, current build.
 set -x
-TAG=${1:-v14}
+TAG=${1:-v15}
 mkdir -p gpurun_out
 python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_$TAG.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/ncu1.log 2>&1
