@@ -98,6 +98,13 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 def reference_rows(step, rows_per_step, H):
     r0 = (H // 4 + step * rows_per_step) % (H - rows_per_step)
     return r0, r0 + rows_per_step
@@ -115,13 +122,15 @@ def run_reference(args, rank):
         return
     W, H = wl["size"]
     scene = pt.Scene(wl["scene"], W, H, load_sky=wl["sky"])
-    cores = ptref.max_threads()
+    # all the host threads this process may use: torchrun exports OMP_NUM_THREADS=1 to its workers, which would leave the reference
+    # kernel on one core (14 k instead of 230 k samples/s) — the thread count is passed explicitly (num_threads clause)
+    cores = host_threads()
     rows = args.ref_rows
     times = []
     for step in range(args.warmup + args.steps):
         r0, r1 = reference_rows(step, rows, H)
         t0 = time.perf_counter()
-        ptref.render(scene, W, H, DEPTH, 0, 0, 1, rows=(r0, r1))
+        ptref.render(scene, W, H, DEPTH, 0, 0, 1, nthreads=cores, rows=(r0, r1))
         dt = time.perf_counter() - t0
         if step >= args.warmup:
             times.append(dt)

@@ -19,7 +19,7 @@ def run_ours(args, rank, local_rank, world):
     import torch.distributed as dist
 
     import opencl_pathtracer_b200 as pt
-    from bench import DEPTH, WORKLOADS, ClockSampler, load_peaks
+    from bench import DEPTH, WORKLOADS, ClockSampler, host_threads, load_peaks
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — this benchmark has no CPU fallback (use --impl reference for the CPU reference)")
@@ -230,9 +230,9 @@ def run_ours(args, rank, local_rank, world):
             from oracle import ptref
             rows = (0, H)  # the whole frame once: ~10-15 s on 16 host cores
             t0 = time.perf_counter()
-            ptref.render(scene, W, H, DEPTH, 0, 0, 1, rows=rows)
+            ptref.render(scene, W, H, DEPTH, 0, 0, 1, nthreads=host_threads(), rows=rows)
             dt = time.perf_counter() - t0
-            cpu = {"value": (rows[1] - rows[0]) * W / dt, "unit": "samples/s", "cores": ptref.max_threads(), "kind": "reference",
+            cpu = {"value": (rows[1] - rows[0]) * W / dt, "unit": "samples/s", "cores": host_threads(), "kind": "reference",
                    "sample": "rows %d..%d of the %dx%d frame, 1 spp (%d paths), %.1f s; oracle/_ref = the reference kernel source compiled with g++ -O2 + OpenMP"
                              % (rows[0], rows[1], W, H, (rows[1] - rows[0]) * W, dt)}
         except Exception as e:  # the oracle is test infrastructure: its absence must not hide the GPU number
