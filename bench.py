@@ -98,6 +98,22 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+class QuietStdout:
+    """The bench contract is ONE JSON line on stdout. Libraries write there too (NCCL prints its version banner to stdout when the
+    box exports NCCL_DEBUG=VERSION): while the run is in progress file descriptor 1 points at stderr; emit() restores it for the line."""
+
+    def __init__(self):
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        os.dup2(2, 1)
+
+    def emit(self, text):
+        sys.stdout.flush()
+        os.dup2(self.saved, 1)
+        os.close(self.saved)
+        print(text, flush=True)
+
+
 def host_threads():
     try:
         return len(os.sched_getaffinity(0))

@@ -19,12 +19,13 @@ def run_ours(args, rank, local_rank, world):
     import torch.distributed as dist
 
     import opencl_pathtracer_b200 as pt
-    from bench import DEPTH, WORKLOADS, ClockSampler, host_threads, load_peaks
+    from bench import DEPTH, WORKLOADS, ClockSampler, QuietStdout, host_threads, load_peaks
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — this benchmark has no CPU fallback (use --impl reference for the CPU reference)")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    quiet = QuietStdout()
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     wl = WORKLOADS[args.workload]
@@ -254,7 +255,7 @@ def run_ours(args, rank, local_rank, world):
                         "ms_per_step": 1000.0 * e2e_s / K},
                 "gpu_launches": int(launches), "clocks": clk, "roofline": roof, "cpu_baseline": cpu, "mean_rgb": mean_rgb, "setup": setup}
         line.update(extra)
-        print(json.dumps(line), flush=True)
+        quiet.emit(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
 
@@ -270,7 +271,7 @@ def run_progressive(args, rank=0, local_rank=0, world=1):
     import torch
 
     import opencl_pathtracer_b200 as pt
-    from bench import DEPTH, WORKLOADS
+    from bench import DEPTH, WORKLOADS, QuietStdout
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — this benchmark has no CPU fallback")
@@ -278,6 +279,7 @@ def run_progressive(args, rank=0, local_rank=0, world=1):
     from opencl_pathtracer_b200.sharding import STRIPE_ROWS, compose_stripes, display_tensor
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    quiet = QuietStdout()
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     stream = torch.cuda.Stream(device=dev)
@@ -357,4 +359,4 @@ def run_progressive(args, rank=0, local_rank=0, world=1):
                        "parallelism": "whole frame on one GPU" if world == 1 else "interleaved %d-row stripes x%d, one uint8 NCCL reduce per frame" % (STRIPE_ROWS, world)},
             "e2e": {"value": p50, "unit": "ms", "h2d_bytes_per_step": 64, "d2h_bytes_per_step": W * H * 3},
             "gpu_launches": int(per_frame) * frames * world, "mean_rgb8": float(rgb.mean())}
-    print(json.dumps(line), flush=True)
+    quiet.emit(json.dumps(line))
