@@ -76,6 +76,14 @@ enum
                                         c = max throughput / (bounce - 5) and its throughput is divided by c (unbiased). The
                                         reference has this stage disabled and commented out (Kernel/PathTracer_FullKernel_header.cl:12,
                                         PathTracer_FullKernel.cl:1306-1314); the random streams then differ from the reference's. */
+    PTC_FLAG_WORK_COUNTERS = 1u << 7, /* FAST mode: keep the reference's per-ray work counters (Ray3D::numIntersectedBBx / numIntersectedTri,
+                                        Kernel/PathTracer_FullKernel_header.cl:95-96) and the two 5000-bin histograms they feed
+                                        (PathTracer_FullKernel.cl:1319-1331). PARITY always keeps them (they are the reference's, bit for
+                                        bit). In FAST they describe the 8-wide walk, depend on the warp a ray shares and are compared with
+                                        nothing; without this flag FAST drops them (two registers and two atomics per ray in the
+                                        traversal kernels): ptc_read_stats then returns rayDepths and two all-zero work histograms.
+                                        Global totals (ptc_counters.box_tests / triangle_tests) and the parity probes' per-ray counts
+                                        (ptc_trace_primary / ptc_trace_rays) are always kept. */
     PTC_FLAG_TEXTURE_BILINEAR = 1u << 6 /* FAST mode: surface textures are sampled with bilinear interpolation of the four texels
                                         around (u, v) instead of the reference's nearest texel
                                         (Texture_GetPixelColorValue, Kernel/PathTracer_FullKernel_header.cl:430-459); same wrap
@@ -237,6 +245,12 @@ PTC_API int ptc_trace_rays(ptc_ctx *ctx, uint32_t n, const float *origin, const 
 
 /* Parity probe: per-pixel radiance of exactly one iteration (what Kernel_Main adds to imageColor). */
 PTC_API int ptc_render_single(ptc_ctx *ctx, uint32_t iteration, float *radiance);
+
+/* Parity probe: the state of every path of one iteration after `bounces` bounces (0 = the camera rays): ray origin and direction
+ * of bounce `bounces` (4 floats per pixel each), the hit of bounce `bounces` - 1 as (bits of the triangle index in BVH order or
+ * -1, s, t, ray parameter) and the path's meta word (bits 7..0 = reflectionId, i.e. how many bounces the path really took: a
+ * path that ended earlier keeps its last state). Any pointer may be NULL. Does not touch the accumulators. */
+PTC_API int ptc_path_probe(ptc_ctx *ctx, uint32_t iteration, uint32_t bounces, float *origin, float *direction, float *hit, uint32_t *meta);
 
 /* Host utility: the 8-wide compressed BVH that ptc_upload_scene collapses the reference BVH2 into in FAST mode
  * (opencl_pathtracer_b200/csrc/pt_wide_build.cu), exposed for inspection and structural tests. nodes = n_nodes records of

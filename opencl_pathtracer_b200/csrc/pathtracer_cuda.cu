@@ -406,6 +406,7 @@ int ptc_create(const ptc_config *config, ptc_ctx **out_ctx)
     c->capacity = (size_t)b * c->nPix;
     c->lc.stackDepth = 32;
     c->lc.wide = false;
+    c->lc.count = !c->fast || (config->flags & PTC_FLAG_WORK_COUNTERS);
     c->lc.traverseGrid = c->smCount * traverse_ctas_per_sm(c->fast, false, c->lc.stackDepth);
     c->lc.streamGrid = c->smCount * 8;
     c->lc.refillMin = 4;  // idle lanes that trigger a refill from the warp's staged rays (profiles/r01_sweeps.txt)
@@ -554,12 +555,12 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
     std::vector<DevShade> hShade(nT);
     std::vector<float> hVerts(gpuBvh ? 9 * (size_t)nT : 0);  // device builder input: S1, S2, S3
     int badW = -1, badMat = -1;
-#pragma omp parallel for schedule(static)
+#pragma omp parallel for schedule(static) reduction(max : badW, badMat)
     for (long long i = 0; i < (long long)nT; i++)
     {
         const ptc_triangle &t = s->triangulation[i];
-        if (!(t.S1.w == t.S2.w && t.S1.w == t.S3.w)) badW = (int)i;
-        if (t.materialWithPositiveNormalIndex >= nM || t.materialWithNegativeNormalIndex >= nM) badMat = (int)i;
+        if (!(t.S1.w == t.S2.w && t.S1.w == t.S3.w)) badW = std::max(badW, (int)i);
+        if (t.materialWithPositiveNormalIndex >= nM || t.materialWithNegativeNormalIndex >= nM) badMat = std::max(badMat, (int)i);
         const ptc_float4 u = {t.S2.x - t.S1.x, t.S2.y - t.S1.y, t.S2.z - t.S1.z, t.S2.w - t.S1.w};
         const ptc_float4 v = {t.S3.x - t.S1.x, t.S3.y - t.S1.y, t.S3.z - t.S1.z, t.S3.w - t.S1.w};
         const float uv = hdot4(u, v), uu = hdot4(u, u), vv = hdot4(v, v);
@@ -822,6 +823,7 @@ FrameParams frameParams(const ptc_ctx *ctx, uint32_t first, uint32_t nIter)
     fp.stripeRank = ctx->stripeRank;
     fp.stripeWorld = ctx->stripeWorld;
     fp.ownedPix = ctx->stripeRows ? ctx->ownedPix : ctx->nPix;
+    fp.countWork = ctx->lc.count ? 1u : 0u;
     return fp;
 }
 
@@ -1145,7 +1147,9 @@ int ptc_trace_primary(ptc_ctx *ctx, uint32_t iteration, int32_t *hit, float *st,
     const uint32_t n = ctx->nPix;
     launch_reset(ctx->stream, ctx->counters.p, n);
     launch_generate(ctx->stream, ctx->lc, fp, ctx->cam, ctx->st);
-    launch_extend(ctx->stream, ctx->lc, ctx->fast, ctx->sc, ctx->st, nullptr, ctx->counters.p, 0);
+    LaunchCfg lcProbe = ctx->lc;
+    lcProbe.count = true;  // the probe reports per-ray counts in every mode
+    launch_extend(ctx->stream, lcProbe, ctx->fast, ctx->sc, ctx->st, nullptr, ctx->counters.p, 0);
     DevBuf<int32_t> dHit, dSeed;
     DevBuf<float2> dSt;
     DevBuf<float> dD2;
@@ -1198,7 +1202,9 @@ int ptc_trace_rays(ptc_ctx *ctx, uint32_t n, const float *origin, const float *d
     fp.width = n; fp.height = 1; fp.maxDepth = ctx->cfg.ray_max_depth; fp.nIterations = 1; fp.ownedPix = n;
     launch_reset(ctx->stream, ctx->counters.p, n);
     launch_probe_rays(ctx->stream, n, dOrg.p, dDirIn.p, ctx->st);
-    launch_extend(ctx->stream, ctx->lc, ctx->fast, ctx->sc, ctx->st, nullptr, ctx->counters.p, 0);
+    LaunchCfg lcProbe = ctx->lc;
+    lcProbe.count = true;
+    launch_extend(ctx->stream, lcProbe, ctx->fast, ctx->sc, ctx->st, nullptr, ctx->counters.p, 0);
     launch_probe_primary(ctx->stream, fp, ctx->st, dHit.p, dSt.p, dD2.p, dDir.p, nullptr, dCnt.p);
     ctx->launches += 4;
     int rc = PTC_OK;
@@ -1223,6 +1229,25 @@ int ptc_render_single(ptc_ctx *ctx, uint32_t iteration, float *radiance)
     int rc = runBatch(ctx, iteration, 1, false, -1);
     if (rc != PTC_OK) return rc;
     rc = readBack(ctx, radiance, ctx->rad.p, sizeof(float4) * ctx->nPix);
+    if (rc != PTC_OK) return rc;
+    return ptc_synchronize(ctx);
+}
+
+// Parity probe: the state of every path of one iteration after `bounces` bounces (0 = the camera rays), without touching the
+// accumulators. Lets a test walk a pixel's path bounce by bounce next to the reference's (tests/test_gpu_parity.py classifies
+// the pixels whose 1-spp radiance differs by the first bounce at which the two paths part).
+int ptc_path_probe(ptc_ctx *ctx, uint32_t iteration, uint32_t bounces, float *origin, float *direction, float *hit, uint32_t *meta)
+{
+    if (!ctx) return PTC_ERR_INVALID;
+    if (!ctx->sceneLoaded) return fail(ctx, PTC_ERR_STATE, "ptc_path_probe before ptc_upload_scene");
+    if (ctx->stripeRows) return fail(ctx, PTC_ERR_STATE, "ptc_path_probe: not available on a pixel shard (ptc_set_pixel_stripes)");
+    if (bounces > ctx->cfg.ray_max_depth) return fail(ctx, PTC_ERR_INVALID, "ptc_path_probe: %u bounces, ray_max_depth is %u", bounces, ctx->cfg.ray_max_depth);
+    CK(cudaSetDevice(ctx->device));
+    int rc = runBatch(ctx, iteration, 1, false, (int)bounces);
+    if (rc == PTC_OK) rc = readBack(ctx, origin, ctx->org.p, sizeof(float4) * ctx->nPix);
+    if (rc == PTC_OK) rc = readBack(ctx, direction, ctx->dir.p, sizeof(float4) * ctx->nPix);
+    if (rc == PTC_OK) rc = readBack(ctx, hit, ctx->hit.p, sizeof(float4) * ctx->nPix);
+    if (rc == PTC_OK) rc = readBack(ctx, meta, ctx->meta.p, sizeof(uint32_t) * ctx->nPix);
     if (rc != PTC_OK) return rc;
     return ptc_synchronize(ctx);
 }

@@ -141,6 +141,7 @@ struct FrameParams
     // stripeRows = 0: the whole frame. ownedPix = pixels of the shard = path slots per iteration.
     uint32_t stripeRows, stripeRank, stripeWorld;
     uint32_t ownedPix;
+    uint32_t countWork;  // per-path work counters are kept (st.nbbx / st.ntri feed the two 5000-bin histograms)
 };
 
 // pixel `i` of the shard (row-major over the owned rows) -> pixel of the frame

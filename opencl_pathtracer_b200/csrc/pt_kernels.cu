@@ -151,7 +151,12 @@ constexpr size_t kGroupBytes = sizeof(PathGroup) * (kTraverseThreads / 32);
 
 // FAST: 0 = PARITY, 1 = FAST, 2 = FAST for a scene with area lights (extension; connect only — scenes without one run the
 // kernels they always ran)
-template <bool ANY, int FAST, typename LaneT>
+// COUNT: keep the reference's per-ray work counters (Ray3D::numIntersectedBBx / numIntersectedTri, header.cl:95-96) and add them to
+// the path's (they feed the two 5000-bin histograms of K.cl:1319-1331). PARITY always does; FAST only with PTC_FLAG_WORK_COUNTERS
+// and in the parity probes: its counts follow the warp's votes (a parked triangle group shrinks the bound later), are compared
+// with nothing, and cost two registers and two atomics per ray. Without COUNT the lane's counters run on across rays and only
+// the global totals (ptc_counters.box_tests / triangle_tests) are kept.
+template <bool ANY, int FAST, typename LaneT, bool COUNT>
 __global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas * 128 / kTraverseThreads) k_trace(SceneDev sc, PathState st, const uint32_t *__restrict__ queue,
                                                            Counters *__restrict__ cn, int bounce, uint32_t popMin, int stackDepth)
 {
@@ -184,21 +189,35 @@ __global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas * 128 / kTra
         {
             if (!ANY)
             {
-                st.hit[p] = f4(__int_as_float(L.hit_index(sc)), L.hs, L.ht, L.htp);
-                atomicAdd(&st.nbbx[p], L.nb);
-                atomicAdd(&st.ntri[p], L.nt);
+                float hs, ht, htp;
+                uint32_t hmat;
+                L.hit_record(sc, hs, ht, htp, hmat);
+                st.hit[p] = f4(__int_as_float(L.hit_index(sc)), hs, ht, htp);
+                if (COUNT)
+                {
+                    atomicAdd(&st.nbbx[p], L.nb);
+                    atomicAdd(&st.ntri[p], L.nt);
+                }
                 uint32_t flags = 0;
                 if (L.hitTri < 0) flags = kOcclMiss;
-                else if (FAST && !(L.hmat == 0u || L.hmat == 3u)) flags = kOcclUnlit;  // GLASS / WATER / METAL / UNKNOWN never read the direct light (:805-843)
+                else if (FAST && !(hmat == 0u || hmat == 3u)) flags = kOcclUnlit;  // GLASS / WATER / METAL / UNKNOWN never read the direct light (:805-843)
                 st.occl[p] = flags;
             }
             else
             {
                 if (L.found) atomicOr(&st.occl[p], 1u << li);
-                if (L.nb) atomicAdd(&st.nbbx[p], L.nb);  // :946-947 the camera ray inherits its shadow rays' counters
-                if (L.nt) atomicAdd(&st.ntri[p], L.nt);
+                if (COUNT)
+                {
+                    if (L.nb) atomicAdd(&st.nbbx[p], L.nb);  // :946-947 the camera ray inherits its shadow rays' counters
+                    if (L.nt) atomicAdd(&st.ntri[p], L.nt);
+                }
             }
-            nbSum += L.nb; ntSum += L.nt; nRays++;
+            if (COUNT)
+            {
+                nbSum += L.nb; ntSum += L.nt;
+                L.nb = L.nt = 0;
+            }
+            nRays++;
             L.set_idle();
         }
         unsigned idle = __ballot_sync(full, L.idle());
@@ -352,7 +371,7 @@ __global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas * 128 / kTra
             if (8 * nT <= voteTri * nHave) break;
         }
     }
-    flush_work(cn, ANY ? &cn->shadowRays : &cn->extensionRays, nRays, nbSum, ntSum);
+    flush_work(cn, ANY ? &cn->shadowRays : &cn->extensionRays, nRays, COUNT ? nbSum : L.nb, COUNT ? ntSum : L.nt);
 }
 
 // ------------------------------------------------------------------------------------------------ shade
@@ -603,9 +622,11 @@ __device__ __forceinline__ void add_sample_atomic(const ImageDev &img, uint32_t 
 // :1319-1331; the three histograms are privatised in shared memory (most paths of a frame fall into a few bins: global
 // atomics on them serialise) and flushed once per CTA
 constexpr uint32_t kHistBins = 5000u;  // MAX_INTERSECTION_NUMBER
-__device__ __forceinline__ void count_path(uint32_t *sDepth, uint32_t *sBbx, uint32_t *sTri, uint32_t meta, uint32_t nb, uint32_t nt)
+__device__ __forceinline__ void count_path(const FrameParams &fp, const PathState &st, uint32_t k, uint32_t *sDepth, uint32_t *sBbx, uint32_t *sTri)
 {
-    atomicAdd(&sDepth[meta & 0xffu], 1u);
+    atomicAdd(&sDepth[st.meta[k] & 0xffu], 1u);
+    if (!fp.countWork) return;  // FAST without PTC_FLAG_WORK_COUNTERS: no per-path work counters exist
+    const uint32_t nb = st.nbbx[k], nt = st.ntri[k];
     if (nb < kHistBins) atomicAdd(&sBbx[nb], 1u);
     if (nt < kHistBins) atomicAdd(&sTri[nt], 1u);
 }
@@ -634,7 +655,7 @@ __global__ void __launch_bounds__(kStreamThreads) k_accumulate(FrameParams fp, P
                 if (st.meta[k] & kMetaSkipped) continue;  // dropped by k_supersample: the reference's work-item returned at :1221
                 const float4 x = st.rad[k];
                 const uint32_t tp = target_pixel(st.sample[k], fp.width, fp.height);
-                count_path(sDepth, sBbx, sTri, st.meta[k], st.nbbx[k], st.ntri[k]);
+                count_path(fp, st, k, sDepth, sBbx, sTri);
                 if (tp == pix) add_sample(img, pix, x, fp.firstIteration + li);
                 else add_sample_atomic(img, tp, x);
                 nPaths++;
@@ -647,7 +668,7 @@ __global__ void __launch_bounds__(kStreamThreads) k_accumulate(FrameParams fp, P
         for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < total; k += gridDim.x * blockDim.x)
         {
             if (st.meta[k] & kMetaSkipped) continue;
-            count_path(sDepth, sBbx, sTri, st.meta[k], st.nbbx[k], st.ntri[k]);
+            count_path(fp, st, k, sDepth, sBbx, sTri);
             add_sample_atomic(img, target_pixel(st.sample[k], fp.width, fp.height), st.rad[k]);
             nPaths++;
         }
@@ -655,7 +676,7 @@ __global__ void __launch_bounds__(kStreamThreads) k_accumulate(FrameParams fp, P
     __syncthreads();
     for (uint32_t i = threadIdx.x; i <= fp.maxDepth && i <= (uint32_t)kMaxBounces; i += blockDim.x)
         if (sDepth[i]) atomicAdd(&img.rayDepths[i], sDepth[i]);
-    for (uint32_t i = threadIdx.x; i < kHistBins; i += blockDim.x)
+    for (uint32_t i = threadIdx.x; i < kHistBins && fp.countWork; i += blockDim.x)
     {
         if (sBbx[i]) atomicAdd(&img.rayBbx[i], sBbx[i]);
         if (sTri[i]) atomicAdd(&img.rayTri[i], sTri[i]);
@@ -767,9 +788,17 @@ static inline size_t stack_bytes(bool wide, int stackDepth, bool any)
 template <bool ANY, int FAST, typename LaneT>
 static int occupancy_of(size_t bytes)
 {
-    int n = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_trace<ANY, FAST, LaneT>, kTraverseThreads, bytes);
-    return n;
+    // deep trees: more than the default 48 KB of dynamic shared memory needs the opt-in (the device builder on degenerate
+    // geometry can emit them; without it every launch fails with "invalid argument")
+    if (bytes > 48u * 1024u)
+    {
+        cudaFuncSetAttribute(k_trace<ANY, FAST, LaneT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+        cudaFuncSetAttribute(k_trace<ANY, FAST, LaneT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    }
+    int n = 0, m = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_trace<ANY, FAST, LaneT, false>, kTraverseThreads, bytes);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&m, k_trace<ANY, FAST, LaneT, true>, kTraverseThreads, bytes);
+    return n < m ? n : m;
 }
 
 int traverse_ctas_per_sm(bool fast, bool wide, int stackDepth)
@@ -777,8 +806,8 @@ int traverse_ctas_per_sm(bool fast, bool wide, int stackDepth)
     if (const char *e = std::getenv("PTC_CARVEOUT"))  // experiment: shared-memory carve-out in percent (what is left is L1)
     {
         const int v = std::atoi(e);
-        cudaFuncSetAttribute(k_trace<false, 1, WideLane>, cudaFuncAttributePreferredSharedMemoryCarveout, v);
-        cudaFuncSetAttribute(k_trace<true, 1, WideLane>, cudaFuncAttributePreferredSharedMemoryCarveout, v);
+        cudaFuncSetAttribute(k_trace<false, 1, WideLane, false>, cudaFuncAttributePreferredSharedMemoryCarveout, v);
+        cudaFuncSetAttribute(k_trace<true, 1, WideLane, false>, cudaFuncAttributePreferredSharedMemoryCarveout, v);
     }
     const size_t bytes = stack_bytes(wide, stackDepth, false), bytesAny = stack_bytes(wide, stackDepth, true);
     int n, m;
@@ -808,11 +837,13 @@ static void launch_trace(cudaStream_t s, const LaunchCfg &lc, bool fast, const S
 {
     const size_t smem = stack_bytes(lc.wide, lc.stackDepth, ANY);
     const bool area = ANY && sc.areaJump != 1u;  // the scene holds area lights: the connect variant that samples them
-#define PTC_TRACE(MODE, LANE) k_trace<ANY, MODE, LANE><<<lc.traverseGrid, kTraverseThreads, smem, s>>>(sc, st, queue, cn, bounce, lc.refillMin, lc.stackDepth)
+#define PTC_TRACE_(MODE, LANE, CNT) k_trace<ANY, MODE, LANE, CNT><<<lc.traverseGrid, kTraverseThreads, smem, s>>>(sc, st, queue, cn, bounce, lc.refillMin, lc.stackDepth)
+#define PTC_TRACE(MODE, LANE) do { if (lc.count) PTC_TRACE_(MODE, LANE, true); else PTC_TRACE_(MODE, LANE, false); } while (0)
     if (lc.wide) { if (area) PTC_TRACE(ANY ? 2 : 1, WideLane); else PTC_TRACE(1, WideLane); }
     else if (fast) { if (area) PTC_TRACE(ANY ? 2 : 1, TraceLane); else PTC_TRACE(1, TraceLane); }
-    else PTC_TRACE(0, TraceLane);
+    else PTC_TRACE_(0, TraceLane, true);
 #undef PTC_TRACE
+#undef PTC_TRACE_
 }
 
 void launch_extend(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const PathState &st, const uint32_t *queue,

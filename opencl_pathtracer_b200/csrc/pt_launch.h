@@ -12,6 +12,7 @@ struct LaunchCfg
     uint32_t refillMin;  // idle lanes of a warp that trigger a refill from the work cursor (1..32)
     int stackDepth;      // traversal stack entries per thread (BVH depth + 1, at most kStackDepth)
     bool wide;           // FAST mode: traverse the 8-wide compressed BVH (stackDepth then counts 8-byte entries)
+    bool count;          // per-ray work counters + the two 5000-bin histograms (PARITY always; FAST with PTC_FLAG_WORK_COUNTERS)
 };
 
 int traverse_ctas_per_sm(bool fast, bool wide, int stackDepth);

@@ -188,6 +188,7 @@ struct TraceLane
     __device__ __forceinline__ bool wants_node() const { return !(cur & kLeafBit); }
     __device__ __forceinline__ bool wants_tri() const { return (cur & kLeafBit) && cur < kDone; }
     __device__ __forceinline__ int hit_index(const SceneDev &) const { return hitTri; }
+    __device__ __forceinline__ void hit_record(const SceneDev &, float &s, float &t, float &tp, uint32_t &mat) const { s = hs; t = ht; tp = htp; mat = hmat; }
 };
 
 __device__ __forceinline__ bool lane_at_inner(const TraceLane &L) { return !(L.cur & kLeafBit); }
@@ -211,7 +212,6 @@ __device__ __forceinline__ void lane_begin(TraceLane &L, const SceneDev &sc, con
     L.hitTri = -1;
     L.hs = L.ht = L.htp = 0.f;
     L.hmat = 0;
-    L.nb = L.nt = 0;
     L.te = 0;
     L.found = false;
     L.regular = ray_is_regular(r);

@@ -13,6 +13,8 @@
 // so the 24-bit triangle hit mask is a bit spread of the 8 slot results and needs no per-child shifts.
 #pragma once
 
+#include <cuda_fp16.h>
+
 #include "pt_traverse.cuh"
 
 namespace ptc
@@ -52,14 +54,16 @@ struct WideLane
     uint32_t tx, ty;   // triangle group: first record (24 * node) | 24 bits of triangles still to test
     uint32_t oct;      // bits 2..0: 7 - ray octant; kPostponed: a triangle group waits in the lane's slot 0 of the stack
     int sp;            // stack entries, -1 = no ray
-    int hitTri;
-    float hs, ht, htp;
-    uint32_t hmat;
+    int hitTri;        // wide record index of the accepted hit, -1 = none; (s, t, parameter, material) are recomputed from it once
+                       // per ray (hit_record) instead of riding in four registers through every step
     uint32_t nb, nt;
     bool found;
 
     typedef uint2 StackT;
-    static constexpr int kMinCtas = 8;  // 64 registers: 8 CTAs of 4 warps per SM
+#ifndef PTC_WIDE_MIN_CTAS
+#define PTC_WIDE_MIN_CTAS 8
+#endif
+    static constexpr int kMinCtas = PTC_WIDE_MIN_CTAS;  // 64 registers: 8 CTAs of 4 warps per SM
     __device__ __forceinline__ void reset() { sp = -1; gy = ty = 0; nb = nt = 0; found = false; hitTri = -1; }
     __device__ __forceinline__ bool idle() const { return sp < 0; }
     __device__ __forceinline__ void set_idle() { sp = -1; }
@@ -77,6 +81,16 @@ struct WideLane
     __device__ __forceinline__ bool wants_tri() const { return sp >= 0 && (ty != 0u || (oct & kPostponed)); }
     // BVH-order index of the hit (what the shade stage and the reference's ids use), -1 = miss
     __device__ __forceinline__ int hit_index(const SceneDev &sc) const { return hitTri < 0 ? -1 : (int)__ldg(&sc.tri8Index[hitTri]); }
+    // (s, t, ray parameter, MaterialType of the side hit) of the final hit: the accepted test once more — the same operations on
+    // the same operands, hence the same bits the walk saw when it accepted the triangle
+    __device__ __forceinline__ void hit_record(const SceneDev &sc, float &hs, float &ht, float &htp, uint32_t &hmat) const
+    {
+        hs = ht = htp = 0.f;
+        hmat = 0u;
+        if (hitTri < 0) return;
+        float inf = INFINITY;
+        tri_test(sc.tris8, (uint32_t)hitTri, r, inf, hs, ht, htp, hmat);
+    }
 };
 
 __device__ __forceinline__ float finite_inverse(float inv, float d)
@@ -114,9 +128,6 @@ __device__ __forceinline__ void lane_begin(WideLane &L, const SceneDev &sc, cons
     L.tx = L.ty = 0u;
     L.sp = 0;
     L.hitTri = -1;
-    L.hs = L.ht = L.htp = 0.f;
-    L.hmat = 0;
-    L.nb = L.nt = 0;
     L.found = false;
 }
 
@@ -135,6 +146,18 @@ __device__ __forceinline__ void wide_normalise(WideLane &L, const uint2 *stk, co
 }
 
 __device__ __forceinline__ float q8(uint32_t w, int j) { return (float)((w >> (8 * j)) & 0xffu); }
+
+#ifdef PTC_Q8_HALF
+// Quantised planes without the conversion pipe: a byte q placed under the half-precision exponent 0x64 is the half 1024 + q
+// (exact), two bytes per PRMT; half -> float is exact as well and runs beside the FMAs. The 1024 is folded into the constant
+// term of t(q) = q * a + b. (48 I2F.U8 per node visit -> 24 PRMT + 48 HADD2.F32.)
+__device__ __forceinline__ void q8x4(uint32_t w, float &f0, float &f1, float &f2, float &f3)
+{
+    const uint32_t h01 = __byte_perm(w, 0x64646464u, 0x4140), h23 = __byte_perm(w, 0x64646464u, 0x4342);
+    const float2 a = __half22float2(*reinterpret_cast<const __half2 *>(&h01)), b = __half22float2(*reinterpret_cast<const __half2 *>(&h23));
+    f0 = a.x; f1 = a.y; f2 = b.x; f3 = b.y;
+}
+#endif
 
 // One node visit: take the nearest unvisited child of the current group, postpone its siblings, test its 8 children.
 template <bool FAST>
@@ -168,9 +191,17 @@ __device__ __forceinline__ void lane_node_step(WideLane &L, const SceneDev &sc, 
     const float by = (__uint_as_float(n0.y) - L.r.oy) * L.r.iy;
     const float bz = (__uint_as_float(n0.z) - L.r.oz) * L.r.iz;
     const float kPad = 4.76837158e-7f;
+#ifdef PTC_Q8_HALF
+    // planes arrive as 1024 + q: the constant term takes the -1024 * a and is padded after that
+    const float cx = __fmaf_rn(-1024.f, adx, bx), cy = __fmaf_rn(-1024.f, ady, by), cz = __fmaf_rn(-1024.f, adz, bz);
+    const float bxl = __fmaf_rn(-fabsf(cx), kPad, cx), bxh = __fmaf_rn(fabsf(cx), kPad, cx);
+    const float byl = __fmaf_rn(-fabsf(cy), kPad, cy), byh = __fmaf_rn(fabsf(cy), kPad, cy);
+    const float bzl = __fmaf_rn(-fabsf(cz), kPad, cz), bzh = __fmaf_rn(fabsf(cz), kPad, cz);
+#else
     const float bxl = __fmaf_rn(-fabsf(bx), kPad, bx), bxh = __fmaf_rn(fabsf(bx), kPad, bx);
     const float byl = __fmaf_rn(-fabsf(by), kPad, by), byh = __fmaf_rn(fabsf(by), kPad, by);
     const float bzl = __fmaf_rn(-fabsf(bz), kPad, bz), bzh = __fmaf_rn(fabsf(bz), kPad, bz);
+#endif
     // entry planes are the low ones along axes the ray travels up, the high ones otherwise
     const bool nx = L.r.ix < 0, ny = L.r.iy < 0, nz = L.r.iz < 0;
     // words: n2 = qlo.x[0] qlo.x[1] qlo.y[0] qlo.y[1]; n3 = qlo.z[0] qlo.z[1] qhi.x[0] qhi.x[1]; n4 = qhi.y[0] qhi.y[1] qhi.z[0] qhi.z[1]
@@ -183,12 +214,24 @@ __device__ __forceinline__ void lane_node_step(WideLane &L, const SceneDev &sc, 
         const uint32_t ex = nx ? hix : lox, fx = nx ? lox : hix;
         const uint32_t ey = ny ? hiy : loy, fy = ny ? loy : hiy;
         const uint32_t ez = nz ? hiz : loz, fz = nz ? loz : hiz;
+#ifdef PTC_Q8_HALF
+        float qex[4], qfx[4], qey[4], qfy[4], qez[4], qfz[4];
+        q8x4(ex, qex[0], qex[1], qex[2], qex[3]); q8x4(fx, qfx[0], qfx[1], qfx[2], qfx[3]);
+        q8x4(ey, qey[0], qey[1], qey[2], qey[3]); q8x4(fy, qfy[0], qfy[1], qfy[2], qfy[3]);
+        q8x4(ez, qez[0], qez[1], qez[2], qez[3]); q8x4(fz, qfz[0], qfz[1], qfz[2], qfz[3]);
+#endif
 #pragma unroll
         for (int j = 0; j < 4; j++)
         {
+#ifdef PTC_Q8_HALF
+            const float tex = __fmaf_rn(qex[j], adx, bxl), tfx = __fmaf_rn(qfx[j], adx, bxh);
+            const float tey = __fmaf_rn(qey[j], ady, byl), tfy = __fmaf_rn(qfy[j], ady, byh);
+            const float tez = __fmaf_rn(qez[j], adz, bzl), tfz = __fmaf_rn(qfz[j], adz, bzh);
+#else
             const float tex = __fmaf_rn(q8(ex, j), adx, bxl), tfx = __fmaf_rn(q8(fx, j), adx, bxh);
             const float tey = __fmaf_rn(q8(ey, j), ady, byl), tfy = __fmaf_rn(q8(fy, j), ady, byh);
             const float tez = __fmaf_rn(q8(ez, j), adz, bzl), tfz = __fmaf_rn(q8(fz, j), adz, bzh);
+#endif
             const float tEnter = fmaxf(fmaxf(tex, tey), fmaxf(tez, 0.f));
             const float tExit = fminf(fminf(tfx, tfy), fminf(tfz, L.tmax));
             if (tEnter <= tExit) slotHit |= 1u << (4 * h + j);
@@ -231,9 +274,11 @@ __device__ __forceinline__ void lane_tri_step(WideLane &L, const SceneDev &sc, c
     L.ty &= L.ty - 1u;
     const uint32_t i = L.tx + (uint32_t)bit;
     L.nt++;
-    const bool acc = tri_test(sc.tris8, i, L.r, L.best, L.hs, L.ht, L.htp, L.hmat, ANY ? nullptr : sc.tri8Index, L.hitTri);
+    float hs, ht, htp = 0.f;
+    uint32_t hmat;
+    const bool acc = tri_test(sc.tris8, i, L.r, L.best, hs, ht, htp, hmat, ANY ? nullptr : sc.tri8Index, L.hitTri);
     L.hitTri = acc ? (int)i : L.hitTri;
-    L.tmax = acc ? bound_as_parameter(L.htp, L.r) : L.tmax;
+    L.tmax = acc ? bound_as_parameter(htp, L.r) : L.tmax;
     if (ANY)
     {
         L.found = L.found || acc;

@@ -385,10 +385,11 @@ void buildGallery(SceneBuilder &s, uint seed, uint w, uint h)
 }
 
 // ------------------------------------------------------------------------------------------------------
-// "atrium": Sponza-scale hall. k divides the tessellation (k = 1 -> ~262 k triangles).
-void buildAtrium(SceneBuilder &s, uint seed, int k, uint w, uint h)
+// "atrium": Sponza-scale hall. k divides the tessellation, m multiplies it (k = m = 1 -> ~262 k triangles; "atrium:4" -> ~16 k;
+// "atrium@2" -> ~1.05 M, the north star's target size: same surfaces, materials and lights, every grid twice as fine).
+void buildAtrium(SceneBuilder &s, uint seed, int k, int m, uint w, uint h)
 {
-    auto R = [&](int n) { int v = n / k; return v < 2 ? 2 : v; };
+    auto R = [&](int n) { int v = n * m / k; return v < 2 ? 2 : v; };
     const double LX = 3000, LY = 1800, LZ = 1200;
     uint wall = s.addMaterial(MAT_STANDART, 0.75f, 0.70f, 0.62f);
     uint floorM = s.addMaterial(MAT_VARNHISHED, 0.60f, 0.55f, 0.50f);
@@ -540,6 +541,14 @@ void PathTracerProceduralImporter::Import(uint image_width, uint image_height, b
 
     std::string name = sceneName;
     int param = 0;
+    int refine = 1;  // "name@m": finer tessellation (atrium only)
+    size_t at = name.find('@');
+    if (at != std::string::npos)
+    {
+        refine = std::atoi(name.c_str() + at + 1);
+        if (refine < 1 || refine > 8) throw std::runtime_error("PathTracerProceduralImporter: refinement must be 1..8 in '" + sceneName + "'");
+        name = name.substr(0, at);
+    }
     size_t colon = name.find(':');
     if (colon != std::string::npos)
     {
@@ -553,7 +562,7 @@ void PathTracerProceduralImporter::Import(uint image_width, uint image_height, b
     else if (name == "cornell_specular") buildCornell(s, true, image_width, image_height);
     else if (name == "cornell_area") buildCornell(s, false, image_width, image_height, true);
     else if (name == "gallery") { buildGallery(s, seed, image_width, image_height); skySize = 32; }
-    else if (name == "atrium") buildAtrium(s, seed, param > 0 ? param : 1, image_width, image_height);
+    else if (name == "atrium") buildAtrium(s, seed, param > 0 ? param : 1, refine, image_width, image_height);
     else if (name == "terrain") { int g = param > 0 ? param : 64; buildTerrain(s, seed, g, image_width, image_height); skySize = g >= 64 ? 512 : 64; }
     else throw std::runtime_error("PathTracerProceduralImporter: unknown scene '" + sceneName + "'");
     s.buildSky(loadSky, skySize);

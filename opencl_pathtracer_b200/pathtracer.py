@@ -142,6 +142,15 @@ class PathTracerCUDA:
                                           out["dist2"].ctypes.data, out["dir"].ctypes.data, out["counts"].ctypes.data))
         return out
 
+    def path_probe(self, iteration, bounces):
+        """State of every path of `iteration` after `bounces` bounces: dict(org [n,4], dir [n,4], hit [n] int32, st [n,2],
+        tpar [n], refl [n] = bounces the path really took)."""
+        n = self.n_pixels
+        o, d, h = np.empty((n, 4), np.float32), np.empty((n, 4), np.float32), np.empty((n, 4), np.float32)
+        m = np.empty(n, np.uint32)
+        self._ck(self._lib.ptc_path_probe(self._h, iteration, bounces, o.ctypes.data, d.ctypes.data, h.ctypes.data, m.ctypes.data))
+        return {"org": o, "dir": d, "hit": h[:, 0].copy().view(np.int32), "st": h[:, 1:3].copy(), "tpar": h[:, 3].copy(), "refl": (m & 0xff).astype(np.int32)}
+
     def wide_bvh(self):
         """The wide BVH this context traverses, read back from the device: (nodes as scene.NODE8 records, tri_order[24 n],
         depth, device build time in ms — 0 for the host-built tree)."""

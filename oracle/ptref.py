@@ -44,6 +44,7 @@ def lib():
         L.ptref_rng.argtypes = [u32, u32, u32, u32, u32, C.c_int, vp, vp, vp]
         L.ptref_cosine_sample.argtypes = [C.c_int32, vp, vp, vp]
         L.ptref_x2inv.argtypes = [vp, C.c_int]
+        L.ptref_path_debug.argtypes = [C.POINTER(RefScene), u32, u32, u32, u32, u32, u32, vp, vp, vp, vp]
         _lib = L
     return _lib
 
@@ -142,6 +143,20 @@ def cosine_sample(seed, normal4):
     after = C.c_int32()
     lib().ptref_cosine_sample(seed, nrm.ctypes.data, out.ctypes.data, C.byref(after))
     return out, after.value
+
+
+def path_debug(scene, W, H, max_depth, x, y, iteration):
+    """Kernel_Main's path loop for ONE work-item, bounce by bounce, made of the reference's own functions (ref_glue.cpp
+    ptref_path_debug). Returns dict(n = bounces logged, org [n,4], dir [n,4], hit [n] (triangle index or -1), mat [n]
+    (MaterialType of the hit or -1), work [n,4], st [n,2])."""
+    rays = np.zeros((max_depth + 1, 8), np.float32)
+    ids = np.zeros((max_depth + 1, 2), np.int32)
+    work = np.zeros((max_depth + 1, 4), np.uint32)
+    st = np.zeros((max_depth + 1, 2), np.float32)
+    rs = ref_scene(scene)
+    n = lib().ptref_path_debug(C.byref(rs), W, H, max_depth, x, y, iteration, rays.ctypes.data, ids.ctypes.data, work.ctypes.data, st.ctypes.data)
+    return {"n": n, "org": rays[:n, :4].copy(), "dir": rays[:n, 4:].copy(), "hit": ids[:n, 0].copy(), "mat": ids[:n, 1].copy(),
+            "work": work[:n].copy(), "st": st[:n].copy()}
 
 
 def max_threads():

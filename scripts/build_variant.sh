@@ -1,5 +1,5 @@
 #!/bin/bash
-# A/B builds: scripts/build_variant.sh NAME "-DSOME_MACRO ..." -> opencl_pathtracer_b200/_lib_NAME/ (select with PTC_LIB_DIR)
+# A/B builds: [FMAD=true] scripts/build_variant.sh NAME "-DSOME_MACRO ..." -> opencl_pathtracer_b200/_lib_NAME/ (select with PTC_LIB_DIR)
 set -e
 NAME=$1; shift
 ROOT=$(cd "$(dirname "$0")/.." && pwd)
@@ -7,8 +7,9 @@ OUT=$ROOT/opencl_pathtracer_b200/_lib_$NAME
 mkdir -p $OUT
 cp $ROOT/opencl_pathtracer_b200/_lib/libpathtracer_host.so $OUT/
 OBJS=""
+FMAD=${FMAD:-false}
 for f in pt_kernels pt_wide_build pt_lbvh pathtracer_cuda; do
-  nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -fmad=false -std=c++17 "$@" -Xcompiler -fPIC,-fopenmp,-ffp-contract=off,-fvisibility=hidden \
+  nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -fmad=$FMAD -std=c++17 "$@" -Xcompiler -fPIC,-fopenmp,-ffp-contract=off,-fvisibility=hidden \
        -I $ROOT/include -I $ROOT/opencl_pathtracer_b200/csrc -c $ROOT/opencl_pathtracer_b200/csrc/$f.cu -o $OUT/$f.o &
   OBJS="$OBJS $OUT/$f.o"
 done

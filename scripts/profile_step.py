@@ -36,6 +36,7 @@ with pt.PathTracerCUDA(W, H, mode=mode, flags=pt.FLAG_NO_VARIANCE | pt.FLAG_STAG
     dt = time.perf_counter() - t0
     c = r.counters()
     rays = c["extension_rays"] + c["shadow_rays"]
-    print("env REFILL=%s CTAS=%s | %.1f Msamples/s %.0f Mrays/s | ms: ext %.1f con %.1f shade %.1f acc %.1f | box/path %.0f tri/path %.0f" % (
-        os.environ.get("PTC_REFILL_MIN"), os.environ.get("PTC_CTAS_PER_SM"), c["paths"] / dt / 1e6, rays / dt / 1e6,
+    env = " ".join("%s=%s" % (k[4:], v) for k, v in sorted(os.environ.items()) if k.startswith("PTC_"))
+    print("env %s | %.1f Msamples/s %.0f Mrays/s | ms: ext %.1f con %.1f shade %.1f acc %.1f | box/path %.0f tri/path %.0f" % (
+        env, c["paths"] / dt / 1e6, rays / dt / 1e6,
         c["ms_extend"], c["ms_connect"], c["ms_shade"], c["ms_accumulate"], c["box_tests"] / c["paths"], c["triangle_tests"] / c["paths"]))

@@ -1,0 +1,194 @@
+"""GPU parity at the sizes BASELINE.json words its configurations with (the small-frame versions are in test_gpu_parity.py):
+
+  C1  Cornell 512x512, 16 spp                     accumulated image vs the reference kernel, RMSE / mean <= 1e-3
+  C3  atrium 262 k triangles, 1920x1080, depth 10 1-spp radiance of iterations 0 and 7 vs the reference kernel, every offending pixel
+                                                  CLASSIFIED by walking its path bounce by bounce next to the reference's
+  C4  terrain + instances 10.1 M triangles,       primary hits of a 1080p frame bit-exact (oracle + committed hash), 1-spp radiance of a
+      16 textures, sky cube map                   512x288 frame vs the reference kernel (texture lookup K.cl:591-602, sky :438-512 at scale)
+
+The oracle is oracle/_ref (the reference's own kernel source compiled for the CPU); it travels to the GPU box prebuilt.
+"""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+import opencl_pathtracer_b200 as pt
+
+pytestmark = pytest.mark.gpu
+
+REL_TOL, ABS_TOL = 1e-3, 1e-6  # north_star: single-sample radiance within 1e-3 relative error
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "c4_primary_hash.json")
+
+
+def _bad_pixels(a, b):
+    a = a.reshape(-1, 4).astype(np.float64)
+    b = b.reshape(-1, 4).astype(np.float64)
+    return (np.abs(a - b) > REL_TOL * np.maximum(np.abs(a), np.abs(b)) + ABS_TOL).any(axis=1)
+
+
+def _ulp(x):
+    return np.spacing(np.abs(x).astype(np.float32)).astype(np.float64)
+
+
+def classify_divergence(ptref, sc, renderer, w, h, depth, iteration, pixels):
+    """For each pixel index in `pixels`: walk the PARITY path and the reference's path of (pixel, iteration) side by side and name
+    the first bounce at which they part. Returns {class: [pixel, ...]}. Classes:
+      cos_sin    bounce b >= 1: rays 0..b-1 and their hits (index, (s, t) bits) are bit-identical, the hit of bounce b-1 is a
+                 material that draws a cosine-weighted direction (MAT_STANDART / MAT_VARNHISHED, K.cl:303-336), and ray b differs in
+                 the last bits only (direction within 1e-6, origin within 4 ulp): libm cosf/sinf of the oracle vs the kernel's
+                 correctly rounded ones (K.cl:412-413 calls OpenCL built-ins of unspecified accuracy). The paths then hit
+                 different triangles somewhere downstream (a triangle edge between the two directions).
+      same_path  no ray differs at any bounce both paths have: unexplained
+      hit        same ray bits, different hit: a traversal bug
+      other      anything else (camera ray differs, a ray differs by more than last bits, non-diffuse material before it)
+    """
+    pixels = np.asarray(pixels, dtype=np.int64)
+    probes = []
+    for b in range(depth + 1):
+        p = renderer.path_probe(iteration, b)
+        probes.append({k: v[pixels].copy() for k, v in p.items()})
+    out = {"cos_sin": [], "same_path": [], "hit": [], "other": []}
+    for i, pix in enumerate(pixels):
+        ref = ptref.path_debug(sc, w, h, depth, int(pix % w), int(pix // w), iteration)
+        cls = "same_path"
+        for b in range(ref["n"]):
+            go, gd = probes[b]["org"][i], probes[b]["dir"][i]
+            same_ray = np.array_equal(go.view(np.uint32), ref["org"][b].view(np.uint32)) and np.array_equal(gd.view(np.uint32), ref["dir"][b].view(np.uint32))
+            if not same_ray:
+                if b == 0:
+                    cls = "other"
+                    break
+                small = (np.abs(gd.astype(np.float64) - ref["dir"][b]) <= 1e-6).all() and \
+                    (np.abs(go.astype(np.float64) - ref["org"][b]) <= 4 * _ulp(ref["org"][b]) + 1e-9).all()
+                cls = "cos_sin" if (small and ref["mat"][b - 1] in (0, 3)) else "other"
+                break
+            if b + 1 <= depth:  # the hit of ray b as the GPU found it (valid: the GPU traced ray b, all its rays so far being the reference's)
+                gh = probes[b + 1]["hit"][i] if b + 1 < len(probes) else None
+                if gh is not None:
+                    same_hit = int(gh) == int(ref["hit"][b])
+                    if same_hit and ref["hit"][b] >= 0:
+                        same_hit = np.array_equal(probes[b + 1]["st"][i].view(np.uint32), ref["st"][b].view(np.uint32))
+                    if not same_hit:
+                        cls = "hit"
+                        break
+        out[cls].append(int(pix))
+    return out
+
+
+def test_c3_full_size_radiance_with_classified_mismatches(ptref, scene_factory):
+    """BASELINE.json configs[2] at its stated size. PARITY 1-spp radiance of iterations 0 and 7 against the reference kernel for all
+    2,073,600 pixels; the pixels outside the 1e-3 band are not merely counted: up to 400 of them per iteration are walked bounce by
+    bounce in both implementations and every one must be a `cos_sin` divergence (see classify_divergence). Fractions are printed."""
+    w, h, depth = 1920, 1080, 10
+    sc = scene_factory("atrium", w, h, False)
+    rng = np.random.default_rng(7)
+    with pt.PathTracerCUDA(w, h, ray_max_depth=depth, mode=pt.MODE_PARITY, flags=pt.FLAG_NO_VARIANCE, iterations_per_batch=1) as r:
+        r.upload(sc)
+        for it in (0, 7):
+            ref = ptref.render(sc, w, h, depth, 0, it, it + 1)["imageColor"]
+            got = r.render_single(it)
+            assert np.isfinite(got).all()
+            bad = _bad_pixels(got, ref)
+            exact = (got.view(np.uint32) == ref.view(np.uint32)).all(axis=-1).mean()
+            idx = np.flatnonzero(bad)
+            pick = idx if len(idx) <= 400 else rng.choice(idx, 400, replace=False)
+            classes = classify_divergence(ptref, sc, r, w, h, depth, it, pick)
+            n = {k: len(v) for k, v in classes.items()}
+            print("C3 1080p it=%d: %d of %d pixels outside 1e-3 (%.4f %%), bit-identical pixels %.2f %%; of %d offenders walked: %s"
+                  % (it, bad.sum(), bad.size, 100 * bad.mean(), 100 * exact, len(pick), n))
+            assert bad.mean() <= 2e-3, "fraction of pixels whose path diverged too large: %g" % bad.mean()
+            assert n["hit"] == 0 and n["other"] == 0 and n["same_path"] == 0, "unexplained radiance mismatches: %s" % {k: v[:5] for k, v in classes.items() if k != "cos_sin"}
+            # a control group of agreeing pixels: their paths must be the reference's ray for ray or differ in last bits only
+            ok = np.flatnonzero(~bad)
+            ctrl = classify_divergence(ptref, sc, r, w, h, depth, it, rng.choice(ok, 200, replace=False))
+            assert len(ctrl["hit"]) == 0 and len(ctrl["other"]) == 0, ctrl
+
+
+def test_c1_cornell_512_16spp(ptref, scene_factory):
+    """BASELINE.json configs[0] as worded: Cornell box 512x512, 16 spp (4.19 M paths), depth 10 — the reference kernel on the host
+    cores in full, PARITY and FAST against it. Bound: RMSE / mean <= 1e-3; counts and path totals exact."""
+    w, h, depth, spp = 512, 512, 10, 16
+    sc = scene_factory("cornell", w, h, False)
+    ref = ptref.render(sc, w, h, depth, 0, 0, spp)
+    mean = ref["imageColor"][..., :3].mean()
+    for mode, label in ((pt.MODE_PARITY, "PARITY"), (pt.MODE_FAST, "FAST")):
+        with pt.PathTracerCUDA(w, h, ray_max_depth=depth, mode=mode) as r:
+            r.upload(sc)
+            r.render(0, spp)
+            color, nb = r.read_image()
+            d, b, t = r.read_stats()
+            c = r.counters()
+        assert np.array_equal(nb, ref["imageRayNb"]) and c["paths"] == w * h * spp
+        rmse = np.sqrt(((color[..., :3].astype(np.float64) - ref["imageColor"][..., :3]) ** 2).mean())
+        moved = np.abs(d.astype(np.int64) - ref["rayDepths"].astype(np.int64)).sum() / (w * h * spp)
+        print("C1 512x512 16 spp %s: RMSE / mean = %.3g, paths that changed depth bin %.3g" % (label, rmse / mean, moved))
+        assert rmse / mean <= 1e-3
+        assert d.sum() == ref["rayDepths"].sum() == w * h * spp and moved <= 2e-3
+        if mode == pt.MODE_PARITY:  # the work histograms are the reference's up to the paths that diverged on a last-bit direction
+            assert b.sum() == ref["rayIntersectedBBx"].sum() and t.sum() == ref["rayIntersectedTri"].sum()
+            assert np.abs(b.astype(np.int64) - ref["rayIntersectedBBx"].astype(np.int64)).sum() <= 4e-3 * w * h * spp
+
+
+def _hash(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def test_c4_scene_primary_hits_and_radiance(ptref):
+    """BASELINE.json configs[3]'s scene (terrain + 4,096 flattened rock instances, 10.1 M triangles, 16 textures of 1024^2, sun + sky
+    cube map): primary hits of a 1920x1080 frame bit-exact against the reference kernel AND against the committed hash
+    (tests/golden/c4_primary_hash.json, made by tests/golden/make_c4_golden.py from the oracle), then PARITY 1-spp radiance of a
+    512x288 frame against the reference kernel: textures (K.cl:591-602, header.cl:430-459) and the sky (K.cl:438-512) at scale."""
+    w, h, depth = 1920, 1080, 10
+    sc = pt.Scene("terrain", w, h, load_sky=True)
+    info = sc.info
+    assert info.triangulationSize > 10_000_000 and info.texturesSize == 16 and info.bvhMaxDepth < 30
+    with open(GOLDEN) as f:
+        golden = json.load(f)
+    with pt.PathTracerCUDA(w, h, ray_max_depth=depth, mode=pt.MODE_PARITY, flags=pt.FLAG_NO_VARIANCE, iterations_per_batch=1) as r:
+        r.upload(sc)
+        got = r.trace_primary(0)
+    assert (got["hit"] >= 0).mean() > 0.5 and (got["hit"] < 0).any(), "the frame should show terrain and sky"
+    assert _hash(got["hit"]) == golden["hit_sha256"], "primary hit indices differ from the committed oracle hash"
+    assert _hash(got["st"].view(np.uint32)) == golden["st_sha256"]
+    assert _hash(got["counts"]) == golden["counts_sha256"]
+    ref = ptref.primary(sc, w, h, sampler=0, iteration=0)
+    for k in ("seed_after", "hit", "counts"):
+        assert np.array_equal(got[k], ref[k]), k
+    for k in ("dir", "st", "dist2"):
+        assert np.array_equal(got[k].view(np.uint32), ref[k].view(np.uint32)), k
+    # radiance at 512x288 (same scene and camera, coarser pixel grid): PARITY vs the reference kernel, FAST vs PARITY
+    cw, ch = 512, 288
+    sc.close()
+    sc = pt.Scene("terrain", cw, ch, load_sky=True)
+    textured = sky = 0
+    with pt.PathTracerCUDA(cw, ch, ray_max_depth=depth, mode=pt.MODE_PARITY, flags=pt.FLAG_NO_VARIANCE) as r:
+        r.upload(sc)
+        for it in (0, 7):
+            ref = ptref.render(sc, cw, ch, depth, 0, it, it + 1)["imageColor"]
+            rad = r.render_single(it)
+            bad = _bad_pixels(rad, ref)
+            classes = classify_divergence(ptref, sc, r, cw, ch, depth, it, np.flatnonzero(bad)[:200])
+            n = {k: len(v) for k, v in classes.items()}
+            print("C4 scene 512x288 it=%d: %d of %d pixels outside 1e-3 (%.4f %%); offenders walked: %s" % (it, bad.sum(), bad.size, 100 * bad.mean(), n))
+            assert bad.mean() <= 2e-3
+            assert n["hit"] == 0 and n["other"] == 0 and n["same_path"] == 0, {k: v[:5] for k, v in classes.items() if k != "cos_sin"}
+        prim = r.trace_primary(0)
+        sky = (prim["hit"] < 0).sum()
+        mats = sc.materials()
+        tris = sc.triangles()
+        hit = prim["hit"][prim["hit"] >= 0]
+        textured = (~mats["isSimpleColor"][tris["materialWithPositiveNormalIndex"][hit]].astype(bool)).sum()
+        parity = r.render_single(3)
+    assert sky > 1000 and textured > 1000, "the frame must exercise the sky (%d px) and the texture lookup (%d px)" % (sky, textured)
+    with pt.PathTracerCUDA(cw, ch, ray_max_depth=depth, mode=pt.MODE_FAST, flags=pt.FLAG_NO_VARIANCE) as f:
+        f.upload(sc)
+        fast = f.render_single(3)
+        fp = f.trace_primary(0)
+    assert (fp["hit"] != prim["hit"]).mean() <= 1e-4
+    bad = _bad_pixels(fast, parity).mean()
+    print("C4 scene 512x288 FAST vs PARITY: %.4f %% of pixels outside 1e-3" % (100 * bad))
+    assert bad <= 1e-2
+    sc.close()
