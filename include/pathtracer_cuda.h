@@ -169,6 +169,31 @@ typedef struct ptc_device_buffers
  * never zeroes them) and the wavefront state. */
 PTC_API int ptc_create(const ptc_config *config, ptc_ctx **out_ctx);
 
+/* Multi-GPU: ONE context that drives `n_devices` CUDA devices of this box from the caller's single host thread —
+ * so the reference's own caller (PathTracer_Main -> OpenCL_RunKernel, Controleur/PathTracer.cpp:73-89) scales to the whole box
+ * through the same three calls. `config->device` is ignored, `config->stream` must be NULL. Every ptc_* call accepts the context:
+ *   ptc_upload_scene   flattens and uploads once, then copies the device scene to the other devices (peer copies over NVLink);
+ *   ptc_render(f, n)   n >= n_devices: device g renders the g-th share of the iterations [f, f + n) (shares differ by at most one,
+ *                      earlier devices take the extras) over the whole frame; n < n_devices (a progressive frame): every device
+ *                      renders all n iterations of its interleaved 8-row pixel stripes. The random stream of a path depends on
+ *                      (x, y, iteration, W, H) only (Kernel/PathTracer_FullKernel_header.cl:255-264): either way exactly the
+ *                      paths of a one-device render are traced, each once;
+ *   ptc_read_image / ptc_read_stats / ptc_get_device_buffers   first sum the devices' accumulators into the first device
+ *                      (ncclReduce of imageColor, imageRayNb and the three uint32 histograms; NCCL is bound at run time with dlopen,
+ *                      PTC_MULTI_REDUCE=p2p selects peer copies + an add kernel instead) and clear the other devices';
+ *   ptc_read_rgb8 / ptc_convert_rgb8   after stripes-only renders: every device converts its own rows, one uint8 reduce composes
+ *                      the frame (3 bytes per pixel over NVLink instead of 20); otherwise as ptc_read_image + conversion;
+ *   ptc_read_counters  sums over the devices; the parity probes and ptc_add_image act on the first device.
+ * imageV is not maintained (not linearly summable): ptc_read_variance and ptc_set_supersampling refuse; ptc_set_pixel_stripes
+ * refuses (the context shards by itself). Sums are made in another order than one device makes them: counts and histograms are
+ * exactly those of a one-device render, colours agree to an RMSE of 1e-4 of the mean.
+ * n_devices == 1 is ptc_create on devices[0]. */
+PTC_API int ptc_create_multi(const ptc_config *config, const int32_t *devices, uint32_t n_devices, ptc_ctx **out_ctx);
+/* Devices of a context (1 for ptc_create); writes up to `capacity` ordinals, returns the count. */
+PTC_API int ptc_context_devices(const ptc_ctx *ctx, int32_t *devices, uint32_t capacity);
+/* "nccl", "p2p" (peer copies + add kernel) or "none" (one device): how a context sums its devices' accumulators. */
+PTC_API const char *ptc_multi_reduce_kind(const ptc_ctx *ctx);
+
 /* OpenCL_InitializeMemory: validate, flatten and upload the scene; set the camera. May be called again
  * with a new scene (accumulators are kept; call ptc_reset_accumulation to start over). */
 PTC_API int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *scene);

@@ -2,7 +2,9 @@
 
 libpathtracer_cuda.so  — the C ABI of include/pathtracer_cuda.h (the drop-in boundary, reference
                          Controleur/PathTracer_OpenCL.h:17-19)
-libpathtracer_host.so  — host-side mirror of the reference interface + pth_* helpers
+libpathtracer_scene.so — scene side of the host mirror of the reference interface (importers, BVH builder) + pth_scene_*;
+                         independent of the CUDA library (bench.py's reference arm loads only this one)
+libpathtracer_host.so  — controller side (PathTracer_Main, CUDA_* shims) + pth_main / pth_run_default
 
 Loading never falls back to anything: a missing library raises, and ptc_create fails without a CUDA device.
 """
@@ -68,10 +70,11 @@ class SceneInfo(C.Structure):
 PTC_SYMBOLS = ["ptc_create", "ptc_upload_scene", "ptc_set_camera", "ptc_reset_accumulation", "ptc_set_supersampling", "ptc_render", "ptc_synchronize",
                "ptc_read_image", "ptc_read_variance", "ptc_read_stats", "ptc_read_rgb8", "ptc_convert_rgb8", "ptc_set_pixel_stripes", "ptc_add_image", "ptc_read_counters",
                "ptc_get_device_buffers", "ptc_trace_primary", "ptc_trace_rays", "ptc_render_single", "ptc_path_probe", "ptc_host_alloc", "ptc_host_free",
-               "ptc_last_error", "ptc_version", "ptc_device_count", "ptc_destroy", "ptc_wide_bvh_build", "ptc_wide_bvh_read", "ptc_wide_bvh_free", "ptc_measure_read_bandwidth"]
+               "ptc_last_error", "ptc_version", "ptc_device_count", "ptc_destroy", "ptc_wide_bvh_build", "ptc_wide_bvh_read", "ptc_wide_bvh_free", "ptc_measure_read_bandwidth", "ptc_create_multi", "ptc_context_devices", "ptc_multi_reduce_kind"]
 
 _cuda = None
 _host = None
+_scene = None
 
 
 def _ensure_built():
@@ -115,6 +118,10 @@ def cuda_lib():
     L.ptc_render_single.argtypes = [vp, u32, vp]
     L.ptc_path_probe.argtypes = [vp, u32, u32, vp, vp, vp, vp]
     L.ptc_measure_read_bandwidth.argtypes = [vp, C.c_size_t, u32, P(C.c_double)]
+    L.ptc_create_multi.argtypes = [P(Config), P(i32), u32, P(vp)]
+    L.ptc_context_devices.argtypes = [vp, P(i32), u32]
+    L.ptc_multi_reduce_kind.argtypes = [vp]
+    L.ptc_multi_reduce_kind.restype = C.c_char_p
     L.ptc_host_alloc.argtypes = [C.c_size_t]
     L.ptc_host_alloc.restype = vp
     L.ptc_host_free.argtypes = [vp]
@@ -133,15 +140,15 @@ def cuda_lib():
     return L
 
 
-def host_lib():
-    global _host
-    if _host is not None:
-        return _host
-    cuda_lib()
-    path = os.path.join(LIB_DIR, "libpathtracer_host.so")
+def scene_lib():
+    """libpathtracer_scene.so: procedural / file importers + BVH_Create. Does NOT load the CUDA library."""
+    global _scene
+    if _scene is not None:
+        return _scene
+    path = os.path.join(LIB_DIR, "libpathtracer_scene.so")
     if not os.path.exists(path):
         _ensure_built()
-    L = C.CDLL(path)
+    L = C.CDLL(path, mode=C.RTLD_GLOBAL)
     vp, u32 = C.c_void_p, C.c_uint32
     L.pth_last_error.restype = C.c_char_p
     L.pth_scene_create.argtypes = [C.c_char_p, u32, u32, u32, C.c_int]
@@ -157,7 +164,25 @@ def host_lib():
     L.pth_scene_export.argtypes = [vp, C.c_char_p]
     L.pth_scene_free.argtypes = [vp]
     L.pth_scene_free.restype = None
-    L.pth_main.argtypes = [C.c_char_p, u32, u32, u32, u32, C.c_int, C.c_int, C.c_int, u32, C.c_int, u32, C.c_int, C.c_char_p,
+    _scene = L
+    return L
+
+
+def host_lib():
+    """libpathtracer_host.so: the controller (PathTracer_Main) and the CUDA_* shims; loads the CUDA and scene libraries."""
+    global _host
+    if _host is not None:
+        return _host
+    cuda_lib()
+    scene_lib()
+    path = os.path.join(LIB_DIR, "libpathtracer_host.so")
+    if not os.path.exists(path):
+        _ensure_built()
+    L = C.CDLL(path)
+    vp, u32 = C.c_void_p, C.c_uint32
+    L.pth_host_last_error.restype = C.c_char_p
+    L.pth_main.argtypes = [C.c_char_p, u32, u32, u32, u32, C.c_int, C.c_int, C.c_int, u32, C.c_int, u32, C.c_int, C.c_int, C.c_char_p,
                            vp, vp, vp, vp, vp]
+    L.pth_run_default.argtypes = [vp, u32, u32, C.POINTER(C.c_double), vp]
     _host = L
     return L

@@ -2,8 +2,9 @@
 """Builds the native libraries IN-TREE (opencl_pathtracer_b200/_lib/):
 
   libpathtracer_cuda.so   the product: sm_100a kernels + the C ABI of include/pathtracer_cuda.h
-  libpathtracer_host.so   host-side mirror of the reference interface (importer, BVH builder, controller,
-                          CUDA_* shims) + the pth_* C entry points used by Python
+  libpathtracer_scene.so  scene side of the host mirror of the reference interface (importers, BVH builder) + pth_scene_*;
+                          does not depend on the CUDA library
+  libpathtracer_host.so   controller side (PathTracer_Main, CUDA_* shims, headless dialog) + pth_main / pth_run_default
   pathtracer_alone        headless stand-alone front-end (counterpart of the reference's Alone/main.cpp)
 
 nvcc cross-compiles for sm_100a without a GPU. Bit-exact arithmetic: -fmad=false on the device,
@@ -45,27 +46,34 @@ def build(verbose=False, force=False):
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))] + \
               [os.path.join(INC, f) for f in os.listdir(INC)]
     cu = [os.path.join(CSRC, "pt_kernels.cu"), os.path.join(CSRC, "pt_wide_build.cu"), os.path.join(CSRC, "pt_lbvh.cu"),
-          os.path.join(CSRC, "pathtracer_cuda.cu")]
+          os.path.join(CSRC, "pathtracer_cuda.cu"), os.path.join(CSRC, "pt_multi.cu")]
     if force or _newer(cuda_so, cu + headers + [__file__]):
         objs = []
         for src in cu:
             obj = os.path.join(LIB, os.path.basename(src) + ".o")
             _run(["nvcc"] + NVCC_FLAGS + ["-c", src, "-o", obj], verbose)
             objs.append(obj)
-        _run(["nvcc", "-shared", "-o", cuda_so] + objs + ["-Xcompiler", "-fopenmp", "-lgomp"], verbose)
+        _run(["nvcc", "-shared", "-o", cuda_so] + objs + ["-Xcompiler", "-fopenmp", "-lgomp", "-ldl"], verbose)
         for o in objs:
             os.remove(o)
-    host_so = os.path.join(LIB, "libpathtracer_host.so")
-    host_src = [os.path.join(HOST, f) for f in ("PathTracer_BVH.cpp", "PathTracer_ProceduralImporter.cpp", "PathTracer_CUDA.cpp",
-                                                "PathTracer_Dialog.cpp", "PathTracer_FileImporter.cpp", "PathTracer.cpp", "pth_capi.cpp")]
     host_hdr = [os.path.join(HOST, f) for f in os.listdir(HOST) if f.endswith(".h")] + headers
-    if force or _newer(host_so, host_src + host_hdr + [cuda_so, __file__]):
+    # scene side of the host mirror (importers, BVH builder): no dependency on the CUDA library — bench.py's reference arm
+    # generates its scenes through it without mapping any device code
+    scene_so = os.path.join(LIB, "libpathtracer_scene.so")
+    scene_src = [os.path.join(HOST, f) for f in ("PathTracer_BVH.cpp", "PathTracer_ProceduralImporter.cpp", "PathTracer_FileImporter.cpp",
+                                                 "pth_scene_capi.cpp")]
+    if force or _newer(scene_so, scene_src + host_hdr + [__file__]):
+        _run(["g++"] + CXX_FLAGS + ["-shared", "-o", scene_so] + scene_src, verbose)
+    # controller side: PathTracer_Main, the CUDA_* shims, the headless dialog
+    host_so = os.path.join(LIB, "libpathtracer_host.so")
+    host_src = [os.path.join(HOST, f) for f in ("PathTracer_CUDA.cpp", "PathTracer_Dialog.cpp", "PathTracer.cpp", "pth_capi.cpp")]
+    if force or _newer(host_so, host_src + host_hdr + [cuda_so, scene_so, __file__]):
         _run(["g++"] + CXX_FLAGS + ["-shared", "-o", host_so] + host_src +
-             ["-L", LIB, "-lpathtracer_cuda", "-Wl,-rpath,$ORIGIN"], verbose)
+             ["-L", LIB, "-lpathtracer_scene", "-lpathtracer_cuda", "-Wl,-rpath,$ORIGIN"], verbose)
     exe = os.path.join(LIB, "pathtracer_alone")
     if force or _newer(exe, [os.path.join(HOST, "main.cpp"), host_so]):
-        _run(["g++"] + CXX_FLAGS + ["-o", exe, os.path.join(HOST, "main.cpp"), "-L", LIB, "-lpathtracer_host", "-lpathtracer_cuda",
-                                    "-Wl,-rpath,$ORIGIN"], verbose)
+        _run(["g++"] + CXX_FLAGS + ["-o", exe, os.path.join(HOST, "main.cpp"), "-L", LIB, "-lpathtracer_host", "-lpathtracer_scene",
+                                    "-lpathtracer_cuda", "-Wl,-rpath,$ORIGIN"], verbose)
     return cuda_so, host_so
 
 

@@ -14,143 +14,38 @@
 #include <string>
 #include <vector>
 
-#include "pt_launch.h"
+#include "pt_context.h"
 #include "pt_lbvh.h"
 #include "pt_wide_build.h"
 
 using namespace ptc;
 
-namespace
+namespace ptc
 {
-thread_local std::string g_createError;
-
-struct StageEvent
+std::string &create_error()
 {
-    int stage;  // 0 generate, 1 extend, 2 connect, 3 shade, 4 accumulate
-    cudaEvent_t a, b;
-};
-
-template <typename T>
-struct DevBuf
-{
-    T *p = nullptr;
-    size_t n = 0;
-    cudaError_t alloc(size_t count)
-    {
-        release();
-        n = count;
-        if (count == 0) count = 1;  // the reference clamps empty buffers to 1 byte (PathTracer_OpenCL.cpp:165-171)
-        return cudaMalloc((void **)&p, count * sizeof(T));
-    }
-    void release()
-    {
-        if (p) cudaFree(p);
-        p = nullptr;
-        n = 0;
-    }
-    void adopt(T *ptr, size_t count)  // takes over a cudaMalloc'ed buffer
-    {
-        release();
-        p = ptr;
-        n = count;
-    }
-};
-}  // namespace
-
-struct ptc_ctx
-{
-    ptc_config cfg{};
-    int device = 0;
-    cudaStream_t stream = nullptr;
-    bool ownStream = false;
-    bool fast = false;
-    bool sceneLoaded = false;
-    std::string err;
-
-    uint32_t nPix = 0, batchIters = 1;
-    uint32_t stripeRows = 0, stripeRank = 0, stripeWorld = 1, ownedPix = 0;  // pixel shard (ptc_set_pixel_stripes); 0 rows = whole frame
-    size_t capacity = 0;  // path slots
-    LaunchCfg lc{};
-    int smCount = 0;
-
-    // scene
-    DevBuf<DevNode> nodes;
-    DevBuf<DevTri> tris;
-    DevBuf<DevShade> shade;
-    DevBuf<DevMaterial> materials;
-    DevBuf<DevLight> lights;
-    DevBuf<uint4> textures;
-    DevBuf<uchar4> texels;
-    DevBuf<uint32_t> bigLeaf;
-    DevBuf<DevNode8P> nodes8;  // FAST + wide BVH only; padded records, see pt_wide.cuh
-    DevBuf<DevTri> tris8;
-    DevBuf<uint32_t> tri8Index;
-    bool wide = false;
-    bool gpuBvh = false;      // PTC_FLAG_GPU_BVH: the wide BVH is built on the device, the caller's BVH is ignored
-    uint32_t wideDepth = 0;
-    float msGpuBuild = 0.f;
-    SceneDev sc{};
-    Camera cam{};
-
-    // path state + queues
-    DevBuf<float4> org, dir, thr, rad, hit;
-    DevBuf<int> seed;
-    DevBuf<float2> sample;
-    DevBuf<uint32_t> meta, nbbx, ntri, occl, queue[2];
-    PathState st{};
-    DevBuf<Counters> counters;
-
-    // accumulators
-    DevBuf<float4> imgColor, imgV;
-    DevBuf<float> imgRayNb;
-    DevBuf<uint32_t> rayDepths, rayBbx, rayTri;
-    ImageDev img{};
-    DevBuf<uint8_t> rgb8;
-    DevBuf<float> x2inv;  // ptc_set_supersampling: the chi-square table of the reference's `-D SUPER_SAMPLING` build; empty = off
-    uint32_t x2invSize = 0;
-
-    // host-side counters
-    uint64_t launches = 0, launchesExtend = 0, launchesConnect = 0;
-
-    // A launch-bound batch (progressive frames: ~34 kernels of a few microseconds each) is captured once into a CUDA graph and
-    // replayed; only the generate and accumulate nodes carry per-batch arguments (iteration numbers, camera).
-    struct BatchGraph
-    {
-        cudaGraph_t graph = nullptr;
-        cudaGraphExec_t exec = nullptr;
-        cudaGraphNode_t genNode = nullptr, accNode = nullptr;
-        cudaKernelNodeParams genParams{}, accParams{};
-        uint32_t nIter = 0, ownedPix = 0, stripeRows = 0, stripeRank = 0, stripeWorld = 0;
-        uint64_t sceneVersion = 0;
-        uint64_t launches = 0, launchesExtend = 0, launchesConnect = 0;  // per replay
-    } batchGraph;
-    uint64_t sceneVersion = 0;
-    bool useGraphs = true;
-    double msStage[5] = {0, 0, 0, 0, 0};
-    std::vector<StageEvent> pending;
-    std::vector<cudaEvent_t> eventPool;
-};
-
-namespace
-{
-int fail(ptc_ctx *c, int code, const char *fmt, ...)
-{
-    char buf[512];
-    va_list ap;
-    va_start(ap, fmt);
-    vsnprintf(buf, sizeof(buf), fmt, ap);
-    va_end(ap);
-    if (c) c->err = buf;
-    else g_createError = buf;
-    return code;
+    thread_local std::string e;
+    return e;
 }
+}  // namespace ptc
 
-#define CK(call)                                                                                              \
-    do                                                                                                        \
-    {                                                                                                         \
-        cudaError_t e__ = (call);                                                                             \
-        if (e__ != cudaSuccess) return fail(ctx, PTC_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e__)); \
-    } while (0)
+namespace
+{
+// A multi-device handle (ptc_create_multi, pt_multi.cu) answers the single-device calls through its member 0 — after the members'
+// accumulators have been summed into it where the call reads them — and carries the member's error message over.
+template <typename F>
+int onPrimary(ptc_ctx *h, bool reduceFirst, F f)
+{
+    if (reduceFirst)
+    {
+        const int rc = multi_reduce(h);
+        if (rc != PTC_OK) return rc;
+    }
+    ptc_ctx *p = multi_primary(h);
+    const int rc = f(p);
+    if (rc != PTC_OK) h->err = p->err;
+    return rc;
+}
 
 inline float4 to4(const ptc_float4 &v) { return make_float4(v.x, v.y, v.z, v.w); }
 inline float hdot4(const ptc_float4 &a, const ptc_float4 &b) { return ((a.x * b.x + a.y * b.y) + a.z * b.z) + a.w * b.w; }
@@ -222,7 +117,7 @@ int ptc_device_count(void)
     return n;
 }
 
-const char *ptc_last_error(const ptc_ctx *ctx) { return ctx ? ctx->err.c_str() : g_createError.c_str(); }
+const char *ptc_last_error(const ptc_ctx *ctx) { return ctx ? ctx->err.c_str() : create_error().c_str(); }
 
 void *ptc_host_alloc(size_t bytes)
 {
@@ -238,6 +133,7 @@ void ptc_host_free(void *p)
 int ptc_measure_read_bandwidth(ptc_ctx *ctx, size_t bytes, uint32_t repeats, double *gb_per_s)
 {
     if (!ctx || !gb_per_s || bytes < 32 || repeats == 0) return PTC_ERR_INVALID;
+    if (ctx->group) return onPrimary(ctx, false, [&](ptc_ctx *p) { return ptc_measure_read_bandwidth(p, bytes, repeats, gb_per_s); });
     CK(cudaSetDevice(ctx->device));
     DevBuf<uint4> buf;
     DevBuf<uint32_t> sink;
@@ -269,6 +165,11 @@ int ptc_measure_read_bandwidth(ptc_ctx *ctx, size_t bytes, uint32_t repeats, dou
 void ptc_destroy(ptc_ctx *ctx)
 {
     if (!ctx) return;
+    if (ctx->group)
+    {
+        multi_destroy(ctx);
+        return;
+    }
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     drainTimers(ctx);
@@ -289,6 +190,7 @@ void ptc_destroy(ptc_ctx *ctx)
 int ptc_reset_accumulation(ptc_ctx *ctx)
 {
     if (!ctx) return PTC_ERR_INVALID;
+    if (ctx->group) return multi_reset(ctx);
     CK(cudaSetDevice(ctx->device));
     CK(cudaMemsetAsync(ctx->imgColor.p, 0, sizeof(float4) * ctx->nPix, ctx->stream));
     CK(cudaMemsetAsync(ctx->imgRayNb.p, 0, sizeof(float) * ctx->nPix, ctx->stream));
@@ -311,6 +213,8 @@ int ptc_reset_accumulation(ptc_ctx *ctx)
 int ptc_set_supersampling(ptc_ctx *ctx, const float *x2inv, uint32_t count)
 {
     if (!ctx) return PTC_ERR_INVALID;
+    if (ctx->group)
+        return count == 0 ? PTC_OK : fail(ctx, PTC_ERR_STATE, "supersampling decides on the accumulators of the iterations before: not available on a multi-device context, whose devices render iteration ranges side by side");
     CK(cudaSetDevice(ctx->device));
     CK(cudaStreamSynchronize(ctx->stream));
     if (count == 0)
@@ -341,7 +245,7 @@ int ptc_set_supersampling(ptc_ctx *ctx, const float *x2inv, uint32_t count)
 
 int ptc_create(const ptc_config *config, ptc_ctx **out_ctx)
 {
-    ptc_ctx *ctx = nullptr;  // CK() reports into g_createError while ctx is null
+    ptc_ctx *ctx = nullptr;  // CK() reports into create_error() while ctx is null
     if (!config || !out_ctx) return fail(nullptr, PTC_ERR_INVALID, "ptc_create: null argument");
     *out_ctx = nullptr;
     if (config->struct_size != sizeof(ptc_config)) return fail(nullptr, PTC_ERR_INVALID, "ptc_create: struct_size %u != %zu", config->struct_size, sizeof(ptc_config));
@@ -407,7 +311,8 @@ int ptc_create(const ptc_config *config, ptc_ctx **out_ctx)
     c->lc.stackDepth = 32;
     c->lc.wide = false;
     c->lc.count = !c->fast || (config->flags & PTC_FLAG_WORK_COUNTERS);
-    c->lc.traverseGrid = c->smCount * traverse_ctas_per_sm(c->fast, false, c->lc.stackDepth);
+    c->lc.traverseGrid = c->smCount * traverse_ctas_per_sm(c->fast, false, c->lc.stackDepth, false);
+    c->lc.connectGrid = c->smCount * traverse_ctas_per_sm(c->fast, false, c->lc.stackDepth, true);
     c->lc.streamGrid = c->smCount * 8;
     c->lc.refillMin = 4;  // idle lanes that trigger a refill from the warp's staged rays (profiles/r01_sweeps.txt)
     if (const char *e = std::getenv("PTC_GRAPHS")) c->useGraphs = std::atoi(e) != 0;
@@ -421,7 +326,7 @@ int ptc_create(const ptc_config *config, ptc_ctx **out_ctx)
         if (const char *e = std::getenv("PTC_VOTE_TRI")) vt = (uint32_t)std::max(0, std::min(8, std::atoi(e)));
         c->lc.refillMin |= (vn << 8) | (vt << 16);
     }
-    if (const char *e = std::getenv("PTC_CTAS_PER_SM")) c->lc.traverseGrid = c->smCount * std::max(1, std::atoi(e));
+    if (const char *e = std::getenv("PTC_CTAS_PER_SM")) c->lc.traverseGrid = c->lc.connectGrid = c->smCount * std::max(1, std::atoi(e));
 
     cudaError_t e = cudaSuccess;
     auto A = [&](cudaError_t r) { if (e == cudaSuccess) e = r; };
@@ -444,7 +349,7 @@ int ptc_create(const ptc_config *config, ptc_ctx **out_ctx)
     int rc = ptc_reset_accumulation(c);
     if (rc != PTC_OK)
     {
-        g_createError = c->err;
+        create_error() = c->err;
         ptc_destroy(c);
         return rc;
     }
@@ -463,6 +368,7 @@ int ptc_create(const ptc_config *config, ptc_ctx **out_ctx)
 int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
 {
     if (!ctx || !s) return PTC_ERR_INVALID;
+    if (ctx->group) return multi_upload_scene(ctx, s);
     if (s->struct_size != sizeof(ptc_scene_view)) return fail(ctx, PTC_ERR_INVALID, "ptc_upload_scene: struct_size mismatch");
     const uint32_t nT = s->triangulation_size, nN = ctx->gpuBvh ? 0u : s->bvh_size, nL = s->lights_size, nM = s->materiaux_size, nX = s->textures_size;
     const uint32_t nTexel = s->textures_data_size;
@@ -732,12 +638,63 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
     {
         ctx->lc.stackDepth = (int)std::min<uint32_t>(32u, std::max<uint32_t>(4u, maxDepth + 1));
         if (ctx->wide) ctx->lc.stackDepth = (int)std::max<uint32_t>(3u, wideDepth + 2);  // the parked triangle group + one sibling group per level
-        if (!std::getenv("PTC_CTAS_PER_SM")) ctx->lc.traverseGrid = ctx->smCount * traverse_ctas_per_sm(ctx->fast, ctx->wide, ctx->lc.stackDepth);
+        if (!std::getenv("PTC_CTAS_PER_SM"))
+        {
+            ctx->lc.traverseGrid = ctx->smCount * traverse_ctas_per_sm(ctx->fast, ctx->wide, ctx->lc.stackDepth, false);
+            ctx->lc.connectGrid = ctx->smCount * traverse_ctas_per_sm(ctx->fast, ctx->wide, ctx->lc.stackDepth, true);
+        }
     }
     ctx->sceneLoaded = true;
     ctx->sceneVersion++;  // device pointers and launch configuration may have changed: a captured batch graph is stale
     return PTC_OK;
 }
+
+}  // extern "C"
+
+// Multi-device contexts: the scene is flattened and uploaded once (member 0) and copied device to device to the other members
+// (cudaMemcpyPeer: NVLink where peer access exists), so the host-side work of ptc_upload_scene — validation, wide-BVH collapse,
+// 10 M-triangle flattening — is not repeated per GPU.
+namespace ptc
+{
+int replicate_scene(ptc_ctx *dst, const ptc_ctx *src)
+{
+    ptc_ctx *ctx = dst;
+    CK(cudaSetDevice(dst->device));
+    CK(cudaStreamSynchronize(dst->stream));
+    cudaError_t e = cudaSuccess;
+    auto rep = [&](auto &d, const auto &s_) {
+        if (e != cudaSuccess) return;
+        e = d.alloc(s_.n);
+        if (e == cudaSuccess && s_.n)
+            e = cudaMemcpyPeerAsync(d.p, dst->device, s_.p, src->device, s_.n * sizeof(*s_.p), dst->stream);
+    };
+    rep(dst->nodes, src->nodes); rep(dst->tris, src->tris); rep(dst->shade, src->shade); rep(dst->materials, src->materials);
+    rep(dst->lights, src->lights); rep(dst->textures, src->textures); rep(dst->texels, src->texels); rep(dst->bigLeaf, src->bigLeaf);
+    rep(dst->nodes8, src->nodes8); rep(dst->tris8, src->tris8); rep(dst->tri8Index, src->tri8Index);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(dst->stream);
+    if (e != cudaSuccess) return fail(dst, PTC_ERR_CUDA, "scene replication to device %d: %s", dst->device, cudaGetErrorString(e));
+    SceneDev sc = src->sc;
+    sc.nodes = dst->nodes.p; sc.tris = dst->tris.p; sc.shade = dst->shade.p; sc.materials = dst->materials.p;
+    sc.lights = dst->lights.p; sc.textures = dst->textures.p; sc.texels = dst->texels.p;
+    sc.bigLeafCount = src->sc.bigLeafCount ? dst->bigLeaf.p : nullptr;
+    sc.nodes8 = src->sc.nodes8 ? dst->nodes8.p : nullptr; sc.tris8 = src->sc.tris8 ? dst->tris8.p : nullptr;
+    sc.tri8Index = src->sc.tri8Index ? dst->tri8Index.p : nullptr;
+    dst->sc = sc;
+    dst->cam = src->cam;
+    dst->wideDepth = src->wideDepth;
+    dst->msGpuBuild = src->msGpuBuild;
+    dst->lc.wide = src->lc.wide;
+    dst->lc.stackDepth = src->lc.stackDepth;
+    dst->lc.traverseGrid = dst->smCount * traverse_ctas_per_sm(dst->fast, dst->wide, dst->lc.stackDepth, false);  // also opts this device's kernels in to large stacks
+    dst->lc.connectGrid = dst->smCount * traverse_ctas_per_sm(dst->fast, dst->wide, dst->lc.stackDepth, true);
+    if (const char *env = std::getenv("PTC_CTAS_PER_SM")) dst->lc.traverseGrid = dst->lc.connectGrid = dst->smCount * std::max(1, std::atoi(env));
+    dst->sceneLoaded = true;
+    dst->sceneVersion++;
+    return PTC_OK;
+}
+}  // namespace ptc
+
+extern "C" {
 
 int ptc_wide_bvh_build(const ptc_scene_view *scene, ptc_wide_bvh *out)
 {
@@ -764,6 +721,7 @@ int ptc_wide_bvh_build(const ptc_scene_view *scene, ptc_wide_bvh *out)
 int ptc_wide_bvh_read(ptc_ctx *ctx, ptc_wide_bvh *out)
 {
     if (!ctx || !out) return PTC_ERR_INVALID;
+    if (ctx->group) return onPrimary(ctx, false, [&](ptc_ctx *p) { return ptc_wide_bvh_read(p, out); });
     std::memset(out, 0, sizeof(*out));
     if (!ctx->sceneLoaded) return fail(ctx, PTC_ERR_STATE, "ptc_wide_bvh_read before ptc_upload_scene");
     if (!ctx->wide) return fail(ctx, PTC_ERR_STATE, "ptc_wide_bvh_read: this context walks the BVH2");
@@ -802,6 +760,7 @@ void ptc_wide_bvh_free(ptc_wide_bvh *bvh)
 int ptc_set_camera(ptc_ctx *ctx, const float camera[16])
 {
     if (!ctx || !camera) return PTC_ERR_INVALID;
+    if (ctx->group) return multi_set_camera(ctx, camera);
     std::memcpy(&ctx->cam, camera, sizeof(Camera));
     return PTC_OK;
 }
@@ -961,6 +920,7 @@ int runBatchGraph(ptc_ctx *ctx, uint32_t first, uint32_t nIter)
 int ptc_render(ptc_ctx *ctx, uint32_t first_iteration, uint32_t n_iterations)
 {
     if (!ctx) return PTC_ERR_INVALID;
+    if (ctx->group) return multi_render(ctx, first_iteration, n_iterations);
     if (!ctx->sceneLoaded) return fail(ctx, PTC_ERR_STATE, "ptc_render before ptc_upload_scene");
     CK(cudaSetDevice(ctx->device));
     uint32_t done = 0;
@@ -987,6 +947,7 @@ int ptc_render(ptc_ctx *ctx, uint32_t first_iteration, uint32_t n_iterations)
 int ptc_synchronize(ptc_ctx *ctx)
 {
     if (!ctx) return PTC_ERR_INVALID;
+    if (ctx->group) return multi_synchronize(ctx);
     CK(cudaSetDevice(ctx->device));
     CK(cudaStreamSynchronize(ctx->stream));
     drainTimers(ctx);
@@ -1003,6 +964,7 @@ static int readBack(ptc_ctx *ctx, void *dst, const void *src, size_t bytes)
 int ptc_read_image(ptc_ctx *ctx, float *image_color, float *image_ray_nb)
 {
     if (!ctx) return PTC_ERR_INVALID;
+    if (ctx->group) return onPrimary(ctx, true, [&](ptc_ctx *p) { return ptc_read_image(p, image_color, image_ray_nb); });
     CK(cudaSetDevice(ctx->device));
     int rc = readBack(ctx, image_color, ctx->imgColor.p, sizeof(float4) * ctx->nPix);
     if (rc == PTC_OK) rc = readBack(ctx, image_ray_nb, ctx->imgRayNb.p, sizeof(float) * ctx->nPix);
@@ -1013,6 +975,7 @@ int ptc_read_image(ptc_ctx *ctx, float *image_color, float *image_ray_nb)
 int ptc_read_variance(ptc_ctx *ctx, float *image_v)
 {
     if (!ctx) return PTC_ERR_INVALID;
+    if (ctx->group) return fail(ctx, PTC_ERR_STATE, "imageV is not maintained by a multi-device context (a variance accumulator is not linearly summable)");
     if (!ctx->imgV.p) return fail(ctx, PTC_ERR_STATE, "context created with PTC_FLAG_NO_VARIANCE");
     CK(cudaSetDevice(ctx->device));
     int rc = readBack(ctx, image_v, ctx->imgV.p, sizeof(float4) * ctx->nPix);
@@ -1023,6 +986,7 @@ int ptc_read_variance(ptc_ctx *ctx, float *image_v)
 int ptc_read_stats(ptc_ctx *ctx, uint32_t *ray_depths, uint32_t *ray_bbx, uint32_t *ray_tri)
 {
     if (!ctx) return PTC_ERR_INVALID;
+    if (ctx->group) return onPrimary(ctx, true, [&](ptc_ctx *p) { return ptc_read_stats(p, ray_depths, ray_bbx, ray_tri); });
     CK(cudaSetDevice(ctx->device));
     int rc = readBack(ctx, ray_depths, ctx->rayDepths.p, sizeof(uint32_t) * (ctx->cfg.ray_max_depth + 1));
     if (rc == PTC_OK) rc = readBack(ctx, ray_bbx, ctx->rayBbx.p, sizeof(uint32_t) * PTC_MAX_INTERSECTION_NUMBER);
@@ -1034,6 +998,7 @@ int ptc_read_stats(ptc_ctx *ctx, uint32_t *ray_depths, uint32_t *ray_bbx, uint32
 int ptc_read_rgb8(ptc_ctx *ctx, uint8_t *rgb)
 {
     if (!ctx || !rgb) return PTC_ERR_INVALID;
+    if (ctx->group) return multi_read_rgb8(ctx, rgb);
     CK(cudaSetDevice(ctx->device));
     int rc = ptc_convert_rgb8(ctx);
     if (rc == PTC_OK) rc = readBack(ctx, rgb, ctx->rgb8.p, (size_t)3 * ctx->nPix);
@@ -1044,6 +1009,7 @@ int ptc_read_rgb8(ptc_ctx *ctx, uint8_t *rgb)
 int ptc_convert_rgb8(ptc_ctx *ctx)
 {
     if (!ctx) return PTC_ERR_INVALID;
+    if (ctx->group) return multi_read_rgb8(ctx, nullptr);
     CK(cudaSetDevice(ctx->device));
     if (!ctx->rgb8.p) CK(ctx->rgb8.alloc((size_t)3 * ctx->nPix));
     launch_rgb8(ctx->stream, ctx->img, frameParams(ctx, 0, 0), ctx->rgb8.p);
@@ -1054,6 +1020,7 @@ int ptc_convert_rgb8(ptc_ctx *ctx)
 int ptc_set_pixel_stripes(ptc_ctx *ctx, uint32_t stripe_rows, uint32_t rank, uint32_t world)
 {
     if (!ctx) return PTC_ERR_INVALID;
+    if (ctx->group) return fail(ctx, PTC_ERR_STATE, "a multi-device context shards by itself (iteration ranges, or pixel stripes when a call renders fewer iterations than it has devices)");
     if (stripe_rows == 0)
     {
         ctx->stripeRows = 0; ctx->stripeRank = 0; ctx->stripeWorld = 1; ctx->ownedPix = ctx->nPix;
@@ -1070,22 +1037,28 @@ int ptc_set_pixel_stripes(ptc_ctx *ctx, uint32_t stripe_rows, uint32_t rank, uin
 int ptc_add_image(ptc_ctx *ctx, const float *image_color, const float *image_ray_nb)
 {
     if (!ctx) return PTC_ERR_INVALID;
+    if (ctx->group) return onPrimary(ctx, false, [&](ptc_ctx *p) { return ptc_add_image(p, image_color, image_ray_nb); });
     CK(cudaSetDevice(ctx->device));
     DevBuf<float4> c;
     DevBuf<float> n;
+    cudaError_t e = cudaSuccess;
     if (image_color)
     {
-        CK(c.alloc(ctx->nPix));
-        CK(cudaMemcpyAsync(c.p, image_color, sizeof(float4) * ctx->nPix, cudaMemcpyHostToDevice, ctx->stream));
+        e = c.alloc(ctx->nPix);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(c.p, image_color, sizeof(float4) * ctx->nPix, cudaMemcpyHostToDevice, ctx->stream);
     }
-    if (image_ray_nb)
+    if (image_ray_nb && e == cudaSuccess)
     {
-        CK(n.alloc(ctx->nPix));
-        CK(cudaMemcpyAsync(n.p, image_ray_nb, sizeof(float) * ctx->nPix, cudaMemcpyHostToDevice, ctx->stream));
+        e = n.alloc(ctx->nPix);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(n.p, image_ray_nb, sizeof(float) * ctx->nPix, cudaMemcpyHostToDevice, ctx->stream);
     }
-    launch_add_image(ctx->stream, ctx->img, ctx->nPix, c.p, n.p);
-    ctx->launches++;
-    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    if (e == cudaSuccess)
+    {
+        launch_add_image(ctx->stream, ctx->img, ctx->nPix, c.p, n.p);
+        ctx->launches++;
+    }
+    const cudaError_t es = cudaStreamSynchronize(ctx->stream);  // also on the error paths: the temporaries may be in use
+    if (e == cudaSuccess) e = es;
     c.release();
     n.release();
     if (e != cudaSuccess) return fail(ctx, PTC_ERR_CUDA, "ptc_add_image: %s", cudaGetErrorString(e));
@@ -1095,6 +1068,7 @@ int ptc_add_image(ptc_ctx *ctx, const float *image_color, const float *image_ray
 int ptc_read_counters(ptc_ctx *ctx, ptc_counters *out)
 {
     if (!ctx || !out) return PTC_ERR_INVALID;
+    if (ctx->group) return multi_read_counters(ctx, out);
     int rc = ptc_synchronize(ctx);
     if (rc != PTC_OK) return rc;
     Counters h;
@@ -1123,6 +1097,8 @@ int ptc_read_counters(ptc_ctx *ctx, ptc_counters *out)
 int ptc_get_device_buffers(ptc_ctx *ctx, ptc_device_buffers *out)
 {
     if (!ctx || !out) return PTC_ERR_INVALID;
+    if (ctx->group) return onPrimary(ctx, true, [&](ptc_ctx *p) { return ptc_get_device_buffers(p, out); });
+    CK(cudaSetDevice(ctx->device));
     out->image_color = ctx->imgColor.p;
     out->image_ray_nb = ctx->imgRayNb.p;
     out->image_v = ctx->imgV.p;
@@ -1140,6 +1116,7 @@ int ptc_trace_primary(ptc_ctx *ctx, uint32_t iteration, int32_t *hit, float *st,
                       uint32_t *counts)
 {
     if (!ctx) return PTC_ERR_INVALID;
+    if (ctx->group) return onPrimary(ctx, false, [&](ptc_ctx *p) { return ptc_trace_primary(p, iteration, hit, st, dist2, dir, seed_after, counts); });
     if (!ctx->sceneLoaded) return fail(ctx, PTC_ERR_STATE, "ptc_trace_primary before ptc_upload_scene");
     if (ctx->stripeRows) return fail(ctx, PTC_ERR_STATE, "ptc_trace_primary: not available on a pixel shard (ptc_set_pixel_stripes)");
     CK(cudaSetDevice(ctx->device));
@@ -1181,6 +1158,7 @@ int ptc_trace_rays(ptc_ctx *ctx, uint32_t n, const float *origin, const float *d
                    float *dir, uint32_t *counts)
 {
     if (!ctx || !origin || !direction) return PTC_ERR_INVALID;
+    if (ctx->group) return onPrimary(ctx, false, [&](ptc_ctx *p) { return ptc_trace_rays(p, n, origin, direction, hit, st, dist2, dir, counts); });
     if (!ctx->sceneLoaded) return fail(ctx, PTC_ERR_STATE, "ptc_trace_rays before ptc_upload_scene");
     if (n == 0) return PTC_OK;
     if ((size_t)n > ctx->capacity) return fail(ctx, PTC_ERR_LIMIT, "ptc_trace_rays: %u rays, the context holds %zu path slots", n, ctx->capacity);
@@ -1223,6 +1201,7 @@ int ptc_trace_rays(ptc_ctx *ctx, uint32_t n, const float *origin, const float *d
 int ptc_render_single(ptc_ctx *ctx, uint32_t iteration, float *radiance)
 {
     if (!ctx || !radiance) return PTC_ERR_INVALID;
+    if (ctx->group) return onPrimary(ctx, false, [&](ptc_ctx *p) { return ptc_render_single(p, iteration, radiance); });
     if (!ctx->sceneLoaded) return fail(ctx, PTC_ERR_STATE, "ptc_render_single before ptc_upload_scene");
     if (ctx->stripeRows) return fail(ctx, PTC_ERR_STATE, "ptc_render_single: not available on a pixel shard (ptc_set_pixel_stripes)");
     CK(cudaSetDevice(ctx->device));
@@ -1239,6 +1218,7 @@ int ptc_render_single(ptc_ctx *ctx, uint32_t iteration, float *radiance)
 int ptc_path_probe(ptc_ctx *ctx, uint32_t iteration, uint32_t bounces, float *origin, float *direction, float *hit, uint32_t *meta)
 {
     if (!ctx) return PTC_ERR_INVALID;
+    if (ctx->group) return onPrimary(ctx, false, [&](ptc_ctx *p) { return ptc_path_probe(p, iteration, bounces, origin, direction, hit, meta); });
     if (!ctx->sceneLoaded) return fail(ctx, PTC_ERR_STATE, "ptc_path_probe before ptc_upload_scene");
     if (ctx->stripeRows) return fail(ctx, PTC_ERR_STATE, "ptc_path_probe: not available on a pixel shard (ptc_set_pixel_stripes)");
     if (bounces > ctx->cfg.ray_max_depth) return fail(ctx, PTC_ERR_INVALID, "ptc_path_probe: %u bounces, ray_max_depth is %u", bounces, ctx->cfg.ray_max_depth);

@@ -136,6 +136,7 @@ struct StagedRays  // one per warp
     float4 dir[32];
     float4 invBest[32];  // reciprocal direction (header.cl:280-282) and the initial distance bound
     uint32_t item[32];
+    uint32_t laneItem[32];  // the item each lane is tracing: cold state, read back once at completion instead of riding in a register
 };
 constexpr size_t kStageBytes = sizeof(StagedRays) * (kTraverseThreads / 32);
 
@@ -157,7 +158,7 @@ constexpr size_t kGroupBytes = sizeof(PathGroup) * (kTraverseThreads / 32);
 // with nothing, and cost two registers and two atomics per ray. Without COUNT the lane's counters run on across rays and only
 // the global totals (ptc_counters.box_tests / triangle_tests) are kept.
 template <bool ANY, int FAST, typename LaneT, bool COUNT>
-__global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas * 128 / kTraverseThreads) k_trace(SceneDev sc, PathState st, const uint32_t *__restrict__ queue,
+__global__ void __launch_bounds__(kTraverseThreads, (ANY ? LaneT::kMinCtasAny : LaneT::kMinCtas) * 128 / kTraverseThreads) k_trace(SceneDev sc, PathState st, const uint32_t *__restrict__ queue,
                                                            Counters *__restrict__ cn, int bounce, uint32_t popMin, int stackDepth)
 {
     typedef typename LaneT::StackT StackT;
@@ -180,13 +181,16 @@ __global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas * 128 / kTra
     uint32_t qHead = 0, qCount = 0;  // staged rays [qHead, qCount) are waiting (warp-uniform)
     uint32_t gMask = 0, gLight = 0;  // connect: lanes of the current path group that are lit, next light to stage for it
     bool lastGroup = false;
-    uint32_t p = 0, li = 0;
-    uint32_t nbSum = 0, ntSum = 0, nRays = 0;
+    uint32_t nbSum = 0, ntSum = 0;  // COUNT: per-lane sums of the finished rays' counters; else warp totals (uniform, from the votes)
+    uint32_t nRays = 0;             // rays this warp staged (uniform): every staged ray is traced
     while (true)
     {
         // ---- completion: write the result of a finished ray (the counters are fire-and-forget reductions)
         if (L.finished())
         {
+            const uint32_t item = stage.laneItem[lane];
+            const uint32_t p = ANY ? (item & ((1u << kLightShift) - 1u)) : item;
+            const uint32_t li = ANY ? (item >> kLightShift) : 0u;
             if (!ANY)
             {
                 float hs, ht, htp;
@@ -217,7 +221,6 @@ __global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas * 128 / kTra
                 nbSum += L.nb; ntSum += L.nt;
                 L.nb = L.nt = 0;
             }
-            nRays++;
             L.set_idle();
         }
         unsigned idle = __ballot_sync(full, L.idle());
@@ -321,6 +324,7 @@ __global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas * 128 / kTra
                 }
                 qHead = 0;
                 qCount = (uint32_t)__popc(m);
+                nRays += qCount;
                 __syncwarp();
             }
             // ---- refill: idle lanes take staged rays
@@ -331,9 +335,7 @@ __global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas * 128 / kTra
                 if (L.idle() && e < qCount)
                 {
                     const float4 o = stage.org[e], d = stage.dir[e], ib = stage.invBest[e];
-                    const uint32_t item = stage.item[e];
-                    p = ANY ? (item & ((1u << kLightShift) - 1u)) : item;
-                    li = ANY ? (item >> kLightShift) : 0u;
+                    stage.laneItem[lane] = stage.item[e];
                     Ray r;
                     r.ox = o.x; r.oy = o.y; r.oz = o.z; r.ow = o.w;
                     r.dx = d.x; r.dy = d.y; r.dz = d.z; r.dw = d.w;
@@ -359,6 +361,7 @@ __global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas * 128 / kTra
             const bool wantNode = L.wants_node();
             const int nN = __popc(__ballot_sync(full, wantNode));
             if (nN == 0 || 8 * nN < voteNode * nHave) break;
+            if (!COUNT) nbSum += (uint32_t)(LaneT::kBoxesPerNodeStep * nN);
             if (wantNode) lane_node_step<(FAST != 0)>(L, sc, stk, kTraverseThreads);
         }
         // ---- triangle phase: at least one step if any lane waits for a triangle, then while they are the majority
@@ -367,11 +370,13 @@ __global__ void __launch_bounds__(kTraverseThreads, LaneT::kMinCtas * 128 / kTra
             const bool wantTri = L.wants_tri();
             const int nT = __popc(__ballot_sync(full, wantTri));
             if (nT == 0) break;
+            if (!COUNT) ntSum += (uint32_t)nT;
             if (wantTri) lane_tri_step<ANY>(L, sc, stk, kTraverseThreads);
             if (8 * nT <= voteTri * nHave) break;
         }
     }
-    flush_work(cn, ANY ? &cn->shadowRays : &cn->extensionRays, nRays, COUNT ? nbSum : L.nb, COUNT ? ntSum : L.nt);
+    // warp totals live in lane 0 only (the per-lane sums of COUNT are added up by flush_work's reduction)
+    flush_work(cn, ANY ? &cn->shadowRays : &cn->extensionRays, lane == 0 ? nRays : 0u, (COUNT || lane == 0) ? nbSum : 0u, (COUNT || lane == 0) ? ntSum : 0u);
 }
 
 // ------------------------------------------------------------------------------------------------ shade
@@ -801,7 +806,7 @@ static int occupancy_of(size_t bytes)
     return n < m ? n : m;
 }
 
-int traverse_ctas_per_sm(bool fast, bool wide, int stackDepth)
+int traverse_ctas_per_sm(bool fast, bool wide, int stackDepth, bool any)
 {
     if (const char *e = std::getenv("PTC_CARVEOUT"))  // experiment: shared-memory carve-out in percent (what is left is L1)
     {
@@ -814,7 +819,7 @@ int traverse_ctas_per_sm(bool fast, bool wide, int stackDepth)
     if (wide) { n = occupancy_of<false, 1, WideLane>(bytes); m = occupancy_of<true, 1, WideLane>(bytesAny); }
     else if (fast) { n = occupancy_of<false, 1, TraceLane>(bytes); m = occupancy_of<true, 1, TraceLane>(bytesAny); }
     else { n = occupancy_of<false, 0, TraceLane>(bytes); m = occupancy_of<true, 0, TraceLane>(bytesAny); }
-    n = n < m ? n : m;
+    n = any ? m : n;
     return n < 1 ? 1 : n;
 }
 
@@ -837,7 +842,7 @@ static void launch_trace(cudaStream_t s, const LaunchCfg &lc, bool fast, const S
 {
     const size_t smem = stack_bytes(lc.wide, lc.stackDepth, ANY);
     const bool area = ANY && sc.areaJump != 1u;  // the scene holds area lights: the connect variant that samples them
-#define PTC_TRACE_(MODE, LANE, CNT) k_trace<ANY, MODE, LANE, CNT><<<lc.traverseGrid, kTraverseThreads, smem, s>>>(sc, st, queue, cn, bounce, lc.refillMin, lc.stackDepth)
+#define PTC_TRACE_(MODE, LANE, CNT) k_trace<ANY, MODE, LANE, CNT><<<(ANY ? lc.connectGrid : lc.traverseGrid), kTraverseThreads, smem, s>>>(sc, st, queue, cn, bounce, lc.refillMin, lc.stackDepth)
 #define PTC_TRACE(MODE, LANE) do { if (lc.count) PTC_TRACE_(MODE, LANE, true); else PTC_TRACE_(MODE, LANE, false); } while (0)
     if (lc.wide) { if (area) PTC_TRACE(ANY ? 2 : 1, WideLane); else PTC_TRACE(1, WideLane); }
     else if (fast) { if (area) PTC_TRACE(ANY ? 2 : 1, TraceLane); else PTC_TRACE(1, TraceLane); }

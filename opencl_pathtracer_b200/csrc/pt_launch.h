@@ -7,7 +7,8 @@ namespace ptc
 {
 struct LaunchCfg
 {
-    int traverseGrid;  // persistent extend / connect CTAs (multiple of the SM count)
+    int traverseGrid;  // persistent extend CTAs (multiple of the SM count)
+    int connectGrid;   // persistent connect CTAs
     int streamGrid;    // grid of the streaming stages (generate / shade / accumulate)
     uint32_t refillMin;  // idle lanes of a warp that trigger a refill from the work cursor (1..32)
     int stackDepth;      // traversal stack entries per thread (BVH depth + 1, at most kStackDepth)
@@ -15,7 +16,7 @@ struct LaunchCfg
     bool count;          // per-ray work counters + the two 5000-bin histograms (PARITY always; FAST with PTC_FLAG_WORK_COUNTERS)
 };
 
-int traverse_ctas_per_sm(bool fast, bool wide, int stackDepth);
+int traverse_ctas_per_sm(bool fast, bool wide, int stackDepth, bool any);  // resident CTAs per SM of the extend (any = false) / connect kernel
 
 void launch_reset(cudaStream_t s, Counters *cn, uint32_t nPaths);
 void launch_generate(cudaStream_t s, const LaunchCfg &lc, const FrameParams &fp, const Camera &cam, const PathState &st);

@@ -180,6 +180,8 @@ struct TraceLane
 
     // the interface k_trace drives (shared with WideLane, pt_wide.cuh)
     typedef uint32_t StackT;
+    static constexpr int kBoxesPerNodeStep = 2;
+    static constexpr int kMinCtasAny = 8;
     static constexpr int kMinCtas = 8;  // 64 registers (PARITY connect spills 16 B): 53.7 -> 58.9 Msamples/s against an unbounded 79 registers / 6 CTAs
     __device__ __forceinline__ void reset() { cur = kIdle; nb = nt = 0; found = false; hitTri = -1; }
     __device__ __forceinline__ bool idle() const { return cur == kIdle; }

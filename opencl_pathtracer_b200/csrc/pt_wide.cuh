@@ -60,10 +60,15 @@ struct WideLane
     bool found;
 
     typedef uint2 StackT;
+    static constexpr int kBoxesPerNodeStep = 8;
 #ifndef PTC_WIDE_MIN_CTAS
 #define PTC_WIDE_MIN_CTAS 8
 #endif
     static constexpr int kMinCtas = PTC_WIDE_MIN_CTAS;  // 64 registers: 8 CTAs of 4 warps per SM
+#ifndef PTC_WIDE_MIN_CTAS_ANY
+#define PTC_WIDE_MIN_CTAS_ANY 8
+#endif
+    static constexpr int kMinCtasAny = PTC_WIDE_MIN_CTAS_ANY;  // connect (its staging holds a light record and a shading normal besides the lane)
     __device__ __forceinline__ void reset() { sp = -1; gy = ty = 0; nb = nt = 0; found = false; hitTri = -1; }
     __device__ __forceinline__ bool idle() const { return sp < 0; }
     __device__ __forceinline__ void set_idle() { sp = -1; }
@@ -145,19 +150,17 @@ __device__ __forceinline__ void wide_normalise(WideLane &L, const uint2 *stk, co
     L.sp -= pop ? 1 : 0;
 }
 
-__device__ __forceinline__ float q8(uint32_t w, int j) { return (float)((w >> (8 * j)) & 0xffu); }
-
-#ifdef PTC_Q8_HALF
 // Quantised planes without the conversion pipe: a byte q placed under the half-precision exponent 0x64 is the half 1024 + q
 // (exact), two bytes per PRMT; half -> float is exact as well and runs beside the FMAs. The 1024 is folded into the constant
-// term of t(q) = q * a + b. (48 I2F.U8 per node visit -> 24 PRMT + 48 HADD2.F32.)
+// term of t(q) = q * a + b. 48 I2F.U8 per node visit (quarter rate, the busiest pipe of round 1's captures: XU 66-72 %) became
+// 24 PRMT + 48 HADD2.F32: +1.4 % samples/s on the 262 k-triangle atrium, +1.8 % on the 10 M-triangle terrain, +11 % on the
+// 1 M-triangle atrium (profiles/r02_sweeps.txt).
 __device__ __forceinline__ void q8x4(uint32_t w, float &f0, float &f1, float &f2, float &f3)
 {
     const uint32_t h01 = __byte_perm(w, 0x64646464u, 0x4140), h23 = __byte_perm(w, 0x64646464u, 0x4342);
     const float2 a = __half22float2(*reinterpret_cast<const __half2 *>(&h01)), b = __half22float2(*reinterpret_cast<const __half2 *>(&h23));
     f0 = a.x; f1 = a.y; f2 = b.x; f3 = b.y;
 }
-#endif
 
 // One node visit: take the nearest unvisited child of the current group, postpone its siblings, test its 8 children.
 template <bool FAST>
@@ -191,17 +194,11 @@ __device__ __forceinline__ void lane_node_step(WideLane &L, const SceneDev &sc, 
     const float by = (__uint_as_float(n0.y) - L.r.oy) * L.r.iy;
     const float bz = (__uint_as_float(n0.z) - L.r.oz) * L.r.iz;
     const float kPad = 4.76837158e-7f;
-#ifdef PTC_Q8_HALF
     // planes arrive as 1024 + q: the constant term takes the -1024 * a and is padded after that
     const float cx = __fmaf_rn(-1024.f, adx, bx), cy = __fmaf_rn(-1024.f, ady, by), cz = __fmaf_rn(-1024.f, adz, bz);
     const float bxl = __fmaf_rn(-fabsf(cx), kPad, cx), bxh = __fmaf_rn(fabsf(cx), kPad, cx);
     const float byl = __fmaf_rn(-fabsf(cy), kPad, cy), byh = __fmaf_rn(fabsf(cy), kPad, cy);
     const float bzl = __fmaf_rn(-fabsf(cz), kPad, cz), bzh = __fmaf_rn(fabsf(cz), kPad, cz);
-#else
-    const float bxl = __fmaf_rn(-fabsf(bx), kPad, bx), bxh = __fmaf_rn(fabsf(bx), kPad, bx);
-    const float byl = __fmaf_rn(-fabsf(by), kPad, by), byh = __fmaf_rn(fabsf(by), kPad, by);
-    const float bzl = __fmaf_rn(-fabsf(bz), kPad, bz), bzh = __fmaf_rn(fabsf(bz), kPad, bz);
-#endif
     // entry planes are the low ones along axes the ray travels up, the high ones otherwise
     const bool nx = L.r.ix < 0, ny = L.r.iy < 0, nz = L.r.iz < 0;
     // words: n2 = qlo.x[0] qlo.x[1] qlo.y[0] qlo.y[1]; n3 = qlo.z[0] qlo.z[1] qhi.x[0] qhi.x[1]; n4 = qhi.y[0] qhi.y[1] qhi.z[0] qhi.z[1]
@@ -214,24 +211,16 @@ __device__ __forceinline__ void lane_node_step(WideLane &L, const SceneDev &sc, 
         const uint32_t ex = nx ? hix : lox, fx = nx ? lox : hix;
         const uint32_t ey = ny ? hiy : loy, fy = ny ? loy : hiy;
         const uint32_t ez = nz ? hiz : loz, fz = nz ? loz : hiz;
-#ifdef PTC_Q8_HALF
         float qex[4], qfx[4], qey[4], qfy[4], qez[4], qfz[4];
         q8x4(ex, qex[0], qex[1], qex[2], qex[3]); q8x4(fx, qfx[0], qfx[1], qfx[2], qfx[3]);
         q8x4(ey, qey[0], qey[1], qey[2], qey[3]); q8x4(fy, qfy[0], qfy[1], qfy[2], qfy[3]);
         q8x4(ez, qez[0], qez[1], qez[2], qez[3]); q8x4(fz, qfz[0], qfz[1], qfz[2], qfz[3]);
-#endif
 #pragma unroll
         for (int j = 0; j < 4; j++)
         {
-#ifdef PTC_Q8_HALF
             const float tex = __fmaf_rn(qex[j], adx, bxl), tfx = __fmaf_rn(qfx[j], adx, bxh);
             const float tey = __fmaf_rn(qey[j], ady, byl), tfy = __fmaf_rn(qfy[j], ady, byh);
             const float tez = __fmaf_rn(qez[j], adz, bzl), tfz = __fmaf_rn(qfz[j], adz, bzh);
-#else
-            const float tex = __fmaf_rn(q8(ex, j), adx, bxl), tfx = __fmaf_rn(q8(fx, j), adx, bxh);
-            const float tey = __fmaf_rn(q8(ey, j), ady, byl), tfy = __fmaf_rn(q8(fy, j), ady, byh);
-            const float tez = __fmaf_rn(q8(ez, j), adz, bzl), tfz = __fmaf_rn(q8(fz, j), adz, bzh);
-#endif
             const float tEnter = fmaxf(fmaxf(tex, tey), fmaxf(tez, 0.f));
             const float tExit = fminf(fminf(tfx, tfy), fminf(tfz, L.tmax));
             if (tEnter <= tExit) slotHit |= 1u << (4 * h + j);

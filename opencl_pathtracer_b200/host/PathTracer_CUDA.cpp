@@ -56,7 +56,21 @@ void CUDA_SetupContext(GlobalVars &globalVars, Sampler sampler)
     cfg.flags = g_options.flags;
     if (globalVars.superSampling) cfg.flags &= ~(uint32_t)PTC_FLAG_NO_VARIANCE;  // the criterion reads imageV
     globalVars.sampler = sampler;
-    check(ptc_create(&cfg, &g_ctx), "CUDA_SetupContext");
+    int nDev = g_options.nDevices;
+    if (nDev < 0) nDev = ptc_device_count();
+    if (nDev > 16) nDev = 16;
+    if (nDev > 1)
+    {
+        int32_t devs[16];
+        for (int i = 0; i < nDev; i++) devs[i] = g_options.devices[i];
+        if (globalVars.superSampling) throw std::runtime_error("CUDA_SetupContext : superSampling reads the running variance image, which several devices cannot share");
+        check(ptc_create_multi(&cfg, devs, (uint32_t)nDev, &g_ctx), "CUDA_SetupContext");
+    }
+    else
+    {
+        if (nDev == 1) cfg.device = g_options.devices[0];
+        check(ptc_create(&cfg, &g_ctx), "CUDA_SetupContext");
+    }
     // reference Controleur/PathTracer_OpenCL.cpp:311 `-D SUPER_SAMPLING`. Its table file Kernel/X2inv.cl is empty (the option
     // cannot compile there); the library's own 95 % chi-square quantiles stand in, 4096 entries
     if (globalVars.superSampling) check(ptc_set_supersampling(g_ctx, nullptr, 4096), "CUDA_SetupContext");

@@ -21,6 +21,11 @@ void CUDA_RunKernel(GlobalVars &globalVars, bool (*UpdateWindowFunc)(void), uint
 struct CUDA_Options
 {
     int device = 0;
+    // Several GPUs of the box behind the same three calls (ptc_create_multi): nDevices > 1 selects devices[0 .. nDevices); -1 = every
+    // CUDA device present. The devices render iteration ranges (or pixel stripes when a read-back interval holds fewer iterations
+    // than there are devices); CUDA_RunKernel's read-backs sum them with an NCCL reduce.
+    int nDevices = 0;
+    int devices[16] = {0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15};
     int mode = 0;                 // ptc_mode
     uint readBackEvery = 1;       // iterations between read-back + UpdateWindowFunc (the last iteration always reads back)
     uint iterationsPerBatch = 0;  // 0 = auto

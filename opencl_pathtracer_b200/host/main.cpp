@@ -3,6 +3,7 @@
 // instead of being hard-coded, and the importer is the procedural one).
 //
 // usage: pathtracer_alone [scene] [width] [height] [numImages] [rayMaxDepth] [sampler 0|1|2] [mode 0|1] [save 0|1] [outdir] [exportdir]
+//   environment: PATHTRACER_DEVICES = n (the first n CUDA devices) or "all": one context over several GPUs (ptc_create_multi)
 //   scene      a procedural scene name (cornell, gallery, atrium[:n], terrain[:n]) or file:<folder> = the .pth triple
 //              in <folder> (PathTracer_FileImporter.h, what the reference's PathTracerFileImporter reads)
 //   exportdir  if given, the imported scene is written there as sizes.pth / pointers.pth / textureData.pth before
@@ -29,6 +30,7 @@ int main(int argc, char **argv)
     bool saveRenderedImages = argc > 8 ? std::atoi(argv[8]) != 0 : true;
     if (argc > 9) PathTracerNS::PathTracerDialog::exportFolderPath = argv[9];
     opt.readBackEvery = saveRenderedImages ? numImageToRender : 1;  // one picture at the end
+    if (const char *d = std::getenv("PATHTRACER_DEVICES")) opt.nDevices = std::strcmp(d, "all") == 0 ? -1 : std::atoi(d);
     PathTracerNS::CUDA_SetOptions(opt);
 
     const bool exportScene = argc > 10;

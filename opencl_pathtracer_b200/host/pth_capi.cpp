@@ -1,5 +1,7 @@
-// pth_capi.cpp — plain-C entry points over the host-side mirror (importer, BVH builder, controller) for the
-// Python binding, the tests and bench.py. Not part of the device boundary (that is include/pathtracer_cuda.h).
+// pth_capi.cpp — plain-C entry points over the controller side of the host mirror (PathTracer_Main and the CUDA_* shims) for the
+// Python binding, the tests and bench.py. The scene side (importers, BVH builder) is pth_scene_capi.cpp / libpathtracer_scene.so.
+// Not part of the device boundary (that is include/pathtracer_cuda.h).
+#include <chrono>
 #include <cstring>
 #include <stdexcept>
 #include <string>
@@ -8,155 +10,22 @@
 #include "PathTracer_FileImporter.h"
 #include "PathTracer_ProceduralImporter.h"
 #include "pathtracer_cuda.h"
+#include "pth_scene.h"
 
 using namespace PathTracerNS;
 
-#define PTH_API extern "C" __attribute__((visibility("default")))
-
-struct pth_scene
-{
-    GlobalVars gv;
-    std::string err;
-};
-
-struct pth_scene_info
-{
-    uint32_t bvhSize, bvhMaxDepth, triangulationSize, lightsSize, materiauxSize, texturesSize, texturesDataSize, imageWidth, imageHeight;
-    uint32_t reserved;
-    const void *bvh, *triangulation, *lights, *materiaux, *textures, *texturesData, *sky;
-    float camera[16];  // position, direction, right, up
-};
-
 static thread_local std::string g_err;
-PTH_API const char *pth_last_error() { return g_err.c_str(); }
-
-// Runs the procedural importer (no BVH yet). Returns NULL on failure.
-PTH_API pth_scene *pth_scene_create(const char *name, uint32_t seed, uint32_t width, uint32_t height, int loadSky)
-{
-    pth_scene *s = new pth_scene();
-    try
-    {
-        PathTracerProceduralImporter imp(name, seed);
-        imp.Initialize(s->gv);
-        imp.Import(width, height, loadSky != 0);
-    }
-    catch (std::exception const &e)
-    {
-        g_err = e.what();
-        delete s;
-        return nullptr;
-    }
-    return s;
-}
-
-// PathTracerFileImporter::Import: a scene from sizes.pth / pointers.pth / textureData.pth in `folder` (no BVH yet).
-PTH_API pth_scene *pth_scene_import(const char *folder, uint32_t width, uint32_t height, int loadSky)
-{
-    pth_scene *s = new pth_scene();
-    try
-    {
-        PathTracerFileImporter imp(folder);
-        imp.Initialize(s->gv);
-        imp.Import(width, height, loadSky != 0);
-    }
-    catch (std::exception const &e)
-    {
-        g_err = e.what();
-        GlobalVars &g = s->gv;
-        delete[] g.triangulation; delete[] g.lights; delete[] g.materiaux; delete[] g.textures; delete[] g.texturesData;
-        delete s;
-        return nullptr;
-    }
-    return s;
-}
-
-// PathTracerFileImporter::Export of the scene as it is now (after pth_scene_build_bvh: triangles in BVH order).
-PTH_API int pth_scene_export(pth_scene *s, const char *folder)
-{
-    try
-    {
-        PathTracerFileImporter exp(folder);
-        exp.Initialize(s->gv);
-        exp.Export();
-    }
-    catch (std::exception const &e)
-    {
-        g_err = e.what();
-        return 1;
-    }
-    return 0;
-}
-
-// BVH_Create of this repository (host/PathTracer_BVH.cpp). Permutes the triangles.
-PTH_API int pth_scene_build_bvh(pth_scene *s)
-{
-    try
-    {
-        delete[] s->gv.bvh;
-        s->gv.bvh = nullptr;
-        BVH_Create(s->gv);
-    }
-    catch (std::exception const &e)
-    {
-        g_err = e.what();
-        return 1;
-    }
-    return 0;
-}
-
-// Installs an externally built BVH (e.g. the reference builder's output from oracle/_ref) — nodes are copied.
-PTH_API int pth_scene_set_bvh(pth_scene *s, const void *nodes, uint32_t bvhSize, uint32_t bvhMaxDepth)
-{
-    delete[] s->gv.bvh;
-    s->gv.bvh = new Node[bvhSize ? bvhSize : 1];
-    std::memcpy((void *)s->gv.bvh, nodes, sizeof(Node) * (size_t)bvhSize);
-    s->gv.bvhSize = bvhSize;
-    s->gv.bvhMaxDepth = bvhMaxDepth;
-    return 0;
-}
-
-PTH_API void pth_scene_get_info(pth_scene *s, pth_scene_info *o)
-{
-    const GlobalVars &g = s->gv;
-    o->bvhSize = g.bvhSize; o->bvhMaxDepth = g.bvhMaxDepth; o->triangulationSize = g.triangulationSize; o->lightsSize = g.lightsSize;
-    o->materiauxSize = g.materiauxSize; o->texturesSize = g.texturesSize; o->texturesDataSize = g.texturesDataSize;
-    o->imageWidth = g.imageWidth; o->imageHeight = g.imageHeight; o->reserved = 0;
-    o->bvh = g.bvh; o->triangulation = g.triangulation; o->lights = g.lights; o->materiaux = g.materiaux; o->textures = g.textures;
-    o->texturesData = g.texturesData; o->sky = &g.sky;
-    std::memcpy(o->camera + 0, &g.cameraPosition, 16);
-    std::memcpy(o->camera + 4, &g.cameraDirection, 16);
-    std::memcpy(o->camera + 8, &g.cameraRight, 16);
-    std::memcpy(o->camera + 12, &g.cameraUp, 16);
-}
-
-PTH_API void pth_scene_get_view(pth_scene *s, ptc_scene_view *v)
-{
-    const GlobalVars &g = s->gv;
-    std::memset(v, 0, sizeof(*v));
-    v->struct_size = sizeof(*v);
-    v->bvh_size = g.bvhSize; v->triangulation_size = g.triangulationSize; v->lights_size = g.lightsSize; v->materiaux_size = g.materiauxSize;
-    v->textures_size = g.texturesSize; v->textures_data_size = g.texturesDataSize;
-    v->bvh = g.bvh; v->triangulation = g.triangulation; v->lights = g.lights; v->materiaux = g.materiaux; v->textures = g.textures;
-    v->textures_data = g.texturesData; v->sky = &g.sky;
-    v->camera_position = g.cameraPosition; v->camera_direction = g.cameraDirection; v->camera_right = g.cameraRight; v->camera_up = g.cameraUp;
-}
-
-PTH_API void pth_scene_free(pth_scene *s)
-{
-    if (!s) return;
-    GlobalVars &g = s->gv;
-    delete[] g.bvh; delete[] g.triangulation; delete[] g.lights; delete[] g.materiaux; delete[] g.textures; delete[] g.texturesData;
-    delete s;
-}
+PTH_API const char *pth_host_last_error() { return g_err.c_str(); }
 
 // The whole reference pipeline through PathTracer_Main (importer -> BVH_Create -> CUDA_* shims -> statistics),
 // i.e. what Alone/main.cpp does, with the results copied out. Any output pointer may be NULL.
 PTH_API int pth_main(const char *scene, uint32_t seed, uint32_t width, uint32_t height, uint32_t numImagesToRender, int saveRenderedImages,
-                     int loadSky, int sampler, uint32_t rayMaxDepth, int mode, uint32_t readBackEvery, int device, const char *exportFolder,
+                     int loadSky, int sampler, uint32_t rayMaxDepth, int mode, uint32_t readBackEvery, int device, int nDevices, const char *exportFolder,
                      float *imageColor, float *imageRayNb, uint32_t *rayDepths, uint32_t *rayBbx, uint32_t *rayTri)
 {
     CUDA_Options opt;
     opt.device = device;
+    opt.nDevices = nDevices;
     opt.mode = mode;
     opt.readBackEvery = readBackEvery ? readBackEvery : 1;
     CUDA_SetOptions(opt);
@@ -178,4 +47,39 @@ PTH_API int pth_main(const char *scene, uint32_t seed, uint32_t width, uint32_t 
     }
     PathTracer_KeepResults(false);
     return ok ? 0 : 1;
+}
+
+// The drop-in DEFAULT, timed: what a maintainer gets from INTEGRATION.md's three-line change with CUDA_Options{} untouched —
+// PARITY arithmetic, read-back of imageColor + imageRayNb and the callback after EVERY iteration, as the reference's loop does
+// (Controleur/PathTracer_OpenCL.cpp:76-107) — on a scene that is already imported and has its BVH. times = {setup + upload,
+// path tracing, read-back, display} in milliseconds as CUDA_RunKernel reports them. Returns 0 on success.
+PTH_API int pth_run_default(pth_scene *s, uint32_t numImagesToRender, uint32_t rayMaxDepth, double times[4], uint32_t *rayDepths)
+{
+    GlobalVars &g = s->gv;
+    const size_t n = (size_t)g.imageWidth * g.imageHeight;
+    RGBAColor *color = new RGBAColor[n];
+    float *nb = new float[n];
+    uint *depths = new uint[rayMaxDepth + 1](), *bbx = new uint[MAX_INTERSETCION_NUMBER](), *tri = new uint[MAX_INTERSETCION_NUMBER]();
+    g.imageColor = color; g.imageRayNb = nb; g.rayDepths = depths; g.rayIntersectedBBx = bbx; g.rayIntersectedTri = tri;
+    g.rayMaxDepth = rayMaxDepth;
+    int rc = 0;
+    try
+    {
+        CUDA_SetOptions(CUDA_Options{});
+        using clock = std::chrono::steady_clock;
+        const clock::time_point t0 = clock::now();
+        CUDA_SetupContext(g, JITTERED);
+        CUDA_InitializeMemory(g);
+        times[0] = std::chrono::duration<double, std::milli>(clock::now() - t0).count();
+        CUDA_RunKernel(g, nullptr, numImagesToRender, &times[1], &times[2], &times[3]);
+        if (rayDepths) std::memcpy(rayDepths, depths, sizeof(uint) * (rayMaxDepth + 1));
+    }
+    catch (std::exception const &e)
+    {
+        g_err = e.what();
+        rc = 1;
+    }
+    delete[] color; delete[] nb; delete[] depths; delete[] bbx; delete[] tri;
+    g.imageColor = nullptr; g.imageRayNb = nullptr; g.rayDepths = nullptr; g.rayIntersectedBBx = nullptr; g.rayIntersectedTri = nullptr;
+    return rc;
 }

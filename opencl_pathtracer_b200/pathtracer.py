@@ -20,7 +20,9 @@ class PathTracerError(RuntimeError):
 
 class PathTracerCUDA:
     def __init__(self, width, height, ray_max_depth=10, sampler=N.SAMPLER_JITTERED, mode=N.MODE_PARITY, device=0,
-                 iterations_per_batch=0, flags=0, stream=None):
+                 iterations_per_batch=0, flags=0, stream=None, devices=None):
+        """devices: a list of CUDA ordinals = ONE context over several GPUs (ptc_create_multi): iteration ranges (or pixel
+        stripes for calls with fewer iterations than devices) per GPU, accumulators summed by NCCL when they are read."""
         self._lib = N.cuda_lib()
         cfg = N.Config()
         cfg.struct_size = C.sizeof(N.Config)
@@ -29,12 +31,25 @@ class PathTracerCUDA:
         cfg.iterations_per_batch, cfg.flags = iterations_per_batch, flags
         cfg.stream = stream
         h = C.c_void_p()
-        rc = self._lib.ptc_create(C.byref(cfg), C.byref(h))
+        if devices is not None:
+            arr = (C.c_int32 * len(devices))(*devices)
+            rc = self._lib.ptc_create_multi(C.byref(cfg), arr, len(devices), C.byref(h))
+        else:
+            rc = self._lib.ptc_create(C.byref(cfg), C.byref(h))
         if rc != N.PTC_OK:
             raise PathTracerError(rc, self._lib.ptc_last_error(None).decode())
         self._h = h
         self.width, self.height, self.ray_max_depth = width, height, ray_max_depth
         self.n_pixels = width * height
+
+    def devices(self):
+        a = (C.c_int32 * 64)()
+        n = self._lib.ptc_context_devices(self._h, a, 64)
+        return list(a[:n])
+
+    def reduce_kind(self):
+        """'nccl' / 'p2p' for a multi-device context, 'none' for one device."""
+        return self._lib.ptc_multi_reduce_kind(self._h).decode()
 
     def _ck(self, rc):
         if rc != N.PTC_OK:
@@ -194,7 +209,7 @@ class PathTracerCUDA:
 
 
 def PathTracer_Main(scene, image_width, image_height, numImagesToRender, saveRenderedImages=False, loadSky=False, sampler=0, rayDepth=10,
-                    mode=N.MODE_PARITY, readBackEvery=0, device=0, exportFolder=None, seed=20261104):
+                    mode=N.MODE_PARITY, readBackEvery=0, device=0, exportFolder=None, seed=20261104, nDevices=0):
     """The reference's whole host pipeline (Controleur/PathTracer.cpp:25-110) through the C++ controller of
     host/PathTracer.cpp: importer -> BVH_Create -> CUDA_SetupContext / CUDA_InitializeMemory / CUDA_RunKernel.
     Returns dict(imageColor, imageRayNb, rayDepths, rayIntersectedBBx, rayIntersectedTri)."""
@@ -205,8 +220,20 @@ def PathTracer_Main(scene, image_width, image_height, numImagesToRender, saveRen
     b = np.zeros(N.MAX_INTERSECTION_NUMBER, np.uint32)
     t = np.zeros(N.MAX_INTERSECTION_NUMBER, np.uint32)
     rc = L.pth_main(scene.encode(), seed, image_width, image_height, numImagesToRender, int(saveRenderedImages), int(loadSky), sampler,
-                    rayDepth, mode, readBackEvery or numImagesToRender, device, exportFolder.encode() if exportFolder else None,
+                    rayDepth, mode, readBackEvery or numImagesToRender, device, nDevices, exportFolder.encode() if exportFolder else None,
                     color.ctypes.data, nb.ctypes.data, d.ctypes.data, b.ctypes.data, t.ctypes.data)
     if rc != 0:
         raise RuntimeError("PathTracer_Main failed (see stderr)")
     return {"imageColor": color, "imageRayNb": nb, "rayDepths": d, "rayIntersectedBBx": b, "rayIntersectedTri": t}
+
+
+def run_default_drop_in(scene, numImagesToRender, rayDepth=10):
+    """CUDA_SetupContext / CUDA_InitializeMemory / CUDA_RunKernel with CUDA_Options{} untouched (PARITY, read-back and callback
+    after every iteration: the reference's loop, Controleur/PathTracer_OpenCL.cpp:76-107) on an imported scene with its BVH.
+    Returns dict(setup_ms, trace_ms, readback_ms, display_ms, paths)."""
+    L = N.host_lib()
+    t = (C.c_double * 4)()
+    d = np.zeros(rayDepth + 1, np.uint32)
+    if L.pth_run_default(scene._h, numImagesToRender, rayDepth, t, d.ctypes.data) != 0:
+        raise RuntimeError(L.pth_host_last_error().decode())
+    return {"setup_ms": t[0], "trace_ms": t[1], "readback_ms": t[2], "display_ms": t[3], "paths": int(d.sum())}

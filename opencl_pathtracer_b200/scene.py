@@ -59,7 +59,7 @@ class Scene:
     """A GlobalVars-like scene produced by PathTracerProceduralImporter (host/PathTracer_ProceduralImporter.h)."""
 
     def __init__(self, name, width, height, seed=20261104, load_sky=False, build_bvh=True):
-        self._lib = N.host_lib()
+        self._lib = N.scene_lib()
         self._h = self._lib.pth_scene_create(name.encode(), seed, width, height, 1 if load_sky else 0)
         if not self._h:
             raise RuntimeError(self._lib.pth_last_error().decode())
@@ -72,7 +72,7 @@ class Scene:
         """A scene from the reference's file triple sizes.pth / pointers.pth / textureData.pth (host/PathTracer_FileImporter.h,
         counterpart of reference Controleur/PathTracer_FileImporter.cpp:67-146)."""
         self = cls.__new__(cls)
-        self._lib = N.host_lib()
+        self._lib = N.scene_lib()
         self._h = self._lib.pth_scene_import(str(folder).encode(), width, height, 1 if load_sky else 0)
         if not self._h:
             raise RuntimeError(self._lib.pth_last_error().decode())

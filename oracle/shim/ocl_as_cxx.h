@@ -14,7 +14,15 @@
 //   length(v)            = sqrtf(dot(v,v))
 //   normalize(v)         = v / length(v)                                (4 IEEE divides)
 //   cross(a,b)           = 3-lane, w = 0
-//   sqrt/cos/sin/exp     = sqrtf / cosf / sinf / expf of the host libm
+//   sqrt/exp             = sqrtf / expf of the host libm (sqrtf is IEEE; exp is only reached from dead code)
+//   cos/sin              = the CORRECTLY ROUNDED single-precision value: evaluated in double by the host libm and rounded once.
+//                          OpenCL leaves the accuracy of cos/sin to the implementation (the Intel CPU runtime the reference ran
+//                          on is not here to ask); the correctly rounded value is the one definition within every conforming
+//                          error budget that a second implementation can reproduce bit for bit (the CUDA kernels evaluate it
+//                          the same way, pt_shade.cuh concentric_sample_disk). With glibc's cosf/sinf (< 1 ulp, not always
+//                          the nearest float) 1.5 % of the 1080p pixels of BASELINE.json configs[2] left the 1e-3 band through a
+//                          last-bit direction difference after a diffuse bounce — every one of 800 walked offenders was that class
+//                          (round 2, tests/test_gpu_configs.py) — which hid the rest of the pipeline behind a tolerance.
 //   fmax/fmin/max/min    = IEEE compare-select on floats
 // Build flags that go with it: -O2 -ffp-contract=off -fno-fast-math -fwrapv.
 
@@ -24,8 +32,8 @@
 
 // ---- scalar helpers -------------------------------------------------------------------
 static inline float sqrt(float x) { return ::sqrtf(x); }
-static inline float cos(float x) { return ::cosf(x); }
-static inline float sin(float x) { return ::sinf(x); }
+static inline float cos(float x) { return (float)::cos((double)x); }
+static inline float sin(float x) { return (float)::sin((double)x); }
 static inline float exp(float x) { return ::expf(x); }
 static inline float fabs(float x) { return ::fabsf(x); }
 static inline float fmax(float a, float b) { return ::fmaxf(a, b); }

@@ -91,14 +91,67 @@ def test_iteration_range_partition():
         iteration_range(2, 2, 0, 4)
 
 
-def test_bmp_writer(tmp_path):
-    """PathTracerDialog::PaintWindow writes NNN.bmp with the reference's conversion (Alone/PathTracer_bitmap.cpp:237-286)."""
+def test_alone_fails_loudly_without_a_device(tmp_path):
+    """Without a GPU the stand-alone front-end must exit with an error (exit code 1), never render on the CPU.
+    (With a device present this test has nothing to check: the picture it writes is tested by test_alone_writes_the_reference_bmp.)"""
     exe = os.path.join(N.LIB_DIR, "pathtracer_alone")
     assert os.path.exists(exe)
-    # without a GPU the stand-alone front-end must fail loudly (exit code 1), never render on the CPU
     if N.cuda_lib().ptc_device_count() == 0:
         r = subprocess.run([exe, "cornell", "16", "16", "1", "2", "0", "0", "1", str(tmp_path) + "/"], capture_output=True, text=True)
         assert r.returncode == 1 and "ERROR" in r.stderr
+
+
+def bmp_bytes(color, ray_nb):
+    """ConvertRGBAToBMPBuffer + SaveBMP of the reference (Alone/PathTracer_bitmap.cpp:237-286, :146-201) restated in numpy: rows top to
+    bottom as stored, B G R per pixel, rows padded to 4 bytes, value = (int) min(sum * 255.f / count, 255.f) in float32, a negative
+    red sum marks the pixel pure red; 14-byte file header + 40-byte info header (24 bit, 0x0ec4 pixels per metre)."""
+    import struct
+
+    import numpy as np
+    h, w = ray_nb.shape
+    c = color.reshape(h, w, 4).astype(np.float32)
+    n = ray_nb.astype(np.float32)[..., None]
+    with np.errstate(divide="ignore", invalid="ignore"):
+        v = np.minimum(c[..., :3] * np.float32(255.0) / n, np.float32(255.0))
+    v = np.nan_to_num(v, nan=0.0).astype(np.int32).astype(np.uint8)
+    neg = c[..., 0] < 0
+    v[neg] = (255, 0, 0)
+    psw = (3 * w + 3) & ~3
+    rows = np.zeros((h, psw), np.uint8)
+    rows[:, :3 * w] = v[..., ::-1].reshape(h, 3 * w)
+    hdr = b"BM" + struct.pack("<IHHI", 54 + psw * h, 0, 0, 0x36) + struct.pack("<IiiHHIIiiII", 40, w, h, 1, 24, 0, 0, 0x0ec4, 0x0ec4, 0, 0)
+    return hdr + rows.tobytes()
+
+
+@pytest.mark.gpu
+def test_alone_writes_the_reference_bmp(tmp_path):
+    """N1's host half on a device: the headless front-end (counterpart of reference Alone/main.cpp:9-34) renders Cornell 66x48, 2
+    iterations, PARITY, and PathTracerDialog::PaintWindow saves the picture. The file must equal, byte for byte, the reference's
+    conversion (restated above) of the accumulators the library itself returns for those iterations; against the ORACLE's
+    accumulators (the reference kernel on the CPU) at most a last-bit handful of channel values may differ by one."""
+    import numpy as np
+    import opencl_pathtracer_b200 as pt
+    from oracle import ptref
+    exe = os.path.join(N.LIB_DIR, "pathtracer_alone")
+    w, h, spp, depth = 66, 48, 2, 10  # 66 * 3 = 198 bytes per row: 2 bytes of padding
+    out = str(tmp_path) + "/"
+    r = subprocess.run([exe, "cornell", str(w), str(h), str(spp), str(depth), "0", "0", "1", out], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    files = sorted(f for f in os.listdir(out) if f.endswith(".bmp"))
+    assert len(files) == 1, files
+    got = open(os.path.join(out, files[0]), "rb").read()
+    sc = pt.Scene("cornell", w, h)
+    with pt.PathTracerCUDA(w, h, ray_max_depth=depth, mode=pt.MODE_PARITY) as ctx:
+        ctx.upload(sc)
+        ctx.render(0, spp)
+        color, nb = ctx.read_image()
+    assert got == bmp_bytes(color, nb), "the saved picture is not the reference's conversion of the library's accumulators"
+    if ptref.available():
+        acc = ptref.render(sc, w, h, depth, 0, 0, spp)
+        ref = bmp_bytes(acc["imageColor"], acc["imageRayNb"])
+        assert got[:54] == ref[:54]
+        a, b = np.frombuffer(got[54:], np.uint8).astype(np.int16), np.frombuffer(ref[54:], np.uint8).astype(np.int16)
+        assert np.abs(a - b).max() <= 1 and (a != b).mean() <= 1e-3, "picture differs from the oracle's: %g of the bytes" % (a != b).mean()
 
 
 def test_area_light_record_packing(tmp_path):
