@@ -150,6 +150,10 @@ typedef struct ptc_counters
     uint64_t scene_bytes_triangles; /* device bytes of the intersection records */
     uint64_t ext_box_tests;         /* share of box_tests / triangle_tests spent by closest-hit traversals */
     uint64_t ext_triangle_tests;
+    /* CHECKED build only (libpathtracer_cuda.so compiled with -DPTC_CHECKED, ptc_version() ends in "checked"): bit c set = bounds check c
+       of the kernels failed (queue entries, node / triangle / material / texture / texel indices, stack levels, target pixels:
+       csrc/pt_device.cuh FaultCode); code / value / bound of the first failure. Always 0 in the normal build. */
+    uint32_t faults, fault_code, fault_value, fault_bound;
 } ptc_counters;
 
 /* Device pointers of the accumulators, for zero-copy collectives (NCCL reduce of per-GPU images). */

@@ -45,7 +45,8 @@ class Counters(C.Structure):
                 ("triangle_tests", C.c_uint64), ("kernel_launches", C.c_uint64), ("ms_generate", C.c_double), ("ms_extend", C.c_double),
                 ("ms_connect", C.c_double), ("ms_shade", C.c_double), ("ms_accumulate", C.c_double), ("launches_extend", C.c_uint64),
                 ("launches_connect", C.c_uint64), ("scene_bytes_nodes", C.c_uint64), ("scene_bytes_triangles", C.c_uint64),
-                ("ext_box_tests", C.c_uint64), ("ext_triangle_tests", C.c_uint64)]
+                ("ext_box_tests", C.c_uint64), ("ext_triangle_tests", C.c_uint64),
+                ("faults", C.c_uint32), ("fault_code", C.c_uint32), ("fault_value", C.c_uint32), ("fault_bound", C.c_uint32)]
 
 
 class DeviceBuffers(C.Structure):

@@ -5,12 +5,14 @@
   libpathtracer_scene.so  scene side of the host mirror of the reference interface (importers, BVH builder) + pth_scene_*;
                           does not depend on the CUDA library
   libpathtracer_host.so   controller side (PathTracer_Main, CUDA_* shims, headless dialog) + pth_main / pth_run_default
+  _lib_checked/           the same three libraries with the device code compiled -DPTC_CHECKED (bounds checks, ptc_counters.faults)
   pathtracer_alone        headless stand-alone front-end (counterpart of the reference's Alone/main.cpp)
 
 nvcc cross-compiles for sm_100a without a GPU. Bit-exact arithmetic: -fmad=false on the device,
 -ffp-contract=off on the host.
 """
 import os
+import shutil
 import subprocess
 import sys
 
@@ -40,9 +42,9 @@ def _run(cmd, verbose):
     subprocess.check_call(cmd)
 
 
-def build(verbose=False, force=False):
-    os.makedirs(LIB, exist_ok=True)
-    cuda_so = os.path.join(LIB, "libpathtracer_cuda.so")
+def _build_cuda(out_dir, extra, verbose, force):
+    os.makedirs(out_dir, exist_ok=True)
+    cuda_so = os.path.join(out_dir, "libpathtracer_cuda.so")
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))] + \
               [os.path.join(INC, f) for f in os.listdir(INC)]
     cu = [os.path.join(CSRC, "pt_kernels.cu"), os.path.join(CSRC, "pt_wide_build.cu"), os.path.join(CSRC, "pt_lbvh.cu"),
@@ -50,12 +52,17 @@ def build(verbose=False, force=False):
     if force or _newer(cuda_so, cu + headers + [__file__]):
         objs = []
         for src in cu:
-            obj = os.path.join(LIB, os.path.basename(src) + ".o")
-            _run(["nvcc"] + NVCC_FLAGS + ["-c", src, "-o", obj], verbose)
+            obj = os.path.join(out_dir, os.path.basename(src) + ".o")
+            _run(["nvcc"] + NVCC_FLAGS + extra + ["-c", src, "-o", obj], verbose)
             objs.append(obj)
         _run(["nvcc", "-shared", "-o", cuda_so] + objs + ["-Xcompiler", "-fopenmp", "-lgomp", "-ldl"], verbose)
         for o in objs:
             os.remove(o)
+    return cuda_so, headers
+
+
+def build(verbose=False, force=False):
+    cuda_so, headers = _build_cuda(LIB, [], verbose, force)
     host_hdr = [os.path.join(HOST, f) for f in os.listdir(HOST) if f.endswith(".h")] + headers
     # scene side of the host mirror (importers, BVH builder): no dependency on the CUDA library — bench.py's reference arm
     # generates its scenes through it without mapping any device code
@@ -74,6 +81,15 @@ def build(verbose=False, force=False):
     if force or _newer(exe, [os.path.join(HOST, "main.cpp"), host_so]):
         _run(["g++"] + CXX_FLAGS + ["-o", exe, os.path.join(HOST, "main.cpp"), "-L", LIB, "-lpathtracer_host", "-lpathtracer_scene",
                                     "-lpathtracer_cuda", "-Wl,-rpath,$ORIGIN"], verbose)
+    # the CHECKED variant of the device library (bounds checks on every index the kernels form, reported through
+    # ptc_counters.faults): tests/test_checked_build.py runs the kernels under it, in the place of compute-sanitizer's memcheck,
+    # which is closed on the GPU pool. Selected with PTC_LIB_DIR=<repo>/opencl_pathtracer_b200/_lib_checked.
+    checked = os.path.join(HERE, "_lib_checked")
+    checked_so, _ = _build_cuda(checked, ["-DPTC_CHECKED"], verbose, force)
+    for so in (scene_so, host_so):
+        dst = os.path.join(checked, os.path.basename(so))
+        if force or _newer(dst, [so]):
+            shutil.copy2(so, dst)
     return cuda_so, host_so
 
 

@@ -108,7 +108,11 @@ void dropBatchGraph(ptc_ctx *ctx)
 // ================================================================================================ create
 extern "C" {
 
-const char *ptc_version(void) { return "PathTracer_CUDA 0.1 (sm_100a)"; }
+#ifdef PTC_CHECKED
+const char *ptc_version(void) { return "PathTracer_CUDA 0.2 (sm_100a) checked"; }
+#else
+const char *ptc_version(void) { return "PathTracer_CUDA 0.2 (sm_100a)"; }
+#endif
 
 int ptc_device_count(void)
 {
@@ -180,7 +184,7 @@ void ptc_destroy(ptc_ctx *ctx)
     ctx->nodes8.release(); ctx->tris8.release(); ctx->tri8Index.release();
     ctx->org.release(); ctx->dir.release(); ctx->thr.release(); ctx->rad.release(); ctx->hit.release();
     ctx->seed.release(); ctx->sample.release(); ctx->meta.release(); ctx->nbbx.release(); ctx->ntri.release();
-    ctx->occl.release(); ctx->queue[0].release(); ctx->queue[1].release(); ctx->counters.release();
+    ctx->occl.release(); ctx->queue[0].release(); ctx->queue[1].release(); ctx->qlit.release(); ctx->qother.release(); ctx->counters.release();
     ctx->imgColor.release(); ctx->imgV.release(); ctx->imgRayNb.release(); ctx->rayDepths.release();
     ctx->rayBbx.release(); ctx->rayTri.release(); ctx->rgb8.release();
     if (ctx->ownStream && ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -192,13 +196,11 @@ int ptc_reset_accumulation(ptc_ctx *ctx)
     if (!ctx) return PTC_ERR_INVALID;
     if (ctx->group) return multi_reset(ctx);
     CK(cudaSetDevice(ctx->device));
-    CK(cudaMemsetAsync(ctx->imgColor.p, 0, sizeof(float4) * ctx->nPix, ctx->stream));
-    CK(cudaMemsetAsync(ctx->imgRayNb.p, 0, sizeof(float) * ctx->nPix, ctx->stream));
-    if (ctx->imgV.p) CK(cudaMemsetAsync(ctx->imgV.p, 0, sizeof(float4) * ctx->nPix, ctx->stream));
-    CK(cudaMemsetAsync(ctx->rayDepths.p, 0, sizeof(uint32_t) * (kMaxBounces + 1), ctx->stream));
-    CK(cudaMemsetAsync(ctx->rayBbx.p, 0, sizeof(uint32_t) * PTC_MAX_INTERSECTION_NUMBER, ctx->stream));
-    CK(cudaMemsetAsync(ctx->rayTri.p, 0, sizeof(uint32_t) * PTC_MAX_INTERSECTION_NUMBER, ctx->stream));
-    CK(cudaMemsetAsync(ctx->counters.p, 0, sizeof(Counters), ctx->stream));
+    launch_clear(ctx->stream, ctx->lc, ctx->img, ctx->nPix, ctx->counters.p);
+    {
+        const cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return fail(ctx, PTC_ERR_CUDA, "ptc_reset_accumulation: %s", cudaGetErrorString(e));
+    }
     if (ctx->cfg.flags & PTC_FLAG_STAGE_TIMING)  // pending stage timers must be read before their totals are cleared
     {
         CK(cudaStreamSynchronize(ctx->stream));
@@ -333,7 +335,7 @@ int ptc_create(const ptc_config *config, ptc_ctx **out_ctx)
     const size_t n = c->capacity;
     A(c->org.alloc(n)); A(c->dir.alloc(n)); A(c->thr.alloc(n)); A(c->rad.alloc(n)); A(c->hit.alloc(n));
     A(c->seed.alloc(n)); A(c->sample.alloc(n)); A(c->meta.alloc(n)); A(c->nbbx.alloc(n)); A(c->ntri.alloc(n));
-    A(c->occl.alloc(n)); A(c->queue[0].alloc(n)); A(c->queue[1].alloc(n)); A(c->counters.alloc(1));
+    A(c->occl.alloc(n)); A(c->queue[0].alloc(n)); A(c->queue[1].alloc(n)); A(c->qlit.alloc(n)); A(c->qother.alloc(n)); A(c->counters.alloc(1));
     A(c->imgColor.alloc(c->nPix)); A(c->imgRayNb.alloc(c->nPix));
     if (!(config->flags & PTC_FLAG_NO_VARIANCE)) A(c->imgV.alloc(c->nPix));
     A(c->rayDepths.alloc(kMaxBounces + 1)); A(c->rayBbx.alloc(PTC_MAX_INTERSECTION_NUMBER)); A(c->rayTri.alloc(PTC_MAX_INTERSECTION_NUMBER));
@@ -343,7 +345,11 @@ int ptc_create(const ptc_config *config, ptc_ctx **out_ctx)
         ptc_destroy(c);
         return fail(nullptr, PTC_ERR_CUDA, "%s", msg.c_str());
     }
-    c->st = PathState{c->org.p, c->dir.p, c->thr.p, c->rad.p, c->hit.p, c->seed.p, c->sample.p, c->meta.p, c->nbbx.p, c->ntri.p, c->occl.p};
+    c->st = PathState{c->org.p, c->dir.p, c->thr.p, c->rad.p, c->hit.p, c->seed.p, c->sample.p, c->meta.p, c->nbbx.p, c->ntri.p, c->occl.p, c->qlit.p, c->qother.p, (uint32_t)c->capacity};
+#ifdef PTC_CHECKED
+    // self-test of the checked build: with a deliberately wrong bound every queue entry beyond slot 0 must be reported
+    if (std::getenv("PTC_CHECKED_SELFTEST")) c->st.capacity = 1u;
+#endif
     c->img = ImageDev{c->imgColor.p, c->imgRayNb.p, c->imgV.p, c->rayDepths.p, c->rayBbx.p, c->rayTri.p};
     // the reference never zeroes its accumulators; this library always does
     int rc = ptc_reset_accumulation(c);
@@ -632,6 +638,7 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
     sc.tri8Index = ctx->wide ? ctx->tri8Index.p : nullptr; sc.nNodes8 = ctx->wide ? nNodes8 : 0u;
     ctx->lc.wide = ctx->wide;
     sc.rootRef = rootRef; sc.nLights = nL; sc.areaJump = areaJump; sc.nTriangles = nT; sc.sky = sky;
+    sc.nInner = nInner; sc.nMaterials = nM; sc.nTextures = nX; sc.nTexels = nTexel; sc.faultSink = ctx->counters.p;
     ctx->cam = Camera{to4(s->camera_position), to4(s->camera_direction), to4(s->camera_right), to4(s->camera_up)};
     // traversal stack: one entry per level below the root is enough (a push happens only when descending)
     if (!std::getenv("PTC_FULL_STACK"))
@@ -644,6 +651,7 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
             ctx->lc.connectGrid = ctx->smCount * traverse_ctas_per_sm(ctx->fast, ctx->wide, ctx->lc.stackDepth, true);
         }
     }
+    sc.stackDepth = (uint32_t)ctx->lc.stackDepth;
     ctx->sceneLoaded = true;
     ctx->sceneVersion++;  // device pointers and launch configuration may have changed: a captured batch graph is stale
     return PTC_OK;
@@ -679,6 +687,7 @@ int replicate_scene(ptc_ctx *dst, const ptc_ctx *src)
     sc.bigLeafCount = src->sc.bigLeafCount ? dst->bigLeaf.p : nullptr;
     sc.nodes8 = src->sc.nodes8 ? dst->nodes8.p : nullptr; sc.tris8 = src->sc.tris8 ? dst->tris8.p : nullptr;
     sc.tri8Index = src->sc.tri8Index ? dst->tri8Index.p : nullptr;
+    sc.faultSink = dst->counters.p;
     dst->sc = sc;
     dst->cam = src->cam;
     dst->wideDepth = src->wideDepth;
@@ -826,7 +835,7 @@ int runBatch(ptc_ctx *ctx, uint32_t first, uint32_t nIter, bool accumulate, int 
         }
         {
             StageTimer t(ctx, 3);
-            launch_shade(s, ctx->lc, ctx->fast, ctx->sc, fp, ctx->st, qin, qout, cn, b);
+            launch_shade(s, ctx->lc, ctx->fast, ctx->sc, fp, ctx->st, qout, cn, b);
         }
         ctx->launches += 2;
         ctx->launchesExtend++;
@@ -1091,6 +1100,8 @@ int ptc_read_counters(ptc_ctx *ctx, ptc_counters *out)
     out->scene_bytes_triangles = ctx->tris.n * sizeof(DevTri);
     out->ext_box_tests = h.extBoxTests;
     out->ext_triangle_tests = h.extTriTests;
+    out->faults = h.faults;
+    out->fault_code = h.faultInfo[0]; out->fault_value = h.faultInfo[1]; out->fault_bound = h.faultInfo[2];
     return PTC_OK;
 }
 

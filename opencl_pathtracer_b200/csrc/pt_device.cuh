@@ -96,6 +96,10 @@ struct SceneDev
     uint32_t nTriangles;
     uint32_t areaJump;  // 16807^(2 * number of PTC_LIGHT_AREA lights) mod 2^32; 1 without area lights (pt_shade.cuh light_resolve)
     DevSky sky;
+    // array bounds for the CHECKED build (-DPTC_CHECKED, opencl_pathtracer_b200/_lib_checked): every index the kernels form is
+    // compared with these and a violation is recorded in Counters::faults (compute-sanitizer is closed on the GPU pool)
+    uint32_t nInner, nMaterials, nTextures, nTexels, stackDepth;
+    struct Counters *faultSink;
 };
 
 struct Camera
@@ -116,6 +120,11 @@ struct PathState
     uint32_t *nbbx;   // numIntersectedBBx (camera ray + its shadow rays)
     uint32_t *ntri;   // numIntersectedTri
     uint32_t *occl;   // bit i = light i occluded at the current hit
+    // class queues of the current bounce, filled by extend as its rays finish: paths whose hit reads the direct light (connect +
+    // the lit half of shade) and the others (misses; FAST: hits on glass / water, which never read it)
+    uint32_t *qlit;
+    uint32_t *qother;
+    uint32_t capacity;  // path slots (bound of every queue entry; CHECKED build)
 };
 
 // queue / cursor block, one set per bounce so nothing has to be reset inside a batch
@@ -125,9 +134,42 @@ struct Counters
     uint32_t qcount[kMaxBounces + 1];     // live paths entering bounce b
     uint32_t curExtend[kMaxBounces + 1];  // work cursors of the persistent kernels
     uint32_t curConnect[kMaxBounces + 1];
+    uint32_t qlit[kMaxBounces + 1];       // lengths of the class queues of bounce b
+    uint32_t qother[kMaxBounces + 1];
     unsigned long long extensionRays, shadowRays, boxTests, triTests, paths;
     unsigned long long extBoxTests, extTriTests;  // share of boxTests / triTests spent by closest-hit rays
+    uint32_t faults;        // CHECKED build: bit c set = check c failed somewhere (codes below); always 0 in the normal build
+    uint32_t faultInfo[3];  // the first failure: code, offending value, bound
 };
+
+// CHECKED build (compute-sanitizer is closed on the GPU pool; SURVEY.md section 5 asks for memcheck evidence): bounds checks on
+// every index the kernels form — queue entries, path slots, node / triangle / material / texture / texel indices, traversal stack
+// levels, target pixels. A failure sets a bit; nothing traps, so one run reports every class of violation.
+enum FaultCode : uint32_t
+{
+    kFaultQueueItem = 0, kFaultNodeIndex, kFaultTriIndex, kFaultStack, kFaultHitIndex, kFaultQueueAppend, kFaultMaterial, kFaultTexture,
+    kFaultTexel, kFaultPixel, kFaultLight
+};
+#ifdef PTC_CHECKED
+__device__ __forceinline__ void ptc_fault(Counters *cn, uint32_t code, uint32_t value, uint32_t bound)
+{
+    if (atomicOr(&cn->faults, 1u << code) == 0u)
+    {
+        cn->faultInfo[0] = code; cn->faultInfo[1] = value; cn->faultInfo[2] = bound;
+    }
+}
+#define PTC_CHECK(cn, code, value, bound)                                               \
+    do                                                                                  \
+    {                                                                                   \
+        if (!((uint32_t)(value) < (uint32_t)(bound))) ptc_fault(cn, code, (uint32_t)(value), (uint32_t)(bound)); \
+    } while (0)
+#else
+#define PTC_CHECK(cn, code, value, bound) \
+    do                                    \
+    {                                     \
+    } while (0)
+#endif
+
 
 struct FrameParams
 {

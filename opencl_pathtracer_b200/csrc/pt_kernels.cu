@@ -24,6 +24,9 @@ constexpr int kTraverseThreads = PTC_TRAVERSE_THREADS;
 constexpr uint32_t kFlagRussianRoulette = 1u << 5;  // PTC_FLAG_RUSSIAN_ROULETTE (include/pathtracer_cuda.h)
 constexpr uint32_t kFlagTextureBilinear = 1u << 6;  // PTC_FLAG_TEXTURE_BILINEAR
 constexpr int kStreamThreads = 256;
+#ifndef PTC_SHADE_MIN_BLOCKS
+#define PTC_SHADE_MIN_BLOCKS 4  // k_shade: 4 CTAs of 8 warps per SM = 64 registers (A/B: scripts/build_variant.sh shade3 -DPTC_SHADE_MIN_BLOCKS=3)
+#endif
 
 // ------------------------------------------------------------------------------------------------ reset
 __global__ void k_reset(Counters *cn, uint32_t nPaths)
@@ -34,6 +37,8 @@ __global__ void k_reset(Counters *cn, uint32_t nPaths)
         cn->qcount[i] = i == 0 ? nPaths : 0u;
         cn->curExtend[i] = 0;
         cn->curConnect[i] = 0;
+        cn->qlit[i] = 0;
+        cn->qother[i] = 0;
     }
 }
 
@@ -171,7 +176,8 @@ __global__ void __launch_bounds__(kTraverseThreads, (ANY ? LaneT::kMinCtasAny : 
     const unsigned full = 0xffffffffu;
     const int voteNode = (int)((popMin >> 8) & 0xffu), voteTri = (int)((popMin >> 16) & 0xffu);  // in eighths of the warp's rays
     popMin &= 0xffu;
-    const uint32_t count = cn->qcount[bounce];
+    const uint32_t count = ANY ? cn->qlit[bounce] : cn->qcount[bounce];  // connect draws from the lit class queue extend has filled
+    if (ANY) queue = st.qlit;
     const uint32_t nL = ANY ? sc.nLights : 1u;
     const uint32_t total = ANY ? count : count * nL;  // work items drawn from the cursor: paths (connect draws groups of 32 paths)
     uint32_t *cursor = ANY ? &cn->curConnect[bounce] : &cn->curExtend[bounce];
@@ -190,13 +196,16 @@ __global__ void __launch_bounds__(kTraverseThreads, (ANY ? LaneT::kMinCtasAny : 
         {
             const uint32_t item = stage.laneItem[lane];
             const uint32_t p = ANY ? (item & ((1u << kLightShift) - 1u)) : item;
+            PTC_CHECK(cn, kFaultQueueItem, p, st.capacity);
             const uint32_t li = ANY ? (item >> kLightShift) : 0u;
             if (!ANY)
             {
                 float hs, ht, htp;
                 uint32_t hmat;
                 L.hit_record(sc, hs, ht, htp, hmat);
-                st.hit[p] = f4(__int_as_float(L.hit_index(sc)), hs, ht, htp);
+                const int hitIndex = L.hit_index(sc);
+                if (hitIndex >= 0) PTC_CHECK(cn, kFaultHitIndex, hitIndex, sc.nTriangles);
+                st.hit[p] = f4(__int_as_float(hitIndex), hs, ht, htp);
                 if (COUNT)
                 {
                     atomicAdd(&st.nbbx[p], L.nb);
@@ -206,6 +215,18 @@ __global__ void __launch_bounds__(kTraverseThreads, (ANY ? LaneT::kMinCtasAny : 
                 if (L.hitTri < 0) flags = kOcclMiss;
                 else if (FAST && !(hmat == 0u || hmat == 3u)) flags = kOcclUnlit;  // GLASS / WATER / METAL / UNKNOWN never read the direct light (:805-843)
                 st.occl[p] = flags;
+                // the path joins the class queue of this bounce that the later stages draw from: lit hits -> connect and the lit half
+                // of shade; everything else -> the other half. One atomic per class for the lanes that finish together.
+                const bool lit = flags == 0u;
+                const unsigned act = __activemask();
+                const unsigned ml = __ballot_sync(act, lit);
+                const unsigned mine = lit ? ml : (act & ~ml);
+                const int leader = __ffs((int)mine) - 1;
+                uint32_t base = 0;
+                if ((int)lane == leader) base = atomicAdd(lit ? &cn->qlit[bounce] : &cn->qother[bounce], (uint32_t)__popc(mine));
+                base = __shfl_sync(mine, base, leader);
+                PTC_CHECK(cn, kFaultQueueAppend, base + (uint32_t)__popc(mine & lt), st.capacity);
+                (lit ? st.qlit : st.qother)[base + (uint32_t)__popc(mine & lt)] = p;
             }
             else
             {
@@ -244,6 +265,7 @@ __global__ void __launch_bounds__(kTraverseThreads, (ANY ? LaneT::kMinCtasAny : 
                     if (valid)
                     {
                         item = queue ? queue[k] : k;
+                        PTC_CHECK(cn, kFaultQueueItem, item, st.capacity);
                         o = st.org[item];
                         d = st.dir[item];
                     }
@@ -268,6 +290,7 @@ __global__ void __launch_bounds__(kTraverseThreads, (ANY ? LaneT::kMinCtasAny : 
                         if (lit)
                         {
                             pp = queue ? queue[k] : k;
+                            PTC_CHECK(cn, kFaultQueueItem, pp, st.capacity);
                             lit = !(st.occl[pp] & (kOcclUnlit | kOcclMiss));
                         }
                         if (lit)
@@ -296,6 +319,7 @@ __global__ void __launch_bounds__(kTraverseThreads, (ANY ? LaneT::kMinCtasAny : 
                     if (valid)
                     {
                         const float4 q = group.q[lane];
+                        PTC_CHECK(cn, kFaultLight, l, sc.nLights);
                         DevLight light = sc.lights[l];
                         if (FAST == 2 && light.type == 4) light = light_resolve(light, st.seed[group.slot[lane]]);
                         // FAST: a light that sends exactly zero power towards the shading normal (:403-421: behind the surface,
@@ -380,11 +404,171 @@ __global__ void __launch_bounds__(kTraverseThreads, (ANY ? LaneT::kMinCtasAny : 
 }
 
 // ------------------------------------------------------------------------------------------------ shade
-template <int FAST>  // as k_trace
-__global__ void __launch_bounds__(kStreamThreads, 4) k_shade(SceneDev sc, FrameParams fp, PathState st, const uint32_t *__restrict__ qin,
-                                                         uint32_t *__restrict__ qout, Counters *__restrict__ cn, int bounce)
+// One path of the shade stage. CLASS 0: a hit that reads the direct light (the lit class queue: every hit in PARITY, MAT_STANDART /
+// MAT_VARNHISHED hits in FAST); CLASS 1: the others (misses; FAST: hits on glass / water / unknown materials, whose direct light
+// is never read, K.cl:805-843). The class is a compile-time constant, so each copy carries only the branches its class can take:
+// the lit copy has no sky and, in FAST, no Fresnel transmission; the other copy has no light loop and no cosine sampling. Returns
+// whether the path goes on to the next bounce.
+template <int FAST, int CLASS>
+__device__ __forceinline__ bool shade_path(const SceneDev &sc, const FrameParams &fp, const PathState &st, const uint32_t p)
 {
-    const uint32_t count = cn->qcount[bounce];
+    const float4 o = st.org[p], d = st.dir[p], h = st.hit[p];
+    float4 T = st.thr[p], rad = st.rad[p];
+    uint32_t meta = st.meta[p];
+    const int tri = __float_as_int(h.x);
+    PTC_CHECK(sc.faultSink, kFaultQueueItem, p, st.capacity);
+    if (tri >= 0) PTC_CHECK(sc.faultSink, kFaultHitIndex, tri, sc.nTriangles);
+    float4 emitted;
+    // area lights (extension): a camera ray or a specular chain that reaches an emitter ends there with its radiance
+    if (FAST == 2 && ((meta & 0xffu) == 0u || (meta & kMetaSpecular)) && emitter_seen(sc, o, d, tri < 0 ? INFINITY : h.w, emitted))
+    {
+        st.rad[p] = rad + emitted * T;
+        return false;
+    }
+    if (CLASS == 1 && tri < 0)
+    {
+        // :1281-1288 sky
+        st.rad[p] = rad + sky_color(sc, d) * T;
+        return false;
+    }
+    int seed = st.seed[p];
+    const float s = h.y, t = h.z;
+    const float4 q = f4(o.x + d.x * h.w, o.y + d.y * h.w, o.z + d.z * h.w, o.w + d.w * h.w);
+    const float4 N = __ldg(&sc.tris[tri].n);
+    const DevShade *sh = &sc.shade[tri];
+    const float nd = dot4(N, d);
+    const bool positive = nd < 0;  // :568
+    const uint4 ids = __ldg(&sh->ids);
+    PTC_CHECK(sc.faultSink, kFaultMaterial, positive ? ids.x : ids.y, sc.nMaterials);
+    const DevMaterial mat = sc.materials[positive ? ids.x : ids.y];
+    // what the class queue promises about the material (FAST: extend sorted the hit by the MaterialType in its triangle record)
+    const bool litType = mat.type == 0 || mat.type == 3;
+    // :591-602 surface colour of the final hit
+    float4 color;
+    if (mat.isSimpleColor) color = mat.color;
+    else
+    {
+        const float4 a = __ldg(&sh->uvp12), b = __ldg(&sh->uvp3_uvn1), c = __ldg(&sh->uvn23);
+        const float w0 = 1 - s - t;
+        float tu, tv;
+        if (positive) { tu = (a.x * w0 + a.z * s) + b.x * t; tv = (a.y * w0 + a.w * s) + b.y * t; }
+        else { tu = (b.z * w0 + c.x * s) + c.z * t; tv = (b.w * w0 + c.y * s) + c.w * t; }
+        PTC_CHECK(sc.faultSink, kFaultTexture, mat.textureId, sc.nTextures);
+        const uint4 tx = __ldg(&sc.textures[mat.textureId]);
+        color = (FAST && (fp.flags & kFlagTextureBilinear)) ? texture_lookup_bilinear(sc, tx.x, tx.y, tx.z, tu, tv)
+                                                               : texture_lookup(sc, tx.x, tx.y, tx.z, tu, tv);
+    }
+    // :1267-1274 normals
+    const bool same = dot4(d, N) > 0;
+    const float4 Ng = same ? -N : N;
+    const float4 Ns = shading_normal(sh, N, d, s, t);
+    // :901-954 direct illumination from the occlusion bits the connect stage left
+    float4 L = f4(0, 0, 0, 0);
+    if (CLASS == 0)
+    {
+        const uint32_t occl = st.occl[p] & kOcclMask;
+        for (uint32_t li = 0; li < sc.nLights; li++)
+        {
+            // an occluded light adds nothing (:944-949); neither does one the connect stage found to send zero power
+            // (its term would be +-0): both carry their bit, and the term is not evaluated at all
+            if ((occl >> li) & 1u) continue;
+            DevLight l = sc.lights[li];
+            if (FAST == 2 && l.type == 4) l = light_resolve(l, seed);
+            const float4 full = (l.type == 0) ? -l.direction : (l.position - q);
+            const float4 ldir = normalize4(full);
+            const float brdf = material_brdf(mat.type, -ldir, Ns, d);
+            L = L + (light_power_toward<FAST == 2>(l, q, Ns) * brdf) * l.color;
+        }
+    }
+    // area lights (extension): the stream moves past the draws their sample points took, lit hit or not
+    if (FAST == 2) seed = (int)(((unsigned)seed * sc.areaJump) & 0x7FFFFFFFu);
+    // :791-891
+    float4 Nref = d, out = d;
+    float4 add = f4(0, 0, 0, 0);
+    bool inWater = (meta >> 8) & 1u;
+    // the cosine-weighted bounce of MAT_STANDART and of the diffuse branch of MAT_VARNHISHED is drawn in one place,
+    // after the per-material part, so that the lanes of both materials run it together (same draws, same order)
+    bool diffuseBounce = false;
+    bool specular = mat.type == 1 || mat.type == 2;  // only read by the area-light variant
+    // which material branches this copy can reach: PARITY's lit class holds every material, FAST's only the two lit ones
+    const bool mayBeLit = CLASS == 0, mayBeUnlit = CLASS == 1 || !FAST;
+    if (mayBeLit && mat.type == 0)
+    {
+        T = T * color;
+        add = L * T;
+        diffuseBounce = true;
+        Nref = Ns;
+    }
+    else if (mayBeUnlit && mat.type == 2)
+    {
+        float cos2;
+        const float cos1 = -dot4(d, Ns);
+        const float rF = fresnel(1, 1.55f, cos1, cos2);
+        if (rng_next(seed) < rF) { out = d - (Ns * (2 * dot4(d, Ns))); Nref = Ng; }
+        else { T = T * (color * (1 - mat.opacity)); Nref = d; }
+    }
+    else if (mayBeUnlit && mat.type == 1)
+    {
+        const float n1w = inWater ? 1.333f : 1.f, n2w = inWater ? 1.f : 1.333f;
+        float cos2;
+        const float cos1 = -dot4(d, Ns);
+        const float rF = fresnel(n1w, n2w, cos1, cos2);
+        // on total reflection the reference leaves refractedDirection unset and never reads it
+        const float4 refr = d * (n1w / n2w) + Ns * (n1w / n2w * cos1 - cos2);
+        const float coeff = (n2w * n2w) / (n1w * n1w);
+        if (rng_next(seed) < rF) { out = d - (Ns * (2 * dot4(d, Ns))); Nref = Ng; }
+        else { inWater = !inWater; out = refr; Nref = -Ng; T = T * coeff; }
+    }
+    else if (mayBeLit && mat.type == 3)
+    {
+        add = add + L * color * T;
+        const float rF = fresnel_varnish(d, Ns);
+        if (rng_next(seed) < rF) { out = d - (Ns * (2 * dot4(d, Ns))); specular = true; }
+        else { diffuseBounce = true; T = T * color; }
+    }
+    (void)litType;
+    if (mayBeLit && diffuseBounce) out = cosine_sample_hemisphere(seed, Ns);
+    put_in_same_hemisphere(out, Nref);
+    rad = rad + add;
+    const uint32_t refl = (meta & 0xffu) + 1u;
+    meta = refl | (inWater ? 0x100u : 0u) | ((FAST == 2 && specular) ? kMetaSpecular : 0u);
+    st.org[p] = q + 0.001f * out;  // :880
+    st.dir[p] = normalize4(out);
+    st.thr[p] = T;
+    if (CLASS == 0) st.rad[p] = rad;  // the other class adds nothing to the radiance at a hit
+    st.seed[p] = seed;
+    st.meta[p] = meta;
+    // :1294-1304 and the loop condition :1248
+    const float maxContribution = clmax(T.x, clmax(T.y, T.z));
+    bool alive = !(maxContribution <= 0.001f) && refl < fp.maxDepth;
+    // Russian roulette (opt-in, FAST only). The reference carries it disabled and commented out
+    // (:12-13, :1306-1314: coefficient maxContribution / (reflectionId - MIN_REFLECTION_NUMBER), MIN = 5), and as written
+    // there it would be biased (it keeps a path with probability 1 - c yet divides by c). Here: survive with
+    // probability c, divide the throughput by c — unbiased; one extra draw from the path's stream.
+    if (FAST && (fp.flags & kFlagRussianRoulette) && alive && refl > 5u)
+    {
+        const float c = maxContribution / (float)(refl - 5u);
+        if (c < 1.f)
+        {
+            alive = rng_next(seed) < c;
+            T = T / c;
+            st.thr[p] = T;
+            st.seed[p] = seed;
+        }
+    }
+    return alive;
+}
+
+// Both class queues of the bounce in one launch: the lit queue is padded to a multiple of 32 in the index space, so every warp
+// shades paths of one class and runs one copy of shade_path (round 1's single mixed queue ran 16 of 32 lanes and waited on
+// instruction fetch: 3,200 SASS lines touched by every warp). Survivors of both classes are appended to the next bounce's queue.
+template <int FAST>  // as k_trace
+__global__ void __launch_bounds__(kStreamThreads, PTC_SHADE_MIN_BLOCKS) k_shade(SceneDev sc, FrameParams fp, PathState st, uint32_t *__restrict__ qout,
+                                                         Counters *__restrict__ cn, int bounce)
+{
+    const uint32_t nLit = cn->qlit[bounce], nOther = cn->qother[bounce];
+    const uint32_t nLitPad = (nLit + 31u) & ~31u;
+    const uint32_t count = nLitPad + nOther;
     const uint32_t stride = blockDim.x * gridDim.x;
     const uint32_t rounds = (count + stride - 1) / stride;
     for (uint32_t it = 0; it < rounds; it++)
@@ -392,145 +576,18 @@ __global__ void __launch_bounds__(kStreamThreads, 4) k_shade(SceneDev sc, FrameP
         const uint32_t k = it * stride + blockIdx.x * blockDim.x + threadIdx.x;
         bool alive = false;
         uint32_t p = 0;
-        if (k < count)
+        if (k < nLitPad)
         {
-            p = qin ? qin[k] : k;
-            const float4 o = st.org[p], d = st.dir[p], h = st.hit[p];
-            float4 T = st.thr[p], rad = st.rad[p];
-            uint32_t meta = st.meta[p];
-            const int tri = __float_as_int(h.x);
-            float4 emitted;
-            // area lights (extension): a camera ray or a specular chain that reaches an emitter ends there with its radiance
-            if (FAST == 2 && ((meta & 0xffu) == 0u || (meta & kMetaSpecular)) && emitter_seen(sc, o, d, tri < 0 ? INFINITY : h.w, emitted))
+            if (k < nLit)
             {
-                rad = rad + emitted * T;
-                st.rad[p] = rad;
+                p = st.qlit[k];
+                alive = shade_path<FAST, 0>(sc, fp, st, p);
             }
-            else if (tri < 0)
-            {
-                // :1281-1288 sky
-                rad = rad + sky_color(sc, d) * T;
-                st.rad[p] = rad;
-            }
-            else
-            {
-                int seed = st.seed[p];
-                const float s = h.y, t = h.z;
-                const float4 q = f4(o.x + d.x * h.w, o.y + d.y * h.w, o.z + d.z * h.w, o.w + d.w * h.w);
-                const float4 N = __ldg(&sc.tris[tri].n);
-                const DevShade *sh = &sc.shade[tri];
-                const float nd = dot4(N, d);
-                const bool positive = nd < 0;  // :568
-                const uint4 ids = __ldg(&sh->ids);
-                const DevMaterial mat = sc.materials[positive ? ids.x : ids.y];
-                // :591-602 surface colour of the final hit
-                float4 color;
-                if (mat.isSimpleColor) color = mat.color;
-                else
-                {
-                    const float4 a = __ldg(&sh->uvp12), b = __ldg(&sh->uvp3_uvn1), c = __ldg(&sh->uvn23);
-                    const float w0 = 1 - s - t;
-                    float tu, tv;
-                    if (positive) { tu = (a.x * w0 + a.z * s) + b.x * t; tv = (a.y * w0 + a.w * s) + b.y * t; }
-                    else { tu = (b.z * w0 + c.x * s) + c.z * t; tv = (b.w * w0 + c.y * s) + c.w * t; }
-                    const uint4 tx = __ldg(&sc.textures[mat.textureId]);
-                    color = (FAST && (fp.flags & kFlagTextureBilinear)) ? texture_lookup_bilinear(sc, tx.x, tx.y, tx.z, tu, tv)
-                                                                           : texture_lookup(sc, tx.x, tx.y, tx.z, tu, tv);
-                }
-                // :1267-1274 normals
-                const bool same = dot4(d, N) > 0;
-                const float4 Ng = same ? -N : N;
-                const float4 Ns = shading_normal(sh, N, d, s, t);
-                // :901-954 direct illumination from the occlusion bits the connect stage left
-                float4 L = f4(0, 0, 0, 0);
-                const uint32_t occl = st.occl[p] & kOcclMask;
-                if (!FAST || mat.type == 0 || mat.type == 3)
-                    for (uint32_t li = 0; li < sc.nLights; li++)
-                    {
-                        // an occluded light adds nothing (:944-949); neither does one the connect stage found to send zero power
-                        // (its term would be +-0): both carry their bit, and the term is not evaluated at all
-                        if ((occl >> li) & 1u) continue;
-                        DevLight l = sc.lights[li];
-                        if (FAST == 2 && l.type == 4) l = light_resolve(l, seed);
-                        const float4 full = (l.type == 0) ? -l.direction : (l.position - q);
-                        const float4 ldir = normalize4(full);
-                        const float brdf = material_brdf(mat.type, -ldir, Ns, d);
-                        L = L + (light_power_toward<FAST == 2>(l, q, Ns) * brdf) * l.color;
-                    }
-                // area lights (extension): the stream moves past the draws their sample points took, lit hit or not
-                if (FAST == 2) seed = (int)(((unsigned)seed * sc.areaJump) & 0x7FFFFFFFu);
-                // :791-891
-                float4 Nref = d, out = d;
-                float4 add = f4(0, 0, 0, 0);
-                bool inWater = (meta >> 8) & 1u;
-                // the cosine-weighted bounce of MAT_STANDART and of the diffuse branch of MAT_VARNHISHED is drawn in one place,
-                // after the per-material part, so that the lanes of both materials run it together (same draws, same order)
-                bool diffuseBounce = false;
-                bool specular = mat.type == 1 || mat.type == 2;  // only read by the area-light variant
-                if (mat.type == 0)
-                {
-                    T = T * color;
-                    add = L * T;
-                    diffuseBounce = true;
-                    Nref = Ns;
-                }
-                else if (mat.type == 2)
-                {
-                    float cos2;
-                    const float cos1 = -dot4(d, Ns);
-                    const float rF = fresnel(1, 1.55f, cos1, cos2);
-                    if (rng_next(seed) < rF) { out = d - (Ns * (2 * dot4(d, Ns))); Nref = Ng; }
-                    else { T = T * (color * (1 - mat.opacity)); Nref = d; }
-                }
-                else if (mat.type == 1)
-                {
-                    const float n1w = inWater ? 1.333f : 1.f, n2w = inWater ? 1.f : 1.333f;
-                    float cos2;
-                    const float cos1 = -dot4(d, Ns);
-                    const float rF = fresnel(n1w, n2w, cos1, cos2);
-                    // on total reflection the reference leaves refractedDirection unset and never reads it
-                    const float4 refr = d * (n1w / n2w) + Ns * (n1w / n2w * cos1 - cos2);
-                    const float coeff = (n2w * n2w) / (n1w * n1w);
-                    if (rng_next(seed) < rF) { out = d - (Ns * (2 * dot4(d, Ns))); Nref = Ng; }
-                    else { inWater = !inWater; out = refr; Nref = -Ng; T = T * coeff; }
-                }
-                else if (mat.type == 3)
-                {
-                    add = add + L * color * T;
-                    const float rF = fresnel_varnish(d, Ns);
-                    if (rng_next(seed) < rF) { out = d - (Ns * (2 * dot4(d, Ns))); specular = true; }
-                    else { diffuseBounce = true; T = T * color; }
-                }
-                if (diffuseBounce) out = cosine_sample_hemisphere(seed, Ns);
-                put_in_same_hemisphere(out, Nref);
-                rad = rad + add;
-                const uint32_t refl = (meta & 0xffu) + 1u;
-                meta = refl | (inWater ? 0x100u : 0u) | ((FAST == 2 && specular) ? kMetaSpecular : 0u);
-                st.org[p] = q + 0.001f * out;  // :880
-                st.dir[p] = normalize4(out);
-                st.thr[p] = T;
-                st.rad[p] = rad;
-                st.seed[p] = seed;
-                st.meta[p] = meta;
-                // :1294-1304 and the loop condition :1248
-                const float maxContribution = clmax(T.x, clmax(T.y, T.z));
-                alive = !(maxContribution <= 0.001f) && refl < fp.maxDepth;
-                // Russian roulette (opt-in, FAST only). The reference carries it disabled and commented out
-                // (:12-13, :1306-1314: coefficient maxContribution / (reflectionId - MIN_REFLECTION_NUMBER), MIN = 5), and as written
-                // there it would be biased (it keeps a path with probability 1 - c yet divides by c). Here: survive with
-                // probability c, divide the throughput by c — unbiased; one extra draw from the path's stream.
-                if (FAST && (fp.flags & kFlagRussianRoulette) && alive && refl > 5u)
-                {
-                    const float c = maxContribution / (float)(refl - 5u);
-                    if (c < 1.f)
-                    {
-                        alive = rng_next(seed) < c;
-                        T = T / c;
-                        st.thr[p] = T;
-                        st.seed[p] = seed;
-                    }
-                }
-            }
+        }
+        else if (k - nLitPad < nOther)
+        {
+            p = st.qother[k - nLitPad];
+            alive = shade_path<FAST, 1>(sc, fp, st, p);
         }
         // warp-aggregated append of the survivors to the next bounce's queue
         const unsigned m = __ballot_sync(0xffffffffu, alive);
@@ -541,6 +598,7 @@ __global__ void __launch_bounds__(kStreamThreads, 4) k_shade(SceneDev sc, FrameP
             uint32_t base = 0;
             if ((int)lane == leader) base = atomicAdd(&cn->qcount[bounce + 1], (uint32_t)__popc(m));
             base = __shfl_sync(0xffffffffu, base, leader);
+            if (alive) PTC_CHECK(cn, kFaultQueueAppend, base + __popc(m & ((1u << lane) - 1u)), st.capacity);
             if (alive) qout[base + __popc(m & ((1u << lane) - 1u))] = p;
         }
     }
@@ -660,6 +718,7 @@ __global__ void __launch_bounds__(kStreamThreads) k_accumulate(FrameParams fp, P
                 if (st.meta[k] & kMetaSkipped) continue;  // dropped by k_supersample: the reference's work-item returned at :1221
                 const float4 x = st.rad[k];
                 const uint32_t tp = target_pixel(st.sample[k], fp.width, fp.height);
+                PTC_CHECK(cn, kFaultPixel, tp, fp.width * fp.height);
                 count_path(fp, st, k, sDepth, sBbx, sTri);
                 if (tp == pix) add_sample(img, pix, x, fp.firstIteration + li);
                 else add_sample_atomic(img, tp, x);
@@ -750,6 +809,26 @@ __global__ void k_rgb8(ImageDev img, uint32_t nPixels, uint8_t *rgb, uint32_t wi
         rgb[3 * p + 0] = (uint8_t)r;
         rgb[3 * p + 1] = (uint8_t)g;
         rgb[3 * p + 2] = (uint8_t)b;
+    }
+}
+
+// ptc_reset_accumulation: every accumulator, histogram and counter in ONE launch (seven memsets before: a progressive frame
+// resets once per frame, and a multi-device context once per frame and device)
+__global__ void __launch_bounds__(kStreamThreads) k_clear(ImageDev img, uint32_t nPixels, Counters *cn)
+{
+    const float4 z = f4(0, 0, 0, 0);
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < nPixels; p += gridDim.x * blockDim.x)
+    {
+        img.color[p] = z;
+        img.rayNb[p] = 0.f;
+        if (img.variance) img.variance[p] = z;
+    }
+    if (blockIdx.x == 0)
+    {
+        for (uint32_t i = threadIdx.x; i < kHistBins; i += blockDim.x) img.rayBbx[i] = img.rayTri[i] = 0u;
+        for (uint32_t i = threadIdx.x; i <= (uint32_t)kMaxBounces; i += blockDim.x) img.rayDepths[i] = 0u;
+        uint32_t *c = reinterpret_cast<uint32_t *>(cn);
+        for (uint32_t i = threadIdx.x; i < sizeof(Counters) / 4; i += blockDim.x) c[i] = 0u;
     }
 }
 
@@ -864,11 +943,11 @@ void launch_connect(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneD
 }
 
 void launch_shade(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const FrameParams &fp, const PathState &st,
-                  const uint32_t *qin, uint32_t *qout, Counters *cn, int bounce)
+                  uint32_t *qout, Counters *cn, int bounce)
 {
-    if (fast && sc.areaJump != 1u) k_shade<2><<<lc.streamGrid, kStreamThreads, 0, s>>>(sc, fp, st, qin, qout, cn, bounce);
-    else if (fast) k_shade<1><<<lc.streamGrid, kStreamThreads, 0, s>>>(sc, fp, st, qin, qout, cn, bounce);
-    else k_shade<0><<<lc.streamGrid, kStreamThreads, 0, s>>>(sc, fp, st, qin, qout, cn, bounce);
+    if (fast && sc.areaJump != 1u) k_shade<2><<<lc.streamGrid, kStreamThreads, 0, s>>>(sc, fp, st, qout, cn, bounce);
+    else if (fast) k_shade<1><<<lc.streamGrid, kStreamThreads, 0, s>>>(sc, fp, st, qout, cn, bounce);
+    else k_shade<0><<<lc.streamGrid, kStreamThreads, 0, s>>>(sc, fp, st, qout, cn, bounce);
 }
 
 void launch_accumulate(cudaStream_t s, const LaunchCfg &lc, const FrameParams &fp, const PathState &st, const ImageDev &img,
@@ -901,6 +980,11 @@ void launch_probe_rays(cudaStream_t s, uint32_t n, const float4 *origin, const f
 void launch_rgb8(cudaStream_t s, const ImageDev &img, const FrameParams &fp, uint8_t *rgb)
 {
     k_rgb8<<<1024, 256, 0, s>>>(img, fp.width * fp.height, rgb, fp.width, fp.stripeRows, fp.stripeRank, fp.stripeWorld);
+}
+
+void launch_clear(cudaStream_t s, const LaunchCfg &lc, const ImageDev &img, uint32_t nPixels, Counters *cn)
+{
+    k_clear<<<lc.streamGrid, kStreamThreads, 0, s>>>(img, nPixels, cn);
 }
 
 void launch_add_image(cudaStream_t s, const ImageDev &img, uint32_t nPixels, const float4 *color, const float *rayNb)

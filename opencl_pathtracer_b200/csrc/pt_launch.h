@@ -27,8 +27,9 @@ void launch_extend(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDe
                    Counters *cn, int bounce);
 void launch_connect(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const PathState &st, const uint32_t *queue,
                     Counters *cn, int bounce);
+// shades both class queues of the bounce (PathState::qlit / qother, filled by extend) and appends the survivors to qout
 void launch_shade(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const FrameParams &fp, const PathState &st,
-                  const uint32_t *qin, uint32_t *qout, Counters *cn, int bounce);
+                  uint32_t *qout, Counters *cn, int bounce);
 void launch_accumulate(cudaStream_t s, const LaunchCfg &lc, const FrameParams &fp, const PathState &st, const ImageDev &img,
                        Counters *cn);
 // batch graphs: host stubs of k_generate(fp, cam, st) and k_accumulate(fp, st, img, cn), to find their nodes in a captured graph
@@ -42,6 +43,7 @@ void launch_probe_rays(cudaStream_t s, uint32_t n, const float4 *origin, const f
 void launch_read_stream(cudaStream_t s, int grid, const void *buf, size_t bytes, uint32_t repeats, uint32_t *sink);
 // display epilogue: sum / count -> clamp -> 8 bit (reference Alone/PathTracer_bitmap.cpp:259-279)
 void launch_rgb8(cudaStream_t s, const ImageDev &img, const FrameParams &fp, uint8_t *rgb);
+void launch_clear(cudaStream_t s, const LaunchCfg &lc, const ImageDev &img, uint32_t nPixels, Counters *cn);
 void launch_add_image(cudaStream_t s, const ImageDev &img, uint32_t nPixels, const float4 *color, const float *rayNb);
 
 }  // namespace ptc

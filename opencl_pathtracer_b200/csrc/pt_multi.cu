@@ -396,6 +396,8 @@ int multi_read_counters(ptc_ctx *h, ptc_counters *out)
         out->box_tests += c.box_tests; out->triangle_tests += c.triangle_tests; out->kernel_launches += c.kernel_launches;
         out->launches_extend += c.launches_extend; out->launches_connect += c.launches_connect;
         out->ext_box_tests += c.ext_box_tests; out->ext_triangle_tests += c.ext_triangle_tests;
+        out->faults |= c.faults;
+        if (c.faults && !out->fault_bound) { out->fault_code = c.fault_code; out->fault_value = c.fault_value; out->fault_bound = c.fault_bound; }
         if (first)
         {
             // stage times and scene sizes: member 0's (every member holds the same scene)

@@ -35,6 +35,7 @@ __device__ __forceinline__ float4 texture_lookup(const SceneDev &sc, uint32_t w,
     v = v - ((int)v) + (v < 0 ? 1 : 0);
     const uint32_t x = (uint32_t)(u * (w - 1));
     const uint32_t y = (uint32_t)(v * (h - 1));
+    PTC_CHECK(sc.faultSink, kFaultTexel, off + y * w + x, sc.nTexels);
     const uchar4 c = __ldg(&sc.texels[off + y * w + x]);
     float4 bgra = f4(over255((float)c.x), over255((float)c.y), over255((float)c.z), over255((float)c.w));
     bgra.w = 1.f - bgra.w;
@@ -51,6 +52,7 @@ __device__ __forceinline__ float4 texture_lookup_bilinear(const SceneDev &sc, ui
     const uint32_t x0 = (uint32_t)fx, y0 = (uint32_t)fy;
     const uint32_t x1 = x0 + 1 < w ? x0 + 1 : x0, y1 = y0 + 1 < h ? y0 + 1 : y0;
     const float ax = fx - (float)x0, ay = fy - (float)y0;
+    PTC_CHECK(sc.faultSink, kFaultTexel, off + y1 * w + x1, sc.nTexels);
     const uchar4 c00 = __ldg(&sc.texels[off + y0 * w + x0]), c10 = __ldg(&sc.texels[off + y0 * w + x1]);
     const uchar4 c01 = __ldg(&sc.texels[off + y1 * w + x0]), c11 = __ldg(&sc.texels[off + y1 * w + x1]);
     const float w00 = (1 - ax) * (1 - ay), w10 = ax * (1 - ay), w01 = (1 - ax) * ay, w11 = ax * ay;

@@ -226,6 +226,7 @@ __device__ __forceinline__ void lane_begin(TraceLane &L, const SceneDev &sc, con
 template <bool FAST>
 __device__ __forceinline__ void lane_node_step(TraceLane &L, const SceneDev &sc, uint32_t *stk, const int stride)
 {
+    PTC_CHECK(sc.faultSink, kFaultNodeIndex, L.cur, sc.nInner);
     const DevNode *nd = &sc.nodes[L.cur];
     float4 a, b, c, dd;
     ldg256(&nd->a, a, b);
@@ -251,6 +252,7 @@ __device__ __forceinline__ void lane_node_step(TraceLane &L, const SceneDev &sc,
     const bool both = hitL && hitR;
     const uint32_t nearRef = leftFirst ? refL : refR, farRef = leftFirst ? refR : refL;
     const uint32_t descend = both ? nearRef : (hitL ? refL : refR);
+    if (both) PTC_CHECK(sc.faultSink, kFaultStack, L.sp, sc.stackDepth);
     if (both) stk[L.sp * stride] = farRef;  // (prefetching the postponed child into L1 measured 2 % slower)
     L.sp += both ? 1 : 0;
     const uint32_t popped = stack_pop(L.sp, stk, stride, !(hitL || hitR));
@@ -261,6 +263,7 @@ template <bool ANY>
 __device__ __forceinline__ void lane_tri_step(TraceLane &L, const SceneDev &sc, const uint32_t *stk, const int stride)
 {
     const uint32_t i = (L.cur >> 4) & 0x7ffffffu;
+    PTC_CHECK(sc.faultSink, kFaultTriIndex, i, sc.nTriangles);
     const bool big = (L.cur & 15u) == 0u;
     if (big && L.te == 0u) L.te = i + __ldg(&sc.bigLeafCount[i]);  // rare: leaves of more than 15 triangles
     L.nt++;

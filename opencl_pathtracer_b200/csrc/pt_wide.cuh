@@ -66,9 +66,11 @@ struct WideLane
 #endif
     static constexpr int kMinCtas = PTC_WIDE_MIN_CTAS;  // 64 registers: 8 CTAs of 4 warps per SM
 #ifndef PTC_WIDE_MIN_CTAS_ANY
-#define PTC_WIDE_MIN_CTAS_ANY 8
+#define PTC_WIDE_MIN_CTAS_ANY 7
 #endif
-    static constexpr int kMinCtasAny = PTC_WIDE_MIN_CTAS_ANY;  // connect (its staging holds a light record and a shading normal besides the lane)
+    // connect: 72 registers, 7 CTAs per SM — its staging holds a light record and a shading normal besides the lane state; at 64
+    // registers it spilled 16-24 B in those cold paths. Spill-free it measures +0.3 % (165.0 vs 164.5 Msamples/s, profiles/r02_sweeps.txt)
+    static constexpr int kMinCtasAny = PTC_WIDE_MIN_CTAS_ANY;
     __device__ __forceinline__ void reset() { sp = -1; gy = ty = 0; nb = nt = 0; found = false; hitTri = -1; }
     __device__ __forceinline__ bool idle() const { return sp < 0; }
     __device__ __forceinline__ void set_idle() { sp = -1; }
@@ -172,6 +174,7 @@ __device__ __forceinline__ void lane_node_step(WideLane &L, const SceneDev &sc, 
     const uint32_t rest = hits & ~(1u << bit);
     const uint32_t rel = (uint32_t)__popc(hits & 0xffu & ((1u << slot) - 1u));
     const uint32_t node = L.gx + rel;
+    PTC_CHECK(sc.faultSink, kFaultNodeIndex, node, sc.nNodes8);
     const char *np = reinterpret_cast<const char *>(sc.nodes8 + node);
     uint4 n0, n1, n2, n3, n4, n5;
     ldg256(np, reinterpret_cast<float4 &>(n0), reinterpret_cast<float4 &>(n1));
@@ -182,7 +185,11 @@ __device__ __forceinline__ void lane_node_step(WideLane &L, const SceneDev &sc, 
         stk[0] = make_uint2(L.tx, L.ty);  // park the untested triangles (wants_node: the slot is free)
         L.oct |= WideLane::kPostponed;
     }
-    if (rest > 0x00ffffffu) stk[(L.sp + 1) * stride] = make_uint2(L.gx, rest);
+    if (rest > 0x00ffffffu)
+    {
+        PTC_CHECK(sc.faultSink, kFaultStack, L.sp + 1, sc.stackDepth);
+        stk[(L.sp + 1) * stride] = make_uint2(L.gx, rest);
+    }
     L.sp += rest > 0x00ffffffu ? 1 : 0;
     L.nb += 8;
 
@@ -262,6 +269,7 @@ __device__ __forceinline__ void lane_tri_step(WideLane &L, const SceneDev &sc, c
     const int bit = __ffs((int)L.ty) - 1;
     L.ty &= L.ty - 1u;
     const uint32_t i = L.tx + (uint32_t)bit;
+    PTC_CHECK(sc.faultSink, kFaultTriIndex, i, sc.nNodes8 * kTriSlots);
     L.nt++;
     float hs, ht, htp = 0.f;
     uint32_t hmat;

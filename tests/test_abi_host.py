@@ -140,7 +140,7 @@ def test_alone_writes_the_reference_bmp(tmp_path):
     files = sorted(f for f in os.listdir(out) if f.endswith(".bmp"))
     assert len(files) == 1, files
     got = open(os.path.join(out, files[0]), "rb").read()
-    sc = pt.Scene("cornell", w, h)
+    sc = pt.Scene("cornell", w, h, load_sky=True)  # the front-end loads the sky, as reference Alone/main.cpp:27 does
     with pt.PathTracerCUDA(w, h, ray_max_depth=depth, mode=pt.MODE_PARITY) as ctx:
         ctx.upload(sc)
         ctx.render(0, spp)
