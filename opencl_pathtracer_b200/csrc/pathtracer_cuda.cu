@@ -184,7 +184,7 @@ void ptc_destroy(ptc_ctx *ctx)
     ctx->nodes8.release(); ctx->tris8.release(); ctx->tri8Index.release();
     ctx->org.release(); ctx->dir.release(); ctx->thr.release(); ctx->rad.release(); ctx->hit.release();
     ctx->seed.release(); ctx->sample.release(); ctx->meta.release(); ctx->nbbx.release(); ctx->ntri.release();
-    ctx->occl.release(); ctx->queue[0].release(); ctx->queue[1].release(); ctx->qlit.release(); ctx->qother.release(); ctx->counters.release();
+    ctx->occl.release(); ctx->queue[0].release(); ctx->queue[1].release(); ctx->qpart.release(); ctx->tileLit.release(); ctx->counters.release();
     ctx->imgColor.release(); ctx->imgV.release(); ctx->imgRayNb.release(); ctx->rayDepths.release();
     ctx->rayBbx.release(); ctx->rayTri.release(); ctx->rgb8.release();
     if (ctx->ownStream && ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -335,7 +335,7 @@ int ptc_create(const ptc_config *config, ptc_ctx **out_ctx)
     const size_t n = c->capacity;
     A(c->org.alloc(n)); A(c->dir.alloc(n)); A(c->thr.alloc(n)); A(c->rad.alloc(n)); A(c->hit.alloc(n));
     A(c->seed.alloc(n)); A(c->sample.alloc(n)); A(c->meta.alloc(n)); A(c->nbbx.alloc(n)); A(c->ntri.alloc(n));
-    A(c->occl.alloc(n)); A(c->queue[0].alloc(n)); A(c->queue[1].alloc(n)); A(c->qlit.alloc(n)); A(c->qother.alloc(n)); A(c->counters.alloc(1));
+    A(c->occl.alloc(n)); A(c->queue[0].alloc(n)); A(c->queue[1].alloc(n)); A(c->qpart.alloc(n)); A(c->tileLit.alloc(n / 1024 + 1)); A(c->counters.alloc(1));
     A(c->imgColor.alloc(c->nPix)); A(c->imgRayNb.alloc(c->nPix));
     if (!(config->flags & PTC_FLAG_NO_VARIANCE)) A(c->imgV.alloc(c->nPix));
     A(c->rayDepths.alloc(kMaxBounces + 1)); A(c->rayBbx.alloc(PTC_MAX_INTERSECTION_NUMBER)); A(c->rayTri.alloc(PTC_MAX_INTERSECTION_NUMBER));
@@ -345,7 +345,7 @@ int ptc_create(const ptc_config *config, ptc_ctx **out_ctx)
         ptc_destroy(c);
         return fail(nullptr, PTC_ERR_CUDA, "%s", msg.c_str());
     }
-    c->st = PathState{c->org.p, c->dir.p, c->thr.p, c->rad.p, c->hit.p, c->seed.p, c->sample.p, c->meta.p, c->nbbx.p, c->ntri.p, c->occl.p, c->qlit.p, c->qother.p, (uint32_t)c->capacity};
+    c->st = PathState{c->org.p, c->dir.p, c->thr.p, c->rad.p, c->hit.p, c->seed.p, c->sample.p, c->meta.p, c->nbbx.p, c->ntri.p, c->occl.p, c->qpart.p, c->tileLit.p, (uint32_t)c->capacity, 0u};
 #ifdef PTC_CHECKED
     // self-test of the checked build: with a deliberately wrong bound every queue entry beyond slot 0 must be reported
     if (std::getenv("PTC_CHECKED_SELFTEST")) c->st.capacity = 1u;
@@ -645,6 +645,10 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
     {
         ctx->lc.stackDepth = (int)std::min<uint32_t>(32u, std::max<uint32_t>(4u, maxDepth + 1));
         if (ctx->wide) ctx->lc.stackDepth = (int)std::max<uint32_t>(3u, wideDepth + 2);  // the parked triangle group + one sibling group per level
+        // a tree too deep for one CTA's shared memory is refused here, with a message, not at the first launch with "invalid argument"
+        if (traverse_shared_bytes(ctx->wide, ctx->lc.stackDepth, true) > 227u * 1024u)
+            return fail(ctx, PTC_ERR_LIMIT, "BVH of %d levels: the traversal stacks (%zu bytes per CTA) exceed the 227 KB of shared memory", ctx->lc.stackDepth,
+                        traverse_shared_bytes(ctx->wide, ctx->lc.stackDepth, true));
         if (!std::getenv("PTC_CTAS_PER_SM"))
         {
             ctx->lc.traverseGrid = ctx->smCount * traverse_ctas_per_sm(ctx->fast, ctx->wide, ctx->lc.stackDepth, false);
@@ -652,6 +656,14 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
         }
     }
     sc.stackDepth = (uint32_t)ctx->lc.stackDepth;
+    // class-partitioned queues (k_classify): where the scene is small enough to live in L1 the traversal is cheap, shade is the
+    // largest stage and instruction bound, and class-uniform warps pay (+28 % samples/s on the Cornell box); on larger scenes shade
+    // is a DRAM-bound minority stage and the partition costs sector efficiency (-6 % on the 262 k-triangle atrium). FAST only: in PARITY
+    // every hit is lit, only misses would separate, and the pass costs more than it saves (Cornell PARITY 940 -> 900 Msamples/s).
+    // PTC_PARTITION=0/1 overrides.
+    ctx->lc.partition = ctx->fast && nT <= 4096u;
+    if (const char *e = std::getenv("PTC_PARTITION")) ctx->lc.partition = std::atoi(e) != 0;
+    ctx->st.partitioned = ctx->lc.partition ? 1u : 0u;
     ctx->sceneLoaded = true;
     ctx->sceneVersion++;  // device pointers and launch configuration may have changed: a captured batch graph is stale
     return PTC_OK;
@@ -694,6 +706,8 @@ int replicate_scene(ptc_ctx *dst, const ptc_ctx *src)
     dst->msGpuBuild = src->msGpuBuild;
     dst->lc.wide = src->lc.wide;
     dst->lc.stackDepth = src->lc.stackDepth;
+    dst->lc.partition = src->lc.partition;
+    dst->st.partitioned = src->st.partitioned;
     dst->lc.traverseGrid = dst->smCount * traverse_ctas_per_sm(dst->fast, dst->wide, dst->lc.stackDepth, false);  // also opts this device's kernels in to large stacks
     dst->lc.connectGrid = dst->smCount * traverse_ctas_per_sm(dst->fast, dst->wide, dst->lc.stackDepth, true);
     if (const char *env = std::getenv("PTC_CTAS_PER_SM")) dst->lc.traverseGrid = dst->lc.connectGrid = dst->smCount * std::max(1, std::atoi(env));
@@ -826,6 +840,12 @@ int runBatch(ptc_ctx *ctx, uint32_t first, uint32_t nIter, bool accumulate, int 
             StageTimer t(ctx, 1);
             launch_extend(s, ctx->lc, ctx->fast, ctx->sc, ctx->st, qin, cn, b);
         }
+        if (ctx->lc.partition)
+        {
+            StageTimer t(ctx, 3);  // charged to the shade stage, whose input it prepares
+            launch_classify(s, ctx->lc, ctx->st, qin, cn, b);
+            ctx->launches++;
+        }
         if (ctx->sc.nLights)
         {
             StageTimer t(ctx, 2);
@@ -835,7 +855,7 @@ int runBatch(ptc_ctx *ctx, uint32_t first, uint32_t nIter, bool accumulate, int 
         }
         {
             StageTimer t(ctx, 3);
-            launch_shade(s, ctx->lc, ctx->fast, ctx->sc, fp, ctx->st, qout, cn, b);
+            launch_shade(s, ctx->lc, ctx->fast, ctx->sc, fp, ctx->st, qin, qout, cn, b);
         }
         ctx->launches += 2;
         ctx->launchesExtend++;

@@ -91,7 +91,7 @@ struct ptc_ctx
     ptc::DevBuf<float4> org, dir, thr, rad, hit;
     ptc::DevBuf<int> seed;
     ptc::DevBuf<float2> sample;
-    ptc::DevBuf<uint32_t> meta, nbbx, ntri, occl, queue[2], qlit, qother;
+    ptc::DevBuf<uint32_t> meta, nbbx, ntri, occl, queue[2], qpart, tileLit;
     ptc::PathState st{};
     ptc::DevBuf<ptc::Counters> counters;
 

@@ -120,11 +120,13 @@ struct PathState
     uint32_t *nbbx;   // numIntersectedBBx (camera ray + its shadow rays)
     uint32_t *ntri;   // numIntersectedTri
     uint32_t *occl;   // bit i = light i occluded at the current hit
-    // class queues of the current bounce, filled by extend as its rays finish: paths whose hit reads the direct light (connect +
-    // the lit half of shade) and the others (misses; FAST: hits on glass / water, which never read it)
-    uint32_t *qlit;
-    uint32_t *qother;
+    // the queue of the current bounce re-written by k_classify with every tile of 1024 entries partitioned: the paths whose hit reads
+    // the direct light first (connect + the lit half of shade), then the others (misses; FAST: hits on glass / water, which never
+    // read it); tileLit[tile] = lit entries of the tile
+    uint32_t *qpart;
+    uint32_t *tileLit;
     uint32_t capacity;  // path slots (bound of every queue entry; CHECKED build)
+    uint32_t partitioned;  // connect and shade draw from qpart (LaunchCfg::partition)
 };
 
 // queue / cursor block, one set per bounce so nothing has to be reset inside a batch
@@ -134,8 +136,6 @@ struct Counters
     uint32_t qcount[kMaxBounces + 1];     // live paths entering bounce b
     uint32_t curExtend[kMaxBounces + 1];  // work cursors of the persistent kernels
     uint32_t curConnect[kMaxBounces + 1];
-    uint32_t qlit[kMaxBounces + 1];       // lengths of the class queues of bounce b
-    uint32_t qother[kMaxBounces + 1];
     unsigned long long extensionRays, shadowRays, boxTests, triTests, paths;
     unsigned long long extBoxTests, extTriTests;  // share of boxTests / triTests spent by closest-hit rays
     uint32_t faults;        // CHECKED build: bit c set = check c failed somewhere (codes below); always 0 in the normal build

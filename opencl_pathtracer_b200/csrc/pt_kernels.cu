@@ -28,6 +28,11 @@ constexpr int kStreamThreads = 256;
 #define PTC_SHADE_MIN_BLOCKS 4  // k_shade: 4 CTAs of 8 warps per SM = 64 registers (A/B: scripts/build_variant.sh shade3 -DPTC_SHADE_MIN_BLOCKS=3)
 #endif
 
+// the partitioned queue of a bounce (k_classify below): tiles of 1024 entries, the lit ones first
+constexpr int kClassifyItems = 4;                                  // consecutive queue entries per thread of k_classify
+constexpr uint32_t kClassTile = kStreamThreads * kClassifyItems;   // 1024
+__device__ __forceinline__ bool entry_is_lit(const PathState &st, uint32_t k) { return (k & (kClassTile - 1u)) < st.tileLit[k / kClassTile]; }
+
 // ------------------------------------------------------------------------------------------------ reset
 __global__ void k_reset(Counters *cn, uint32_t nPaths)
 {
@@ -37,8 +42,6 @@ __global__ void k_reset(Counters *cn, uint32_t nPaths)
         cn->qcount[i] = i == 0 ? nPaths : 0u;
         cn->curExtend[i] = 0;
         cn->curConnect[i] = 0;
-        cn->qlit[i] = 0;
-        cn->qother[i] = 0;
     }
 }
 
@@ -176,8 +179,9 @@ __global__ void __launch_bounds__(kTraverseThreads, (ANY ? LaneT::kMinCtasAny : 
     const unsigned full = 0xffffffffu;
     const int voteNode = (int)((popMin >> 8) & 0xffu), voteTri = (int)((popMin >> 16) & 0xffu);  // in eighths of the warp's rays
     popMin &= 0xffu;
-    const uint32_t count = ANY ? cn->qlit[bounce] : cn->qcount[bounce];  // connect draws from the lit class queue extend has filled
-    if (ANY) queue = st.qlit;
+    const uint32_t count = cn->qcount[bounce];
+    const bool partitioned = ANY && st.partitioned;
+    if (partitioned) queue = st.qpart;  // connect draws from the partitioned queue (k_classify): an entry's class follows from its position
     const uint32_t nL = ANY ? sc.nLights : 1u;
     const uint32_t total = ANY ? count : count * nL;  // work items drawn from the cursor: paths (connect draws groups of 32 paths)
     uint32_t *cursor = ANY ? &cn->curConnect[bounce] : &cn->curExtend[bounce];
@@ -215,18 +219,6 @@ __global__ void __launch_bounds__(kTraverseThreads, (ANY ? LaneT::kMinCtasAny : 
                 if (L.hitTri < 0) flags = kOcclMiss;
                 else if (FAST && !(hmat == 0u || hmat == 3u)) flags = kOcclUnlit;  // GLASS / WATER / METAL / UNKNOWN never read the direct light (:805-843)
                 st.occl[p] = flags;
-                // the path joins the class queue of this bounce that the later stages draw from: lit hits -> connect and the lit half
-                // of shade; everything else -> the other half. One atomic per class for the lanes that finish together.
-                const bool lit = flags == 0u;
-                const unsigned act = __activemask();
-                const unsigned ml = __ballot_sync(act, lit);
-                const unsigned mine = lit ? ml : (act & ~ml);
-                const int leader = __ffs((int)mine) - 1;
-                uint32_t base = 0;
-                if ((int)lane == leader) base = atomicAdd(lit ? &cn->qlit[bounce] : &cn->qother[bounce], (uint32_t)__popc(mine));
-                base = __shfl_sync(mine, base, leader);
-                PTC_CHECK(cn, kFaultQueueAppend, base + (uint32_t)__popc(mine & lt), st.capacity);
-                (lit ? st.qlit : st.qother)[base + (uint32_t)__popc(mine & lt)] = p;
             }
             else
             {
@@ -291,7 +283,7 @@ __global__ void __launch_bounds__(kTraverseThreads, (ANY ? LaneT::kMinCtasAny : 
                         {
                             pp = queue ? queue[k] : k;
                             PTC_CHECK(cn, kFaultQueueItem, pp, st.capacity);
-                            lit = !(st.occl[pp] & (kOcclUnlit | kOcclMiss));
+                            lit = partitioned ? entry_is_lit(st, k) : !(st.occl[pp] & (kOcclUnlit | kOcclMiss));
                         }
                         if (lit)
                         {
@@ -403,12 +395,91 @@ __global__ void __launch_bounds__(kTraverseThreads, (ANY ? LaneT::kMinCtasAny : 
     flush_work(cn, ANY ? &cn->shadowRays : &cn->extensionRays, lane == 0 ? nRays : 0u, (COUNT || lane == 0) ? nbSum : 0u, (COUNT || lane == 0) ? ntSum : 0u);
 }
 
+// ------------------------------------------------------------------------------------------------ classify
+// Between extend and connect: the queue of the bounce is re-written tile by tile (1024 entries) with every tile PARTITIONED —
+// first the paths whose hit reads the direct light (connect + the lit copy of shade), then the others (misses; FAST: hits on
+// glass / water) — by the flags extend left in st.occl; tileLit[tile] = how many of the tile are lit. Later stages take the class
+// of an entry from its position: warps are class-uniform except the one that straddles a tile's boundary.
+// Why tile-local: ORDER MATTERS. Path slots in a queue ascend (the compaction of k_shade keeps them so within an L2-sized window),
+// and the 112 bytes of state per path stream from HBM in that order. Two global class queues — whether appended to by extend in
+// the order rays finish, or split off by a pass like this one with one atomic per tile — concatenate ascending sequences, bounce
+// after bounce, into ever sparser sweeps of the slot range: k_shade went from 1.9 ms to 2.9 ms per launch by bounce 9, and its
+// DRAM traffic up by 50 % (profiles/r02_sweeps.txt, r02_ncu_shade_*). A partition inside the tile moves no entry by more than 1023
+// places, needs no atomic and no scan across tiles, and is deterministic.
+
+__global__ void __launch_bounds__(kStreamThreads) k_classify(PathState st, const uint32_t *__restrict__ queue, Counters *__restrict__ cn, int bounce)
+{
+    __shared__ uint32_t sWarp[kStreamThreads / 32];
+    __shared__ uint32_t sTotal;
+    const uint32_t count = cn->qcount[bounce];
+    const uint32_t nTiles = (count + kClassTile - 1) / kClassTile;
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    for (uint32_t tile = blockIdx.x; tile < nTiles; tile += gridDim.x)
+    {
+        uint32_t p[kClassifyItems];
+        uint32_t litMask = 0, valid = 0;
+#pragma unroll
+        for (int j = 0; j < kClassifyItems; j++)
+        {
+            const uint32_t k = tile * kClassTile + threadIdx.x * kClassifyItems + j;
+            p[j] = 0;
+            if (k < count)
+            {
+                p[j] = queue ? queue[k] : k;
+                valid |= 1u << j;
+                if (!(st.occl[p[j]] & (kOcclUnlit | kOcclMiss))) litMask |= 1u << j;
+            }
+        }
+        const uint32_t nLit = (uint32_t)__popc(litMask);
+        const uint32_t nValid = (uint32_t)__popc(valid);
+        // exclusive prefix of the lit counts over the CTA's threads (entries of a thread are consecutive: the order is kept)
+        uint32_t inc = nLit;
+        for (int o = 1; o < 32; o <<= 1)
+        {
+            const uint32_t a = __shfl_up_sync(0xffffffffu, inc, o);
+            if ((int)lane >= o) inc += a;
+        }
+        if (lane == 31u) sWarp[warp] = inc;
+        __syncthreads();
+        if (warp == 0)
+        {
+            uint32_t a = lane < kStreamThreads / 32 ? sWarp[lane] : 0u;
+            const uint32_t own = a;
+            for (int o = 1; o < 32; o <<= 1)
+            {
+                const uint32_t x = __shfl_up_sync(0xffffffffu, a, o);
+                if ((int)lane >= o) a += x;
+            }
+            if (lane < kStreamThreads / 32) sWarp[lane] = a - own;
+            if (lane == kStreamThreads / 32 - 1)
+            {
+                sTotal = a;
+                st.tileLit[tile] = a;
+            }
+        }
+        __syncthreads();
+        const uint32_t litBefore = sWarp[warp] + inc - nLit;                       // lit entries of the tile before this thread's
+        const uint32_t before = threadIdx.x * kClassifyItems;                       // entries of the tile before this thread's (only the last
+        (void)nValid;                                                               // tile is ragged, and its missing entries are at the end)
+        uint32_t posLit = tile * kClassTile + litBefore;
+        uint32_t posOther = tile * kClassTile + sTotal + (before - litBefore);
+#pragma unroll
+        for (int j = 0; j < kClassifyItems; j++)
+        {
+            if (!((valid >> j) & 1u)) continue;
+            if ((litMask >> j) & 1u) st.qpart[posLit++] = p[j];
+            else st.qpart[posOther++] = p[j];
+        }
+        __syncthreads();
+    }
+}
+
 // ------------------------------------------------------------------------------------------------ shade
-// One path of the shade stage. CLASS 0: a hit that reads the direct light (the lit class queue: every hit in PARITY, MAT_STANDART /
-// MAT_VARNHISHED hits in FAST); CLASS 1: the others (misses; FAST: hits on glass / water / unknown materials, whose direct light
-// is never read, K.cl:805-843). The class is a compile-time constant, so each copy carries only the branches its class can take:
-// the lit copy has no sky and, in FAST, no Fresnel transmission; the other copy has no light loop and no cosine sampling. Returns
-// whether the path goes on to the next bounce.
+// One path of the shade stage. CLASS 0: a hit that reads the direct light (every hit in PARITY, MAT_STANDART / MAT_VARNHISHED hits
+// in FAST); CLASS 1: the others (misses; FAST: hits on glass / water / unknown materials, whose direct light is never read,
+// K.cl:805-843); CLASS 2: any path (the queue is not partitioned, see k_classify). The class is a compile-time constant, so the
+// class copies carry only the branches their class can take: the lit copy has no sky and, in FAST, no Fresnel transmission; the
+// other copy has no light loop and no cosine sampling. Returns whether the path goes on to the next bounce.
 template <int FAST, int CLASS>
 __device__ __forceinline__ bool shade_path(const SceneDev &sc, const FrameParams &fp, const PathState &st, const uint32_t p)
 {
@@ -425,7 +496,7 @@ __device__ __forceinline__ bool shade_path(const SceneDev &sc, const FrameParams
         st.rad[p] = rad + emitted * T;
         return false;
     }
-    if (CLASS == 1 && tri < 0)
+    if (CLASS != 0 && tri < 0)
     {
         // :1281-1288 sky
         st.rad[p] = rad + sky_color(sc, d) * T;
@@ -464,7 +535,7 @@ __device__ __forceinline__ bool shade_path(const SceneDev &sc, const FrameParams
     const float4 Ns = shading_normal(sh, N, d, s, t);
     // :901-954 direct illumination from the occlusion bits the connect stage left
     float4 L = f4(0, 0, 0, 0);
-    if (CLASS == 0)
+    if (CLASS == 0 || (CLASS == 2 && (!FAST || litType)))
     {
         const uint32_t occl = st.occl[p] & kOcclMask;
         for (uint32_t li = 0; li < sc.nLights; li++)
@@ -491,7 +562,7 @@ __device__ __forceinline__ bool shade_path(const SceneDev &sc, const FrameParams
     bool diffuseBounce = false;
     bool specular = mat.type == 1 || mat.type == 2;  // only read by the area-light variant
     // which material branches this copy can reach: PARITY's lit class holds every material, FAST's only the two lit ones
-    const bool mayBeLit = CLASS == 0, mayBeUnlit = CLASS == 1 || !FAST;
+    const bool mayBeLit = CLASS != 1, mayBeUnlit = CLASS != 0 || !FAST;
     if (mayBeLit && mat.type == 0)
     {
         T = T * color;
@@ -526,7 +597,6 @@ __device__ __forceinline__ bool shade_path(const SceneDev &sc, const FrameParams
         if (rng_next(seed) < rF) { out = d - (Ns * (2 * dot4(d, Ns))); specular = true; }
         else { diffuseBounce = true; T = T * color; }
     }
-    (void)litType;
     if (mayBeLit && diffuseBounce) out = cosine_sample_hemisphere(seed, Ns);
     put_in_same_hemisphere(out, Nref);
     rad = rad + add;
@@ -535,7 +605,7 @@ __device__ __forceinline__ bool shade_path(const SceneDev &sc, const FrameParams
     st.org[p] = q + 0.001f * out;  // :880
     st.dir[p] = normalize4(out);
     st.thr[p] = T;
-    if (CLASS == 0) st.rad[p] = rad;  // the other class adds nothing to the radiance at a hit
+    if (CLASS != 1) st.rad[p] = rad;  // the other class adds nothing to the radiance at a hit
     st.seed[p] = seed;
     st.meta[p] = meta;
     // :1294-1304 and the loop condition :1248
@@ -559,16 +629,20 @@ __device__ __forceinline__ bool shade_path(const SceneDev &sc, const FrameParams
     return alive;
 }
 
-// Both class queues of the bounce in one launch: the lit queue is padded to a multiple of 32 in the index space, so every warp
-// shades paths of one class and runs one copy of shade_path (round 1's single mixed queue ran 16 of 32 lanes and waited on
-// instruction fetch: 3,200 SASS lines touched by every warp). Survivors of both classes are appended to the next bounce's queue.
-template <int FAST>  // as k_trace
-__global__ void __launch_bounds__(kStreamThreads, PTC_SHADE_MIN_BLOCKS) k_shade(SceneDev sc, FrameParams fp, PathState st, uint32_t *__restrict__ qout,
-                                                         Counters *__restrict__ cn, int bounce)
+// PART: the queue was partitioned by k_classify and an entry's class follows from its position, so a warp runs ONE class copy of
+// shade_path (the warp that straddles a tile's class boundary runs both); else the bounce's own queue with the generic copy, lanes
+// diverging by material as in the reference's megakernel. Both classes go through the SAME launch in queue order because the
+// survivors are appended to the next bounce's queue in the order warps get here: two launches (or two class queues) append class
+// after class, and every bounce then doubles the number of ascending runs the queue is made of.
+// Which one pays is decided per scene (LaunchCfg::partition): class-uniform warps execute 29 % fewer instructions at 21.9 instead of
+// 16 lanes, but the stage streams 112 B of path state per path and the partition costs sector efficiency — lit warps read slot
+// runs with holes, the others sparse ones: +25 % DRAM sectors. Cornell box (shade is 45 % of a step, instruction bound): 1,036 ->
+// 1,322 Msamples/s. Atrium (shade 16 %, DRAM bound at 4.6 TB/s on bounce 0): 164.5 -> 153.6. (profiles/r02_sweeps.txt)
+template <int FAST, bool PART>  // FAST as k_trace
+__global__ void __launch_bounds__(kStreamThreads, PTC_SHADE_MIN_BLOCKS) k_shade(SceneDev sc, FrameParams fp, PathState st, const uint32_t *__restrict__ qin,
+                                                                            uint32_t *__restrict__ qout, Counters *__restrict__ cn, int bounce)
 {
-    const uint32_t nLit = cn->qlit[bounce], nOther = cn->qother[bounce];
-    const uint32_t nLitPad = (nLit + 31u) & ~31u;
-    const uint32_t count = nLitPad + nOther;
+    const uint32_t count = cn->qcount[bounce];
     const uint32_t stride = blockDim.x * gridDim.x;
     const uint32_t rounds = (count + stride - 1) / stride;
     for (uint32_t it = 0; it < rounds; it++)
@@ -576,18 +650,19 @@ __global__ void __launch_bounds__(kStreamThreads, PTC_SHADE_MIN_BLOCKS) k_shade(
         const uint32_t k = it * stride + blockIdx.x * blockDim.x + threadIdx.x;
         bool alive = false;
         uint32_t p = 0;
-        if (k < nLitPad)
+        if (k < count)
         {
-            if (k < nLit)
+            if (PART)
             {
-                p = st.qlit[k];
-                alive = shade_path<FAST, 0>(sc, fp, st, p);
+                p = st.qpart[k];
+                if (entry_is_lit(st, k)) alive = shade_path<FAST, 0>(sc, fp, st, p);
+                else alive = shade_path<FAST, 1>(sc, fp, st, p);
             }
-        }
-        else if (k - nLitPad < nOther)
-        {
-            p = st.qother[k - nLitPad];
-            alive = shade_path<FAST, 1>(sc, fp, st, p);
+            else
+            {
+                p = qin ? qin[k] : k;
+                alive = shade_path<FAST, 2>(sc, fp, st, p);
+            }
         }
         // warp-aggregated append of the survivors to the next bounce's queue
         const unsigned m = __ballot_sync(0xffffffffu, alive);
@@ -885,6 +960,8 @@ static int occupancy_of(size_t bytes)
     return n < m ? n : m;
 }
 
+size_t traverse_shared_bytes(bool wide, int stackDepth, bool any) { return stack_bytes(wide, stackDepth, any); }
+
 int traverse_ctas_per_sm(bool fast, bool wide, int stackDepth, bool any)
 {
     if (const char *e = std::getenv("PTC_CARVEOUT"))  // experiment: shared-memory carve-out in percent (what is left is L1)
@@ -942,12 +1019,24 @@ void launch_connect(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneD
     launch_trace<true>(s, lc, fast, sc, st, queue, cn, bounce);
 }
 
-void launch_shade(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const FrameParams &fp, const PathState &st,
-                  uint32_t *qout, Counters *cn, int bounce)
+void launch_classify(cudaStream_t s, const LaunchCfg &lc, const PathState &st, const uint32_t *queue, Counters *cn, int bounce)
 {
-    if (fast && sc.areaJump != 1u) k_shade<2><<<lc.streamGrid, kStreamThreads, 0, s>>>(sc, fp, st, qout, cn, bounce);
-    else if (fast) k_shade<1><<<lc.streamGrid, kStreamThreads, 0, s>>>(sc, fp, st, qout, cn, bounce);
-    else k_shade<0><<<lc.streamGrid, kStreamThreads, 0, s>>>(sc, fp, st, qout, cn, bounce);
+    k_classify<<<lc.streamGrid, kStreamThreads, 0, s>>>(st, queue, cn, bounce);
+}
+
+void launch_shade(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const FrameParams &fp, const PathState &st,
+                  const uint32_t *qin, uint32_t *qout, Counters *cn, int bounce)
+{
+#define PTC_SHADE(MODE)                                                                                                    \
+    do                                                                                                                     \
+    {                                                                                                                      \
+        if (lc.partition) k_shade<MODE, true><<<lc.streamGrid, kStreamThreads, 0, s>>>(sc, fp, st, qin, qout, cn, bounce); \
+        else k_shade<MODE, false><<<lc.streamGrid, kStreamThreads, 0, s>>>(sc, fp, st, qin, qout, cn, bounce);             \
+    } while (0)
+    if (fast && sc.areaJump != 1u) PTC_SHADE(2);
+    else if (fast) PTC_SHADE(1);
+    else PTC_SHADE(0);
+#undef PTC_SHADE
 }
 
 void launch_accumulate(cudaStream_t s, const LaunchCfg &lc, const FrameParams &fp, const PathState &st, const ImageDev &img,

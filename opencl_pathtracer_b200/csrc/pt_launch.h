@@ -13,9 +13,12 @@ struct LaunchCfg
     uint32_t refillMin;  // idle lanes of a warp that trigger a refill from the work cursor (1..32)
     int stackDepth;      // traversal stack entries per thread (BVH depth + 1, at most kStackDepth)
     bool wide;           // FAST mode: traverse the 8-wide compressed BVH (stackDepth then counts 8-byte entries)
+    bool partition;      // k_classify partitions every bounce's queue by class; connect and shade take classes from positions (decided per
+                         // scene at upload: pays where shade is instruction bound, costs where it is DRAM bound — k_shade in pt_kernels.cu)
     bool count;          // per-ray work counters + the two 5000-bin histograms (PARITY always; FAST with PTC_FLAG_WORK_COUNTERS)
 };
 
+size_t traverse_shared_bytes(bool wide, int stackDepth, bool any);  // dynamic shared memory of one traversal CTA (stacks + ray staging)
 int traverse_ctas_per_sm(bool fast, bool wide, int stackDepth, bool any);  // resident CTAs per SM of the extend (any = false) / connect kernel
 
 void launch_reset(cudaStream_t s, Counters *cn, uint32_t nPaths);
@@ -27,9 +30,12 @@ void launch_extend(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDe
                    Counters *cn, int bounce);
 void launch_connect(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const PathState &st, const uint32_t *queue,
                     Counters *cn, int bounce);
-// shades both class queues of the bounce (PathState::qlit / qother, filled by extend) and appends the survivors to qout
+// re-writes the queue of the bounce into PathState::qpart with every 1024-entry tile partitioned lit / other (after extend: it reads
+// the flags extend left)
+void launch_classify(cudaStream_t s, const LaunchCfg &lc, const PathState &st, const uint32_t *queue, Counters *cn, int bounce);
+// shades the bounce's queue — qin, or PathState::qpart when LaunchCfg::partition — in queue order and appends the survivors to qout
 void launch_shade(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev &sc, const FrameParams &fp, const PathState &st,
-                  uint32_t *qout, Counters *cn, int bounce);
+                  const uint32_t *qin, uint32_t *qout, Counters *cn, int bounce);
 void launch_accumulate(cudaStream_t s, const LaunchCfg &lc, const FrameParams &fp, const PathState &st, const ImageDev &img,
                        Counters *cn);
 // batch graphs: host stubs of k_generate(fp, cam, st) and k_accumulate(fp, st, img, cn), to find their nodes in a captured graph

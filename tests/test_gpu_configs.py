@@ -99,7 +99,10 @@ def test_c3_full_size_radiance_with_classified_mismatches(ptref, scene_factory):
             n = {k: len(v) for k, v in classes.items()}
             print("C3 1080p it=%d: %d of %d pixels outside 1e-3 (%.4f %%), bit-identical pixels %.2f %%; of %d offenders walked: %s"
                   % (it, bad.sum(), bad.size, 100 * bad.mean(), 100 * exact, len(pick), n))
-            assert bad.mean() <= 2e-3, "fraction of pixels whose path diverged too large: %g" % bad.mean()
+            # measured (round 2, oracle cos / sin correctly rounded): 0 of 2,073,600 pixels outside the band, 100.00 % bit-identical.
+            # The bound leaves room for the double-rounding cases of cos / sin (two double libms, ~2^-27 per call).
+            assert bad.mean() <= 1e-5, "fraction of pixels whose path diverged too large: %g" % bad.mean()
+            assert exact >= 0.99999
             assert n["hit"] == 0 and n["other"] == 0 and n["same_path"] == 0, "unexplained radiance mismatches: %s" % {k: v[:5] for k, v in classes.items() if k != "cos_sin"}
             # a control group of agreeing pixels: their paths must be the reference's ray for ray or differ in last bits only
             ok = np.flatnonzero(~bad)
@@ -125,11 +128,18 @@ def test_c1_cornell_512_16spp(ptref, scene_factory):
         rmse = np.sqrt(((color[..., :3].astype(np.float64) - ref["imageColor"][..., :3]) ** 2).mean())
         moved = np.abs(d.astype(np.int64) - ref["rayDepths"].astype(np.int64)).sum() / (w * h * spp)
         print("C1 512x512 16 spp %s: RMSE / mean = %.3g, paths that changed depth bin %.3g" % (label, rmse / mean, moved))
-        assert rmse / mean <= 1e-3
-        assert d.sum() == ref["rayDepths"].sum() == w * h * spp and moved <= 2e-3
-        if mode == pt.MODE_PARITY:  # the work histograms are the reference's up to the paths that diverged on a last-bit direction
-            assert b.sum() == ref["rayIntersectedBBx"].sum() and t.sum() == ref["rayIntersectedTri"].sum()
-            assert np.abs(b.astype(np.int64) - ref["rayIntersectedBBx"].astype(np.int64)).sum() <= 4e-3 * w * h * spp
+        assert d.sum() == ref["rayDepths"].sum() == w * h * spp
+        if mode == pt.MODE_PARITY:
+            # measured: RMSE 0 — with cos / sin correctly rounded on both sides PARITY reproduces the reference kernel bit for bit
+            assert rmse / mean <= 1e-6 and moved == 0
+            assert np.array_equal(color.view(np.uint32), ref["imageColor"].view(np.uint32)), "PARITY accumulators are not the reference's bits"
+            assert np.array_equal(d, ref["rayDepths"]) and np.array_equal(b, ref["rayIntersectedBBx"]) and np.array_equal(t, ref["rayIntersectedTri"])
+        else:
+            # FAST (measured 1.4e-3, 2e-4 of the paths change their depth bin): inside the unit-sized neighbourhood of the box's edges
+            # the REFERENCE loses the nearer wall — it culls a box by comparing a linear entry distance with a squared hit distance
+            # (K.cl:135) — and FAST, whose cull is a squared distance in both uses, finds it
+            # (tests/test_gpu_parity.py::test_fast_bounce_like_rays reports the classes on the Cornell box too)
+            assert rmse / mean <= 3e-3 and moved <= 1e-3
 
 
 def _hash(a):
@@ -173,7 +183,7 @@ def test_c4_scene_primary_hits_and_radiance(ptref):
             classes = classify_divergence(ptref, sc, r, cw, ch, depth, it, np.flatnonzero(bad)[:200])
             n = {k: len(v) for k, v in classes.items()}
             print("C4 scene 512x288 it=%d: %d of %d pixels outside 1e-3 (%.4f %%); offenders walked: %s" % (it, bad.sum(), bad.size, 100 * bad.mean(), n))
-            assert bad.mean() <= 2e-3
+            assert bad.mean() <= 1e-4  # measured 0
             assert n["hit"] == 0 and n["other"] == 0 and n["same_path"] == 0, {k: v[:5] for k, v in classes.items() if k != "cos_sin"}
         prim = r.trace_primary(0)
         sky = (prim["hit"] < 0).sum()

@@ -70,7 +70,8 @@ def test_single_sample_radiance(ptref, scene_factory, name, w, h, sky, depth):
         print("%s it=%d depth=%d: %d / %d pixels outside 1e-3 (%.4f %%), exact-equal %.2f %%" %
               (name, it, depth, bad.sum(), bad.size, 100 * frac, 100 * (got.view(np.uint32) == ref.view(np.uint32)).all(axis=-1).mean()))
         assert np.isfinite(got).all()
-        assert frac <= 2e-3, "fraction of pixels whose path diverged (fp ties / libm ulps) too large: %g" % frac
+        # measured since the oracle's cos / sin are the correctly rounded ones (oracle/shim/ocl_as_cxx.h): 0 pixels, every pixel bit-identical
+        assert frac <= 1e-4, "fraction of pixels whose path diverged too large: %g" % frac
 
 
 def test_accumulated_image_and_statistics(ptref, scene_factory):
@@ -91,7 +92,7 @@ def test_accumulated_image_and_statistics(ptref, scene_factory):
         mean = ref["imageColor"][..., :3].mean()
         rmse = np.sqrt(((color[..., :3] - ref["imageColor"][..., :3]) ** 2).mean())
         print("batch", batch, "rmse/mean", rmse / mean, "depth hist", d.tolist(), ref["rayDepths"].tolist())
-        assert rmse / mean < 2e-3
+        assert rmse / mean <= 1e-3  # BASELINE.md section 4 (measured 0: PARITY reproduces the reference's bits)
         # histograms: equal up to the handful of paths that diverged on a tie
         assert d.sum() == ref["rayDepths"].sum() == w * h * spp
         assert np.abs(d.astype(np.int64) - ref["rayDepths"].astype(np.int64)).sum() <= 2e-3 * w * h * spp
@@ -293,7 +294,7 @@ def test_bounce_like_rays_bit_exact(ptref, scene_factory, name, sky):
 
 
 @pytest.mark.parametrize("flags,label", [(pt.FLAG_BVH2, "BVH2"), (0, "wide BVH8")])
-@pytest.mark.parametrize("name,sky", [("gallery", True), ("atrium:4", False), ("atrium:16", False)])
+@pytest.mark.parametrize("name,sky", [("gallery", True), ("atrium:4", False), ("atrium:16", False), ("cornell", False)])
 def test_fast_bounce_like_rays(scene_factory, name, sky, flags, label):
     """FAST against PARITY on 200k surface rays. A FAST hit may differ from PARITY's only
       (a) between candidates at the same distance (tie, broken by test order);
