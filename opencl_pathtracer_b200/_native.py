@@ -37,6 +37,7 @@ class SceneView(C.Structure):
                 ("materiaux_size", C.c_uint32), ("textures_size", C.c_uint32), ("textures_data_size", C.c_uint32), ("reserved", C.c_uint32),
                 ("bvh", C.c_void_p), ("triangulation", C.c_void_p), ("lights", C.c_void_p), ("materiaux", C.c_void_p),
                 ("textures", C.c_void_p), ("textures_data", C.c_void_p), ("sky", C.c_void_p),
+                ("_align16", C.c_uint64),  # ptc_float4 is 16-byte aligned in C (include/pathtracer_structs.h); ctypes aligns a float struct to 4
                 ("camera_position", Float4), ("camera_direction", Float4), ("camera_right", Float4), ("camera_up", Float4)]
 
 

@@ -29,9 +29,17 @@ def test_library_exports_every_declared_symbol():
     assert lib.ptc_version().decode().startswith("PathTracer_CUDA")
 
 
-def test_abi_struct_sizes():
-    assert C.sizeof(N.Config) == 48 and C.sizeof(N.SceneView) == 32 + 7 * 8 + 64
-    assert C.sizeof(N.Counters) == 17 * 8
+def test_abi_struct_sizes(tmp_path):
+    """The ctypes mirrors have the sizes the C header gives its structs (the header compiled as plain C)."""
+    assert C.sizeof(N.Config) == 48 and C.sizeof(N.SceneView) == 32 + 7 * 8 + 8 + 64
+    assert C.sizeof(N.Counters) == 17 * 8 + 4 * 4
+    src = tmp_path / "sizes.c"
+    src.write_text('#include <stdio.h>\n#include "pathtracer_cuda.h"\nint main(void){printf("%zu %zu %zu %zu %zu\\n", sizeof(ptc_config), sizeof(ptc_scene_view), '
+                   'sizeof(ptc_counters), sizeof(ptc_device_buffers), sizeof(ptc_wide_bvh)); return 0;}\n')
+    exe = tmp_path / "sizes"
+    subprocess.run(["gcc", "-std=c99", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    got = [int(x) for x in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
+    assert got == [C.sizeof(N.Config), C.sizeof(N.SceneView), C.sizeof(N.Counters), C.sizeof(N.DeviceBuffers), C.sizeof(N.WideBvh)], got
 
 
 def test_no_cpu_fallback():
