@@ -281,6 +281,23 @@ PTC_API int ptc_render_single(ptc_ctx *ctx, uint32_t iteration, float *radiance)
  * path that ended earlier keeps its last state). Any pointer may be NULL. Does not touch the accumulators. */
 PTC_API int ptc_path_probe(ptc_ctx *ctx, uint32_t iteration, uint32_t bounces, float *origin, float *direction, float *hit, uint32_t *meta);
 
+/* ptc_trace_rays without device allocation. NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * ptc_trace_rays allocates and frees seven device buffers per call; this entry point runs the same kernels with ALL of its
+ * scratch — staged rays, the extend kernel's path-state records and queue counters, staged outputs — inside one file-scope
+ * `static __device__` array of PTC_STATIC_SCRATCH_BYTES (opencl_pathtracer_b200/csrc/pt_static.cu), which every GPU that loads
+ * the library holds until the process exits. It calls no cudaMalloc / cudaFree / allocating library routine.
+ *   - n > PTC_STATIC_MAX_RAYS is refused with PTC_ERR_LIMIT (ptc_last_error names the limit); split the batch or use ptc_trace_rays.
+ *   - origin, direction and the outputs may be host OR device pointers (copied with cudaMemcpyDefault on the context's stream);
+ *     meaning and layout as ptc_trace_rays (no `dir` output); any output may be NULL. Results are bit-identical to ptc_trace_rays.
+ *   - Every call on a device shares the array, whatever the context; it keeps the last call's contents and the entry point clears
+ *     what must start at zero. Calls that overlap on the GPU (two host threads, two contexts with their own streams) RACE: serialise
+ *     them. The call returns after the context's stream has drained. Does not touch the accumulators. */
+#define PTC_STATIC_MAX_RAYS 32768u
+#define PTC_STATIC_SCRATCH_BYTES (4u << 20)
+PTC_API int ptc_trace_rays_static(ptc_ctx *ctx, uint32_t n, const float *origin, const float *direction, int32_t *hit, float *st,
+                                  float *dist2, uint32_t *counts);
+
 /* Host utility: the 8-wide compressed BVH that ptc_upload_scene collapses the reference BVH2 into in FAST mode
  * (opencl_pathtracer_b200/csrc/pt_wide_build.cu), exposed for inspection and structural tests. nodes = n_nodes records of
  * 80 bytes (DevNode8, csrc/pt_wide.cuh); tri_order has n_triangles = 24 * n_nodes entries: entry 24 * node + 3 * slot + k =

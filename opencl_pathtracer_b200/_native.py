@@ -18,6 +18,7 @@ PTC_OK = 0
 PTC_ERR_INVALID, PTC_ERR_CUDA, PTC_ERR_NO_DEVICE, PTC_ERR_STATE, PTC_ERR_LIMIT, PTC_ERR_UNSUPPORTED = 1, 2, 3, 4, 5, 6
 SAMPLER_JITTERED, SAMPLER_RANDOM, SAMPLER_UNIFORM = 0, 1, 2
 MODE_PARITY, MODE_FAST = 0, 1
+STATIC_MAX_RAYS, STATIC_SCRATCH_BYTES = 32768, 4 << 20  # ptc_trace_rays_static (include/pathtracer_cuda.h)
 FLAG_STAGE_TIMING, FLAG_NO_VARIANCE, FLAG_NO_GRAPH, FLAG_BVH2, FLAG_GPU_BVH, FLAG_RUSSIAN_ROULETTE, FLAG_TEXTURE_BILINEAR, FLAG_WORK_COUNTERS = 1, 2, 4, 8, 16, 32, 64, 128
 MAX_INTERSECTION_NUMBER = 5000
 
@@ -72,7 +73,8 @@ class SceneInfo(C.Structure):
 PTC_SYMBOLS = ["ptc_create", "ptc_upload_scene", "ptc_set_camera", "ptc_reset_accumulation", "ptc_set_supersampling", "ptc_render", "ptc_synchronize",
                "ptc_read_image", "ptc_read_variance", "ptc_read_stats", "ptc_read_rgb8", "ptc_convert_rgb8", "ptc_set_pixel_stripes", "ptc_add_image", "ptc_read_counters",
                "ptc_get_device_buffers", "ptc_trace_primary", "ptc_trace_rays", "ptc_render_single", "ptc_path_probe", "ptc_host_alloc", "ptc_host_free",
-               "ptc_last_error", "ptc_version", "ptc_device_count", "ptc_destroy", "ptc_wide_bvh_build", "ptc_wide_bvh_read", "ptc_wide_bvh_free", "ptc_measure_read_bandwidth", "ptc_create_multi", "ptc_context_devices", "ptc_multi_reduce_kind"]
+               "ptc_last_error", "ptc_version", "ptc_device_count", "ptc_destroy", "ptc_wide_bvh_build", "ptc_wide_bvh_read", "ptc_wide_bvh_free", "ptc_measure_read_bandwidth", "ptc_create_multi", "ptc_context_devices", "ptc_multi_reduce_kind",
+               "ptc_trace_rays_static"]
 
 _cuda = None
 _host = None
@@ -117,6 +119,7 @@ def cuda_lib():
     L.ptc_wide_bvh_free.restype = None
     L.ptc_trace_primary.argtypes = [vp, u32, vp, vp, vp, vp, vp, vp]
     L.ptc_trace_rays.argtypes = [vp, u32, vp, vp, vp, vp, vp, vp, vp]
+    L.ptc_trace_rays_static.argtypes = [vp, u32, vp, vp, vp, vp, vp, vp]
     L.ptc_render_single.argtypes = [vp, u32, vp]
     L.ptc_path_probe.argtypes = [vp, u32, u32, vp, vp, vp, vp]
     L.ptc_measure_read_bandwidth.argtypes = [vp, C.c_size_t, u32, P(C.c_double)]

@@ -48,7 +48,7 @@ def _build_cuda(out_dir, extra, verbose, force):
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))] + \
               [os.path.join(INC, f) for f in os.listdir(INC)]
     cu = [os.path.join(CSRC, "pt_kernels.cu"), os.path.join(CSRC, "pt_wide_build.cu"), os.path.join(CSRC, "pt_lbvh.cu"),
-          os.path.join(CSRC, "pathtracer_cuda.cu"), os.path.join(CSRC, "pt_multi.cu")]
+          os.path.join(CSRC, "pathtracer_cuda.cu"), os.path.join(CSRC, "pt_multi.cu"), os.path.join(CSRC, "pt_static.cu")]
     if force or _newer(cuda_so, cu + headers + [__file__]):
         objs = []
         for src in cu:

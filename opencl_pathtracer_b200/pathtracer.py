@@ -157,6 +157,19 @@ class PathTracerCUDA:
                                           out["dist2"].ctypes.data, out["dir"].ctypes.data, out["counts"].ctypes.data))
         return out
 
+    def trace_rays_static(self, origin, direction):
+        """trace_rays through ptc_trace_rays_static: no device allocation, scratch in the library's static device array, at most
+        _native.STATIC_MAX_RAYS rays per call (no counterpart in the reference; include/pathtracer_cuda.h)."""
+        o = np.ascontiguousarray(origin, np.float32)
+        d = np.ascontiguousarray(direction, np.float32)
+        n = len(o)
+        assert o.shape == (n, 4) and d.shape == (n, 4)
+        out = {"hit": np.empty(n, np.int32), "st": np.empty((n, 2), np.float32), "dist2": np.empty(n, np.float32),
+               "counts": np.empty((n, 2), np.uint32)}
+        self._ck(self._lib.ptc_trace_rays_static(self._h, n, o.ctypes.data, d.ctypes.data, out["hit"].ctypes.data, out["st"].ctypes.data,
+                                                 out["dist2"].ctypes.data, out["counts"].ctypes.data))
+        return out
+
     def path_probe(self, iteration, bounces):
         """State of every path of `iteration` after `bounces` bounces: dict(org [n,4], dir [n,4], hit [n] int32, st [n,2],
         tpar [n], refl [n] = bounces the path really took)."""
