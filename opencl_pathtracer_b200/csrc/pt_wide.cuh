@@ -81,6 +81,11 @@ struct WideLane
     // rays never park triangles: node step, all of its triangles, next node step — an order that is a function of the ray alone
     // (with parking it followed the warp's votes: about 40 of 2 M pixels of the bench scene changed from run to run).
     static constexpr uint32_t kStrict = 0x200u;
+    // A ray (nearly) parallel to a coordinate plane — one reciprocal direction component 2^14 times another — takes the single-precision
+    // slab test: the packed half-precision one scales a node's times by its coarsest axis and has no resolution left for the others
+    // then (it stays conservative, but such a ray would enter whole slabs of the tree: a camera looking along an axis shoots a column
+    // of them). About 2 in 10^4 of random directions, besides the structural ones.
+    static constexpr uint32_t kSingle = 0x400u;
     __device__ __forceinline__ bool finished() const { return sp == 0 && ty == 0u && gy <= 0x00ffffffu && !(oct & kPostponed); }
     // A lane can take a node step while it still holds untested triangles: it parks that group (once) and tests it in the
     // next triangle phase. So a lane often qualifies for both phases and follows the warp's vote instead of idling.
@@ -130,6 +135,8 @@ __device__ __forceinline__ void lane_begin(WideLane &L, const SceneDev &sc, cons
     L.tmax = best < 3.0e38f ? bound_as_parameter(sqrtf(best), r) : INFINITY;
     const uint32_t oct = (r.dx < 0 ? 4u : 0u) | (r.dy < 0 ? 2u : 0u) | (r.dz < 0 ? 1u : 0u);
     L.oct = (7u - oct) | ((r.dw == 0.f && r.ow == 1.f) ? 0u : WideLane::kStrict);
+    const float ax = fabsf(L.r.ix), ay = fabsf(L.r.iy), az = fabsf(L.r.iz);
+    if (!(fmaxf(fmaxf(ax, ay), az) < 16384.f * fminf(fminf(ax, ay), az))) L.oct |= WideLane::kSingle;
     L.gx = 0u;
     L.gy = sc.nNodes8 ? 0x80000000u : 0u;  // "slot 7 ^ octinv of an imask-less group at index 0" = the root
     L.tx = L.ty = 0u;
@@ -164,35 +171,94 @@ __device__ __forceinline__ void q8x4(uint32_t w, float &f0, float &f1, float &f2
     f0 = a.x; f1 = a.y; f2 = b.x; f3 = b.y;
 }
 
-// One node visit: take the nearest unvisited child of the current group, postpone its siblings, test its 8 children.
-template <bool FAST>
-__device__ __forceinline__ void lane_node_step(WideLane &L, const SceneDev &sc, uint2 *stk, const int stride)
-{
-    const uint32_t hits = L.gy;
-    const int bit = 31 - __clz((int)hits);
-    const uint32_t slot = (uint32_t)(bit - 24) ^ (L.oct & 7u);
-    const uint32_t rest = hits & ~(1u << bit);
-    const uint32_t rel = (uint32_t)__popc(hits & 0xffu & ((1u << slot) - 1u));
-    const uint32_t node = L.gx + rel;
-    PTC_CHECK(sc.faultSink, kFaultNodeIndex, node, sc.nNodes8);
-    const char *np = reinterpret_cast<const char *>(sc.nodes8 + node);
-    uint4 n0, n1, n2, n3, n4, n5;
-    ldg256(np, reinterpret_cast<float4 &>(n0), reinterpret_cast<float4 &>(n1));
-    ldg256(np + 32, reinterpret_cast<float4 &>(n2), reinterpret_cast<float4 &>(n3));
-    ldg256(np + 64, reinterpret_cast<float4 &>(n4), reinterpret_cast<float4 &>(n5));  // n5 = padding
-    if (L.ty != 0u)
-    {
-        stk[0] = make_uint2(L.tx, L.ty);  // park the untested triangles (wants_node: the slot is free)
-        L.oct |= WideLane::kPostponed;
-    }
-    if (rest > 0x00ffffffu)
-    {
-        PTC_CHECK(sc.faultSink, kFaultStack, L.sp + 1, sc.stackDepth);
-        stk[(L.sp + 1) * stride] = make_uint2(L.gx, rest);
-    }
-    L.sp += rest > 0x00ffffffu ? 1 : 0;
-    L.nb += 8;
+#ifndef PTC_WIDE_HALF2
+#define PTC_WIDE_HALF2 1
+#endif
 
+// The 8 slab tests of a node visit in packed half precision: two children per instruction. A byte q over a zero byte IS the
+// (denormal) half q * 2^-24, so one PRMT turns two quantised planes into an HFMA2 operand; per pair of children 6 HFMA2 give
+// the six plane times, 2 three-input + 2 two-input packed min / max the interval, one HSET2 the verdict: 85 instructions for
+// the 8 boxes where the single-precision version (below, PTC_WIDE_HALF2=0) issues 168 (48 HADD2.F32 + 48 FFMA + 32 FMNMX + ...).
+//
+// Half precision has 11 significant bits and a small exponent range, so times are first made node-relative and node-sized:
+// tau = (t - t0) * sigma, t0 = the time the ray enters the node's own box (0 if it starts inside), sigma the power of two that
+// brings the coarsest axis' time per grid step to [2^-10, 2^-9). A child the ray really crosses lies inside the node, so its
+// times are |tau| <= 255 steps of the FINEST axis: half's relative precision is then 1/8 of a grid step at worst.
+//
+// CONSERVATIVE — never misses a box the exact test enters — without an error analysis of the HFMA2 results themselves: the
+// fused multiply-add rounds the exact q * A + B once, and rounding is monotonic, so x <= y implies rn(x) <= rn(y). It is
+// therefore enough that the OPERANDS err outwards: the entry constants are lowered and the exit constants raised by
+//   |B| * 2^-11 (their own rounding to half) + 2^-24 (a denormal result's absolute rounding)
+//   + 0.126 step (q * (A - rn_half(A)), q <= 255) + 2^-21 |b| (the single-precision rounding of (p - o) / d, as the float version)
+// i.e. boxes grow by at most a quarter of a grid step per side on top of the <= 1 step of the 8-bit quantisation. Overflow to
+// +-inf errs outwards as well (a crossed child's times are node-sized, see above); a NaN (0 * inf cannot occur: A is finite by
+// the choice of sigma) only arises when t0 itself is infinite, i.e. the ray never enters the node.
+__device__ __forceinline__ __half2 h2bits(uint32_t u) { return *reinterpret_cast<const __half2 *>(&u); }
+
+__device__ __forceinline__ uint32_t slab_test_half2(const WideLane &L, const uint4 &n0, const uint4 &n2, const uint4 &n3, const uint4 &n4)
+{
+    // single precision: time per grid step a = 2^e / d and time of plane 0 b = (p - o) / d, per axis
+    const float adx = __uint_as_float((n0.w & 0xffu) << 23) * L.r.ix;
+    const float ady = __uint_as_float(((n0.w >> 8) & 0xffu) << 23) * L.r.iy;
+    const float adz = __uint_as_float(((n0.w >> 16) & 0xffu) << 23) * L.r.iz;
+    const float bx = (__uint_as_float(n0.x) - L.r.ox) * L.r.ix;
+    const float by = (__uint_as_float(n0.y) - L.r.oy) * L.r.iy;
+    const float bz = (__uint_as_float(n0.z) - L.r.oz) * L.r.iz;
+    // entry into the node's own box [plane 0, plane 255]^3, not before the origin
+    const float t0 = fmaxf(fmaxf(fminf(bx, __fmaf_rn(255.f, adx, bx)), fminf(by, __fmaf_rn(255.f, ady, by))),
+                           fmaxf(fminf(bz, __fmaf_rn(255.f, adz, bz)), 0.f));
+    // sigma from the exponent of the coarsest axis: A = a * 2^(141 - E) in [2^14, 2^15) multiplies q * 2^-24
+    const float amax = fmaxf(fmaxf(fabsf(adx), fabsf(ady)), fabsf(adz));
+    const uint32_t E = min(max(__float_as_uint(amax) >> 23, 14u), 240u);
+    const float sA = __uint_as_float((268u - E) << 23), sT = __uint_as_float((244u - E) << 23);
+    const float Ax = adx * sA, Ay = ady * sA, Az = adz * sA;
+    const float Bx = (bx - t0) * sT, By = (by - t0) * sT, Bz = (bz - t0) * sT;
+    // the pad (see above); |b| <= |B| / sigma + t0, so the 2^-21 |b| term splits into a share of |B|'s and one of the node's
+    const float kHalfUlp = 4.96e-4f, kStep = 7.52e-9f /* 0.126 * 2^-24 */, kDenorm = 5.9604645e-8f /* 2^-24 */;
+    const float pn = __fmaf_rn(t0 * sT, 4.76837158e-7f, kDenorm);
+    const float px = __fmaf_rn(fabsf(Bx), kHalfUlp, __fmaf_rn(fabsf(Ax), kStep, pn));
+    const float py = __fmaf_rn(fabsf(By), kHalfUlp, __fmaf_rn(fabsf(Ay), kStep, pn));
+    const float pz = __fmaf_rn(fabsf(Bz), kHalfUlp, __fmaf_rn(fabsf(Az), kStep, pn));
+    // the ray's own interval [0, tmax] in node time, erring outwards (t0 >= 0, so tau(0) <= 0)
+    const float tb = __fmaf_rn(t0 * sT, -1.001f, -kDenorm);
+    const float te0 = (L.tmax - t0) * sT, te = __fmaf_rn(fabsf(te0), 1.0e-3f, te0) + kDenorm;
+    // eleven constants in six registers: HFMA2 / HMNMX2 broadcast either half of an operand for free (.H0_H0 / .H1_H1)
+    const __half2 hBx = __floats2half2_rn(Bx - px, Bx + px), hBy = __floats2half2_rn(By - py, By + py), hBz = __floats2half2_rn(Bz - pz, Bz + pz);
+    const __half2 hAxy = __floats2half2_rn(Ax, Ay), hAzT = __floats2half2_rn(Az, tb), hTe = __floats2half2_rn(te, te);
+    const __half2 hAx = __low2half2(hAxy), hAy = __high2half2(hAxy), hAz = __low2half2(hAzT), hT0 = __high2half2(hAzT), hTM = hTe;
+    const __half2 hBlx = __low2half2(hBx), hBhx = __high2half2(hBx), hBly = __low2half2(hBy), hBhy = __high2half2(hBy);
+    const __half2 hBlz = __low2half2(hBz), hBhz = __high2half2(hBz);
+    // entry planes are the low ones along axes the ray travels up, the high ones otherwise
+    const bool nx = L.r.ix < 0, ny = L.r.iy < 0, nz = L.r.iz < 0;
+    // words: n2 = qlo.x[0] qlo.x[1] qlo.y[0] qlo.y[1]; n3 = qlo.z[0] qlo.z[1] qhi.x[0] qhi.x[1]; n4 = qhi.y[0] qhi.y[1] qhi.z[0] qhi.z[1]
+    uint32_t acc = 0;  // child c = 2k: bit c; child c = 2k + 1: bit 16 + c
+#pragma unroll
+    for (int h = 0; h < 2; h++)
+    {
+        const uint32_t lox = h ? n2.y : n2.x, loy = h ? n2.w : n2.z, loz = h ? n3.y : n3.x;
+        const uint32_t hix = h ? n3.w : n3.z, hiy = h ? n4.y : n4.x, hiz = h ? n4.w : n4.z;
+        const uint32_t ex = nx ? hix : lox, fx = nx ? lox : hix;
+        const uint32_t ey = ny ? hiy : loy, fy = ny ? loy : hiy;
+        const uint32_t ez = nz ? hiz : loz, fz = nz ? loz : hiz;
+#pragma unroll
+        for (int k = 0; k < 2; k++)
+        {
+            const uint32_t sel = k ? 0x4342u : 0x4140u;  // bytes (2k, 2k + 1) -> the low bytes of the two halves, zero above
+            const __half2 tex = __hfma2(h2bits(__byte_perm(ex, 0u, sel)), hAx, hBlx), tfx = __hfma2(h2bits(__byte_perm(fx, 0u, sel)), hAx, hBhx);
+            const __half2 tey = __hfma2(h2bits(__byte_perm(ey, 0u, sel)), hAy, hBly), tfy = __hfma2(h2bits(__byte_perm(fy, 0u, sel)), hAy, hBhy);
+            const __half2 tez = __hfma2(h2bits(__byte_perm(ez, 0u, sel)), hAz, hBlz), tfz = __hfma2(h2bits(__byte_perm(fz, 0u, sel)), hAz, hBhz);
+            const __half2 tEnter = __hmax2(__hmax2(tex, tey), __hmax2(tez, hT0));
+            const __half2 tExit = __hmin2(__hmin2(tfx, tfy), __hmin2(tfz, hTM));
+            const int c = 4 * h + 2 * k;
+            acc |= __hle2_mask(tEnter, tExit) & ((1u << c) | (1u << (c + 17)));
+        }
+    }
+    return (acc | (acc >> 16)) & 0xffu;
+}
+
+// The 8 slab tests in single precision: what every ray took before the packed version above, and what rays flagged kSingle take.
+__device__ __forceinline__ uint32_t slab_test_single(const WideLane &L, const uint4 &n0, const uint4 &n2, const uint4 &n3, const uint4 &n4)
+{
     // the ray in the node's grid: t(q) = q * (2^e / d) + (p - o) / d, the constant term padded outwards by 2^-21
     const float adx = __uint_as_float((n0.w & 0xffu) << 23) * L.r.ix;
     const float ady = __uint_as_float(((n0.w >> 8) & 0xffu) << 23) * L.r.iy;
@@ -233,6 +299,43 @@ __device__ __forceinline__ void lane_node_step(WideLane &L, const SceneDev &sc, 
             if (tEnter <= tExit) slotHit |= 1u << (4 * h + j);
         }
     }
+    return slotHit;
+}
+
+// One node visit: take the nearest unvisited child of the current group, postpone its siblings, test its 8 children.
+template <bool FAST>
+__device__ __forceinline__ void lane_node_step(WideLane &L, const SceneDev &sc, uint2 *stk, const int stride)
+{
+    const uint32_t hits = L.gy;
+    const int bit = 31 - __clz((int)hits);
+    const uint32_t slot = (uint32_t)(bit - 24) ^ (L.oct & 7u);
+    const uint32_t rest = hits & ~(1u << bit);
+    const uint32_t rel = (uint32_t)__popc(hits & 0xffu & ((1u << slot) - 1u));
+    const uint32_t node = L.gx + rel;
+    PTC_CHECK(sc.faultSink, kFaultNodeIndex, node, sc.nNodes8);
+    const char *np = reinterpret_cast<const char *>(sc.nodes8 + node);
+    uint4 n0, n1, n2, n3, n4, n5;
+    ldg256(np, reinterpret_cast<float4 &>(n0), reinterpret_cast<float4 &>(n1));
+    ldg256(np + 32, reinterpret_cast<float4 &>(n2), reinterpret_cast<float4 &>(n3));
+    ldg256(np + 64, reinterpret_cast<float4 &>(n4), reinterpret_cast<float4 &>(n5));  // n5 = padding
+    if (L.ty != 0u)
+    {
+        stk[0] = make_uint2(L.tx, L.ty);  // park the untested triangles (wants_node: the slot is free)
+        L.oct |= WideLane::kPostponed;
+    }
+    if (rest > 0x00ffffffu)
+    {
+        PTC_CHECK(sc.faultSink, kFaultStack, L.sp + 1, sc.stackDepth);
+        stk[(L.sp + 1) * stride] = make_uint2(L.gx, rest);
+    }
+    L.sp += rest > 0x00ffffffu ? 1 : 0;
+    L.nb += 8;
+
+#if PTC_WIDE_HALF2
+    const uint32_t slotHit = (L.oct & WideLane::kSingle) ? slab_test_single(L, n0, n2, n3, n4) : slab_test_half2(L, n0, n2, n3, n4);
+#else
+    const uint32_t slotHit = slab_test_single(L, n0, n2, n3, n4);
+#endif
     // inner children: the bit of slot s goes to position 24 + (s ^ octinv), so that "highest bit first" is front to back
     const uint32_t imask = n0.w >> 24;
     uint32_t ih = slotHit & imask;

@@ -8,7 +8,7 @@ mkdir -p $OUT
 cp $ROOT/opencl_pathtracer_b200/_lib/libpathtracer_host.so $ROOT/opencl_pathtracer_b200/_lib/libpathtracer_scene.so $OUT/
 OBJS=""
 FMAD=${FMAD:-false}
-for f in pt_kernels pt_wide_build pt_lbvh pathtracer_cuda pt_multi; do
+for f in pt_kernels pt_wide_build pt_lbvh pathtracer_cuda pt_multi pt_static; do
   nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -fmad=$FMAD -std=c++17 "$@" -Xcompiler -fPIC,-fopenmp,-ffp-contract=off,-fvisibility=hidden \
        -I $ROOT/include -I $ROOT/opencl_pathtracer_b200/csrc -c $ROOT/opencl_pathtracer_b200/csrc/$f.cu -o $OUT/$f.o &
   OBJS="$OBJS $OUT/$f.o"

@@ -163,3 +163,110 @@ def test_wide_bvh_traversal_matches_brute_force(scene_factory):
                 break
         assert hit == best or (best >= 0 and hit >= 0 and abs(tmax - best_t) < 1e-9 * max(1.0, best_t)), (hit, best, tmax, best_t)
     assert visited_total > 0
+
+
+# ---- the packed half-precision slab test of pt_wide.cuh (slab_test_half2), restated operation by operation in numpy
+def _f32(x):
+    return np.asarray(x, dtype=np.float32)
+
+
+def _fma32(a, b, c):
+    return (np.asarray(a, np.float64) * np.asarray(b, np.float64) + np.asarray(c, np.float64)).astype(np.float32)
+
+
+def _hfma(q, a16, b16):
+    # HFMA2: the exact q * A + B rounded once to half (q is the denormal half q * 2^-24: the 2^-24 is applied exactly here)
+    with np.errstate(over="ignore", invalid="ignore"):
+        return (np.ldexp(q.astype(np.float64), -24) * a16.astype(np.float64) + b16.astype(np.float64)).astype(np.float16)
+
+
+def slab_test_half2_restated(p, e, qlo, qhi, o, inv, tmax):
+    """p[3] grid origin, e[3] biased step exponents, qlo/qhi [3, 8] bytes, o[3], inv[3] (float32, finite), tmax -> 8 booleans."""
+    with np.errstate(over="ignore", invalid="ignore"):
+        step = np.ldexp(np.float32(1), e.astype(np.int64) - 127).astype(np.float32)
+        a = (step * inv).astype(np.float32)
+        b = ((p - o).astype(np.float32) * inv).astype(np.float32)
+        t0 = np.float32(max(np.minimum(b, _fma32(255.0, a, b)).max(), 0.0))
+        amax = np.abs(a).max()
+        E = int(min(max(int(np.float32(amax).view(np.uint32)) >> 23, 14), 240))
+        sA, sT = np.float32(np.ldexp(1.0, 268 - E - 127)), np.float32(np.ldexp(1.0, 244 - E - 127))
+        A = (a * sA).astype(np.float32)
+        B = ((b - t0).astype(np.float32) * sT).astype(np.float32)
+        pn = _fma32(np.float32(t0 * sT), 4.76837158e-7, 5.9604645e-8)
+        pad = _fma32(np.abs(B), 4.96e-4, _fma32(np.abs(A), 7.52e-9, pn))
+        hA = A.astype(np.float16)
+        hBl, hBh = (B - pad).astype(np.float32).astype(np.float16), (B + pad).astype(np.float32).astype(np.float16)
+        tb = _fma32(np.float32(t0 * sT), -1.001, -5.9604645e-8).astype(np.float16)
+        te0 = np.float32((np.float32(tmax) - t0) * sT)
+        te = np.float32(_fma32(np.abs(te0), 1.0e-3, te0) + np.float32(5.9604645e-8)).astype(np.float16)
+        neg = inv < 0
+        qe = np.where(neg[:, None], qhi, qlo)
+        qf = np.where(neg[:, None], qlo, qhi)
+        te_ = _hfma(qe, hA[:, None], hBl[:, None])  # [axis, slot]
+        tf_ = _hfma(qf, hA[:, None], hBh[:, None])
+        t_enter = np.fmax(np.fmax(np.fmax(te_[0], te_[1]), te_[2]), tb)  # fmax / fmin: a NaN operand is ignored, as HMNMX2 does
+        t_exit = np.fmin(np.fmin(np.fmin(tf_[0], tf_[1]), tf_[2]), te)
+        return t_enter <= t_exit
+
+
+def test_half2_slab_test_is_conservative(scene_factory):
+    """Every child box the exact slab test (float64, on the quantised boxes) enters is entered by the packed half-precision
+    test the FAST node step runs; the boxes it enters in addition are few (reported)."""
+    sc = scene_factory("atrium:8", 64, 48)
+    nodes, _, _ = sc.wide_bvh()
+    tris = sc.triangles()
+    verts = np.stack([np.stack([tris[k][a] for a in "xyz"], -1) for k in ("S1", "S2", "S3")], 1).astype(np.float64).reshape(-1, 3)
+    slo, shi = verts.min(0), verts.max(0)
+    rng = np.random.default_rng(11)
+    exact_hits = half_hits = missed = 0
+    plain_exact = plain_half = n_single = 0
+    for it in range(6000):
+        i = int(rng.integers(len(nodes)))
+        n, blo, bhi = _decode(nodes, i)
+        # a ray aimed at a point inside (or near) the node, from inside the scene, near or far; some axis-parallel, some with a bound
+        nlo, nhi = blo.min(1), bhi.max(1)
+        target = nlo + (nhi - nlo) * rng.uniform(-0.2, 1.2, 3)
+        o = (slo + (shi - slo) * rng.uniform(0, 1, 3)) if it % 3 else (target + rng.normal(size=3) * (nhi - nlo).max() * 0.7)
+        d = target - o
+        plain = True
+        if it % 7 == 0:
+            d[int(rng.integers(3))] = 0.0
+            plain = False
+        if it % 11 == 0:
+            d[int(rng.integers(3))] *= 1e-6
+            plain = False
+        if it % 13 == 0:
+            d[int(rng.integers(3))] *= 2.0 ** -12  # below the kSingle threshold: the packed test still runs, with less resolution
+            plain = False
+        if not np.any(d):
+            continue
+        o32 = _f32(o)
+        d32 = _f32(d / np.linalg.norm(d))
+        with np.errstate(divide="ignore"):
+            inv = (np.float32(1) / d32).astype(np.float32)
+        inv = np.where(np.abs(inv) < 1e30, inv, np.copysign(np.float32(1e30), d32)).astype(np.float32)  # finite_inverse
+        if not np.abs(inv).max() < np.float32(16384) * np.abs(inv).min():
+            n_single += 1  # WideLane::kSingle: this ray takes the single-precision test
+            continue
+        dist = np.linalg.norm(target - o)
+        tmax = np.inf if it % 2 else dist * rng.uniform(0.5, 1.5)
+        got = slab_test_half2_restated(n["p"].astype(np.float32), n["e"], n["qlo"], n["qhi"], o32, inv, tmax)
+        # exact: the same ray (float32 origin, the reciprocal the kernel uses) against the quantised boxes in float64
+        o64, inv64 = o32.astype(np.float64), inv.astype(np.float64)
+        for s in range(8):
+            t1, t2 = (blo[:, s] - o64) * inv64, (bhi[:, s] - o64) * inv64
+            tn, tf = max(np.minimum(t1, t2).max(), 0.0), min(np.maximum(t1, t2).min(), tmax)
+            ex = tn <= tf
+            exact_hits += ex
+            half_hits += bool(got[s])
+            plain_exact += ex and plain
+            plain_half += bool(got[s]) and plain
+            if ex and not got[s]:
+                missed += 1
+    print("half2 slab test: %d exact hits, %d half hits, %d missed (%d rays flagged kSingle left out); rays without a small direction component: %d -> %d (+%.2f %%)"
+          % (exact_hits, half_hits, missed, n_single, plain_exact, plain_half, 100.0 * (plain_half - plain_exact) / max(plain_exact, 1)))
+    assert missed == 0 and n_single > 500
+    # the scale follows the coarsest axis, so a ray close to parallel to a coordinate plane has less resolution on the other two axes:
+    # more boxes entered, never fewer (beyond a ratio of 2^14 the kernel switches to single precision). For the bulk of the rays the
+    # boxes grow by a fraction of a grid step.
+    assert plain_half <= plain_exact * 1.03 and half_hits <= exact_hits * 1.06
