@@ -644,7 +644,7 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
     if (!std::getenv("PTC_FULL_STACK"))
     {
         ctx->lc.stackDepth = (int)std::min<uint32_t>(32u, std::max<uint32_t>(4u, maxDepth + 1));
-        if (ctx->wide) ctx->lc.stackDepth = (int)std::max<uint32_t>(3u, wideDepth + 2);  // the parked triangle group + one sibling group per level
+        if (ctx->wide) ctx->lc.stackDepth = (int)std::max<uint32_t>(3u, wideDepth + 1 + WideLane::kPark);  // the parked triangle groups + one sibling group per level
         // a tree too deep for one CTA's shared memory is refused here, with a message, not at the first launch with "invalid argument"
         if (traverse_shared_bytes(ctx->wide, ctx->lc.stackDepth, true) > 227u * 1024u)
             return fail(ctx, PTC_ERR_LIMIT, "BVH of %d levels: the traversal stacks (%zu bytes per CTA) exceed the 227 KB of shared memory", ctx->lc.stackDepth,

@@ -165,13 +165,31 @@ constexpr size_t kGroupBytes = sizeof(PathGroup) * (kTraverseThreads / 32);
 // and in the parity probes: its counts follow the warp's votes (a parked triangle group shrinks the bound later), are compared
 // with nothing, and cost two registers and two atomics per ray. Without COUNT the lane's counters run on across rays and only
 // the global totals (ptc_counters.box_tests / triangle_tests) are kept.
+#ifdef PTC_LANE_STATS
+// Diagnostic build only (scripts/build_variant.sh stats -DPTC_LANE_STATS): what the 32 lanes of a warp are doing at every node step
+// and every triangle step, summed over all warps. [0..7] extend, [8..15] connect:
+// 0 node steps, 1 lanes stepping, 2 lanes without a ray, 3 lanes finished (waiting for completion), 4 lanes blocked (hold triangles
+// and cannot park them), 5 triangle steps, 6 lanes testing, 7 lanes that wait for a node meanwhile
+__device__ unsigned long long g_laneStats[16];
+extern "C" __attribute__((visibility("default"))) int ptc_debug_lane_stats(unsigned long long *out, int reset)
+{
+    if (cudaMemcpyFromSymbol(out, g_laneStats, sizeof(g_laneStats)) != cudaSuccess) return 1;
+    if (reset)
+    {
+        unsigned long long z[16] = {0};
+        cudaMemcpyToSymbol(g_laneStats, z, sizeof(z));
+    }
+    return 0;
+}
+#endif
+
 template <bool ANY, int FAST, typename LaneT, bool COUNT>
 __global__ void __launch_bounds__(kTraverseThreads, (ANY ? LaneT::kMinCtasAny : LaneT::kMinCtas) * 128 / kTraverseThreads) k_trace(SceneDev sc, PathState st, const uint32_t *__restrict__ queue,
                                                            Counters *__restrict__ cn, int bounce, uint32_t popMin, int stackDepth)
 {
     typedef typename LaneT::StackT StackT;
     extern __shared__ __align__(16) unsigned char smemRaw[];
-    StackT *stk = reinterpret_cast<StackT *>(smemRaw) + threadIdx.x;
+    const typename LaneT::StackRef stk = LaneT::stack_ref(reinterpret_cast<StackT *>(smemRaw) + threadIdx.x);
     StagedRays &stage = reinterpret_cast<StagedRays *>(smemRaw + sizeof(StackT) * stackDepth * kTraverseThreads)[threadIdx.x >> 5];
     PathGroup &group = reinterpret_cast<PathGroup *>(smemRaw + sizeof(StackT) * stackDepth * kTraverseThreads + kStageBytes)[threadIdx.x >> 5];  // ANY only
     const unsigned lane = threadIdx.x & 31u;
@@ -193,6 +211,9 @@ __global__ void __launch_bounds__(kTraverseThreads, (ANY ? LaneT::kMinCtasAny : 
     bool lastGroup = false;
     uint32_t nbSum = 0, ntSum = 0;  // COUNT: per-lane sums of the finished rays' counters; else warp totals (uniform, from the votes)
     uint32_t nRays = 0;             // rays this warp staged (uniform): every staged ray is traced
+#ifdef PTC_LANE_STATS
+    unsigned long long ls[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#endif
     while (true)
     {
         // ---- completion: write the result of a finished ray (the counters are fire-and-forget reductions)
@@ -372,12 +393,20 @@ __global__ void __launch_bounds__(kTraverseThreads, (ANY ? LaneT::kMinCtasAny : 
         }
         // ---- node phase: node steps while at least half of the lanes that hold a ray wait for a node
         const int nHave = 32 - __popc(__ballot_sync(full, L.idle() || L.finished()));
+        int thrNode = voteNode * nHave;  // kept in a register (the compiler would re-derive it from the kernel parameter in every iteration)
+        asm volatile("" : "+r"(thrNode));
         while (true)
         {
             const bool wantNode = L.wants_node();
             const int nN = __popc(__ballot_sync(full, wantNode));
-            if (nN == 0 || 8 * nN < voteNode * nHave) break;
+            if (nN == 0 || 8 * nN < thrNode) break;
             if (!COUNT) nbSum += (uint32_t)(LaneT::kBoxesPerNodeStep * nN);
+#ifdef PTC_LANE_STATS
+            ls[0]++; ls[1] += nN;
+            ls[2] += __popc(__ballot_sync(full, L.idle()));
+            ls[3] += __popc(__ballot_sync(full, !L.idle() && L.finished()));
+            ls[4] += __popc(__ballot_sync(full, !L.idle() && !L.finished() && !wantNode));
+#endif
             if (wantNode) lane_node_step<(FAST != 0)>(L, sc, stk, kTraverseThreads);
         }
         // ---- triangle phase: at least one step if any lane waits for a triangle, then while they are the majority
@@ -387,10 +416,18 @@ __global__ void __launch_bounds__(kTraverseThreads, (ANY ? LaneT::kMinCtasAny : 
             const int nT = __popc(__ballot_sync(full, wantTri));
             if (nT == 0) break;
             if (!COUNT) ntSum += (uint32_t)nT;
+#ifdef PTC_LANE_STATS
+            ls[5]++; ls[6] += nT;
+            ls[7] += __popc(__ballot_sync(full, !wantTri && L.wants_node()));
+#endif
             if (wantTri) lane_tri_step<ANY>(L, sc, stk, kTraverseThreads);
             if (8 * nT <= voteTri * nHave) break;
         }
     }
+#ifdef PTC_LANE_STATS
+    if (lane == 0)
+        for (int i = 0; i < 8; i++) atomicAdd(&g_laneStats[(ANY ? 8 : 0) + i], ls[i]);
+#endif
     // warp totals live in lane 0 only (the per-lane sums of COUNT are added up by flush_work's reduction)
     flush_work(cn, ANY ? &cn->shadowRays : &cn->extensionRays, lane == 0 ? nRays : 0u, (COUNT || lane == 0) ? nbSum : 0u, (COUNT || lane == 0) ? ntSum : 0u);
 }

@@ -165,6 +165,8 @@ constexpr uint32_t kDone = 0xfffffffeu, kIdle = 0xffffffffu;
 
 struct TraceLane
 {
+    typedef uint32_t *StackRef;
+    static __device__ __forceinline__ StackRef stack_ref(uint32_t *p) { return p; }
     Ray r;
     float best;
     uint32_t cur;

@@ -60,6 +60,29 @@ struct WideLane
     bool found;
 
     typedef uint2 StackT;
+    // The lane's stack as a 32-bit shared-window address, made opaque to the compiler once: left to itself it re-derives the
+    // address (S2UR CgaCtaId, ULEA, S2R tid, IMAD: 7 instructions) in every iteration of the node loop rather than keep a register.
+    struct StackRef
+    {
+        uint32_t a;
+        __device__ __forceinline__ uint2 ld(int level, int stride) const
+        {
+            uint2 v;
+            asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a + (uint32_t)(level * stride) * 8u));
+            return v;
+        }
+        __device__ __forceinline__ void st(int level, int stride, uint2 v) const
+        {
+            asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(a + (uint32_t)(level * stride) * 8u), "r"(v.x), "r"(v.y));
+        }
+    };
+    static __device__ __forceinline__ StackRef stack_ref(StackT *p)
+    {
+        StackRef r;
+        r.a = (uint32_t)__cvta_generic_to_shared(p);
+        asm volatile("" : "+r"(r.a));
+        return r;
+    }
     static constexpr int kBoxesPerNodeStep = 8;
 #ifndef PTC_WIDE_MIN_CTAS
 #define PTC_WIDE_MIN_CTAS 8
@@ -74,23 +97,30 @@ struct WideLane
     __device__ __forceinline__ void reset() { sp = -1; gy = ty = 0; nb = nt = 0; found = false; hitTri = -1; }
     __device__ __forceinline__ bool idle() const { return sp < 0; }
     __device__ __forceinline__ void set_idle() { sp = -1; }
-    static constexpr uint32_t kPostponed = 0x100u;
+    // Parked triangle groups: a lane may take a node step while it still holds untested triangles — it parks the group in one of
+    // the kPark lowest levels of its shared-memory stack (bits 9..8 of oct count them) and tests it in a later triangle phase.
+#ifndef PTC_PARK_SLOTS
+#define PTC_PARK_SLOTS 1
+#endif
+    static constexpr int kPark = PTC_PARK_SLOTS;
+    static_assert(kPark >= 1 && kPark <= 3, "two bits count the parked groups");
+    static constexpr uint32_t kParkedOne = 0x100u, kParkedMask = 0x300u;
     // The reference's 4-lane arithmetic lets a refracted direction keep a w lane != 0 and every later origin of that path a
     // w lane != 1. For such a ray the "distance" a triangle is accepted with is no longer the parameter at which
     // the ray crosses the triangle's box, so which candidates survive the distance cull depends on the order of the tests. These
     // rays never park triangles: node step, all of its triangles, next node step — an order that is a function of the ray alone
     // (with parking it followed the warp's votes: about 40 of 2 M pixels of the bench scene changed from run to run).
-    static constexpr uint32_t kStrict = 0x200u;
+    static constexpr uint32_t kStrict = 0x400u;
     // A ray (nearly) parallel to a coordinate plane — one reciprocal direction component 2^14 times another — takes the single-precision
     // slab test: the packed half-precision one scales a node's times by its coarsest axis and has no resolution left for the others
     // then (it stays conservative, but such a ray would enter whole slabs of the tree: a camera looking along an axis shoots a column
     // of them). About 2 in 10^4 of random directions, besides the structural ones.
-    static constexpr uint32_t kSingle = 0x400u;
-    __device__ __forceinline__ bool finished() const { return sp == 0 && ty == 0u && gy <= 0x00ffffffu && !(oct & kPostponed); }
+    static constexpr uint32_t kSingle = 0x800u;
+    __device__ __forceinline__ bool finished() const { return sp == 0 && ty == 0u && gy <= 0x00ffffffu && !(oct & kParkedMask); }
     // A lane can take a node step while it still holds untested triangles: it parks that group (once) and tests it in the
     // next triangle phase. So a lane often qualifies for both phases and follows the warp's vote instead of idling.
-    __device__ __forceinline__ bool wants_node() const { return sp >= 0 && gy > 0x00ffffffu && (ty == 0u || !(oct & (kPostponed | kStrict))); }
-    __device__ __forceinline__ bool wants_tri() const { return sp >= 0 && (ty != 0u || (oct & kPostponed)); }
+    __device__ __forceinline__ bool wants_node() const { return sp >= 0 && gy > 0x00ffffffu && (ty == 0u || (!(oct & kStrict) && (oct & kParkedMask) < kPark * kParkedOne)); }
+    __device__ __forceinline__ bool wants_tri() const { return sp >= 0 && (ty != 0u || (oct & kParkedMask)); }
     // BVH-order index of the hit (what the shade stage and the reference's ids use), -1 = miss
     __device__ __forceinline__ int hit_index(const SceneDev &sc) const { return hitTri < 0 ? -1 : (int)__ldg(&sc.tri8Index[hitTri]); }
     // (s, t, ray parameter, MaterialType of the side hit) of the final hit: the accepted test once more — the same operations on
@@ -146,13 +176,13 @@ __device__ __forceinline__ void lane_begin(WideLane &L, const SceneDev &sc, cons
 }
 
 // no inner child left in the current node group: continue with the most recently postponed siblings. Stack level 0 of a
-// lane is the slot of its parked triangle group, sibling groups live in levels 1..sp.
-__device__ __forceinline__ void wide_normalise(WideLane &L, const uint2 *stk, const int stride)
+// lane are the slots of its parked triangle groups, sibling groups live in the sp levels above them.
+__device__ __forceinline__ void wide_normalise(WideLane &L, const WideLane::StackRef stk, const int stride)
 {
     const bool pop = L.gy <= 0x00ffffffu && L.sp > 0;
     if (pop)
     {
-        const uint2 e = stk[L.sp * stride];
+        const uint2 e = stk.ld(L.sp + WideLane::kPark - 1, stride);
         L.gx = e.x;
         L.gy = e.y;
     }
@@ -304,7 +334,7 @@ __device__ __forceinline__ uint32_t slab_test_single(const WideLane &L, const ui
 
 // One node visit: take the nearest unvisited child of the current group, postpone its siblings, test its 8 children.
 template <bool FAST>
-__device__ __forceinline__ void lane_node_step(WideLane &L, const SceneDev &sc, uint2 *stk, const int stride)
+__device__ __forceinline__ void lane_node_step(WideLane &L, const SceneDev &sc, const WideLane::StackRef stk, const int stride)
 {
     const uint32_t hits = L.gy;
     const int bit = 31 - __clz((int)hits);
@@ -320,13 +350,13 @@ __device__ __forceinline__ void lane_node_step(WideLane &L, const SceneDev &sc, 
     ldg256(np + 64, reinterpret_cast<float4 &>(n4), reinterpret_cast<float4 &>(n5));  // n5 = padding
     if (L.ty != 0u)
     {
-        stk[0] = make_uint2(L.tx, L.ty);  // park the untested triangles (wants_node: the slot is free)
-        L.oct |= WideLane::kPostponed;
+        stk.st(WideLane::kPark == 1 ? 0 : (int)((L.oct >> 8) & 3u), stride, make_uint2(L.tx, L.ty));  // park the untested triangles (wants_node: a slot is free)
+        L.oct += WideLane::kParkedOne;
     }
     if (rest > 0x00ffffffu)
     {
-        PTC_CHECK(sc.faultSink, kFaultStack, L.sp + 1, sc.stackDepth);
-        stk[(L.sp + 1) * stride] = make_uint2(L.gx, rest);
+        PTC_CHECK(sc.faultSink, kFaultStack, L.sp + WideLane::kPark, sc.stackDepth);
+        stk.st(L.sp + WideLane::kPark, stride, make_uint2(L.gx, rest));
     }
     L.sp += rest > 0x00ffffffu ? 1 : 0;
     L.nb += 8;
@@ -360,14 +390,14 @@ __device__ __forceinline__ void lane_node_step(WideLane &L, const SceneDev &sc, 
 // translates it once per ray) and the new bound follows from the hit's own ray parameter (directions are unit length over
 // the four lanes the reference normalises, so parameter and distance coincide).
 template <bool ANY>
-__device__ __forceinline__ void lane_tri_step(WideLane &L, const SceneDev &sc, const uint2 *stk, const int stride)
+__device__ __forceinline__ void lane_tri_step(WideLane &L, const SceneDev &sc, const WideLane::StackRef stk, const int stride)
 {
     if (L.ty == 0u)
     {
-        const uint2 e = stk[0];  // the parked group
+        L.oct -= WideLane::kParkedOne;
+        const uint2 e = stk.ld(WideLane::kPark == 1 ? 0 : (int)((L.oct >> 8) & 3u), stride);  // the group parked last
         L.tx = e.x;
         L.ty = e.y;
-        L.oct &= ~WideLane::kPostponed;
     }
     const int bit = __ffs((int)L.ty) - 1;
     L.ty &= L.ty - 1u;

@@ -40,3 +40,15 @@ with pt.PathTracerCUDA(W, H, mode=mode, flags=pt.FLAG_NO_VARIANCE | pt.FLAG_STAG
     print("env %s | %.1f Msamples/s %.0f Mrays/s | ms: ext %.1f con %.1f shade %.1f acc %.1f | box/path %.0f tri/path %.0f" % (
         env, c["paths"] / dt / 1e6, rays / dt / 1e6,
         c["ms_extend"], c["ms_connect"], c["ms_shade"], c["ms_accumulate"], c["box_tests"] / c["paths"], c["triangle_tests"] / c["paths"]))
+    try:
+        import ctypes as C
+        from opencl_pathtracer_b200 import _native as N
+        fn = N.cuda_lib().ptc_debug_lane_stats  # only in a -DPTC_LANE_STATS build
+        buf = (C.c_ulonglong * 16)()
+        fn(buf, 1)
+        for k, name in ((0, "extend"), (8, "connect")):
+            ns, ln, idle, fin, blk, ts, lt, wn = [buf[k + i] for i in range(8)]
+            print("lanes %-7s | node steps %.2f M: stepping %.1f, no ray %.1f, finished %.1f, blocked on triangles %.1f | triangle steps %.2f M: testing %.1f, waiting for a node %.1f"
+                  % (name, ns / 1e6, ln / max(ns, 1), idle / max(ns, 1), fin / max(ns, 1), blk / max(ns, 1), ts / 1e6, lt / max(ts, 1), wn / max(ts, 1)))
+    except AttributeError:
+        pass
