@@ -225,12 +225,22 @@ __global__ void __launch_bounds__(kTraverseThreads, (ANY ? LaneT::kMinCtasAny : 
             const uint32_t li = ANY ? (item >> kLightShift) : 0u;
             if (!ANY)
             {
-                float hs, ht, htp;
                 uint32_t hmat;
-                L.hit_record(sc, hs, ht, htp, hmat);
                 const int hitIndex = L.hit_index(sc);
                 if (hitIndex >= 0) PTC_CHECK(cn, kFaultHitIndex, hitIndex, sc.nTriangles);
-                st.hit[p] = f4(__int_as_float(hitIndex), hs, ht, htp);
+                if (LaneT::kStoresHit)
+                {
+                    // (s, t, parameter) were stored when the hit was accepted (lane_tri_step)
+                    if (hitIndex < 0) st.hit[p] = f4(__int_as_float(-1), 0.f, 0.f, 0.f);
+                    else reinterpret_cast<int *>(st.hit + p)[0] = hitIndex;
+                    hmat = (L.oct >> LaneT::kMatShift) & 15u;
+                }
+                else
+                {
+                    float hs, ht, htp;
+                    L.hit_record(sc, hs, ht, htp, hmat);
+                    st.hit[p] = f4(__int_as_float(hitIndex), hs, ht, htp);
+                }
                 if (COUNT)
                 {
                     atomicAdd(&st.nbbx[p], L.nb);
@@ -420,7 +430,7 @@ __global__ void __launch_bounds__(kTraverseThreads, (ANY ? LaneT::kMinCtasAny : 
             ls[5]++; ls[6] += nT;
             ls[7] += __popc(__ballot_sync(full, !wantTri && L.wants_node()));
 #endif
-            if (wantTri) lane_tri_step<ANY>(L, sc, stk, kTraverseThreads);
+            if (wantTri) lane_tri_step<ANY>(L, sc, stk, kTraverseThreads, st.hit, &stage.laneItem[lane]);
             if (8 * nT <= voteTri * nHave) break;
         }
     }

@@ -166,6 +166,9 @@ constexpr uint32_t kDone = 0xfffffffeu, kIdle = 0xffffffffu;
 struct TraceLane
 {
     typedef uint32_t *StackRef;
+    static constexpr bool kStoresHit = false;  // the hit record rides in the lane (hs, ht, htp, hmat) and is written at completion
+    static constexpr uint32_t kMatShift = 0;
+    uint32_t oct;  // unused (WideLane's flag word)
     static __device__ __forceinline__ StackRef stack_ref(uint32_t *p) { return p; }
     Ray r;
     float best;
@@ -262,7 +265,7 @@ __device__ __forceinline__ void lane_node_step(TraceLane &L, const SceneDev &sc,
 }
 
 template <bool ANY>
-__device__ __forceinline__ void lane_tri_step(TraceLane &L, const SceneDev &sc, const uint32_t *stk, const int stride)
+__device__ __forceinline__ void lane_tri_step(TraceLane &L, const SceneDev &sc, const uint32_t *stk, const int stride, float4 *, const uint32_t *)
 {
     const uint32_t i = (L.cur >> 4) & 0x7ffffffu;
     PTC_CHECK(sc.faultSink, kFaultTriIndex, i, sc.nTriangles);
