@@ -25,11 +25,22 @@ constexpr uint32_t kFlagRussianRoulette = 1u << 5;  // PTC_FLAG_RUSSIAN_ROULETTE
 constexpr uint32_t kFlagTextureBilinear = 1u << 6;  // PTC_FLAG_TEXTURE_BILINEAR
 constexpr int kStreamThreads = 256;
 #ifndef PTC_SHADE_MIN_BLOCKS
-#define PTC_SHADE_MIN_BLOCKS 4  // k_shade: 4 CTAs of 8 warps per SM = 64 registers (A/B: scripts/build_variant.sh shade3 -DPTC_SHADE_MIN_BLOCKS=3)
+#define PTC_SHADE_MIN_BLOCKS 2  // k_shade: 2 CTAs of 16 warps per SM = 64 registers (A/B: scripts/build_variant.sh NAME -DPTC_SHADE_MIN_BLOCKS=.. -DPTC_SHADE_THREADS=..)
 #endif
 
 // the partitioned queue of a bounce (k_classify below): tiles of 1024 entries, the lit ones first
 constexpr int kClassifyItems = 4;                                  // consecutive queue entries per thread of k_classify
+#ifndef PTC_SHADE_THREADS
+#define PTC_SHADE_THREADS 512
+#endif
+// k_shade is 3,200 instructions long and every warp walks most of it (2,080 per item); with the warps of an SM spread over the whole
+// kernel the instruction caches thrash: `no_instruction` was its largest stall (4.2 of 13.9 cycles per issue, ncu round 2). A CTA
+// barrier per item round keeps the 16 warps of a CTA in phase: shade 16.4 -> 14.9 ms per step on the bench scene, 5.1 -> 4.7 on the
+// Cornell box (profiles/r02_sweeps.txt Q: 256 x 4 / 512 x 2 / 1024 x 1 threads x CTAs, with and without the barrier)
+#ifndef PTC_SHADE_SYNC
+#define PTC_SHADE_SYNC 1
+#endif
+constexpr int kShadeThreads = PTC_SHADE_THREADS;
 constexpr uint32_t kClassTile = kStreamThreads * kClassifyItems;   // 1024
 __device__ __forceinline__ bool entry_is_lit(const PathState &st, uint32_t k) { return (k & (kClassTile - 1u)) < st.tileLit[k / kClassTile]; }
 
@@ -686,7 +697,7 @@ __device__ __forceinline__ bool shade_path(const SceneDev &sc, const FrameParams
 // runs with holes, the others sparse ones: +25 % DRAM sectors. Cornell box (shade is 45 % of a step, instruction bound): 1,036 ->
 // 1,322 Msamples/s. Atrium (shade 16 %, DRAM bound at 4.6 TB/s on bounce 0): 164.5 -> 153.6. (profiles/r02_sweeps.txt)
 template <int FAST, bool PART>  // FAST as k_trace
-__global__ void __launch_bounds__(kStreamThreads, PTC_SHADE_MIN_BLOCKS) k_shade(SceneDev sc, FrameParams fp, PathState st, const uint32_t *__restrict__ qin,
+__global__ void __launch_bounds__(kShadeThreads, PTC_SHADE_MIN_BLOCKS) k_shade(SceneDev sc, FrameParams fp, PathState st, const uint32_t *__restrict__ qin,
                                                                             uint32_t *__restrict__ qout, Counters *__restrict__ cn, int bounce)
 {
     const uint32_t count = cn->qcount[bounce];
@@ -694,6 +705,9 @@ __global__ void __launch_bounds__(kStreamThreads, PTC_SHADE_MIN_BLOCKS) k_shade(
     const uint32_t rounds = (count + stride - 1) / stride;
     for (uint32_t it = 0; it < rounds; it++)
     {
+#if PTC_SHADE_SYNC
+        __syncthreads();
+#endif
         const uint32_t k = it * stride + blockIdx.x * blockDim.x + threadIdx.x;
         bool alive = false;
         uint32_t p = 0;
@@ -1077,8 +1091,8 @@ void launch_shade(cudaStream_t s, const LaunchCfg &lc, bool fast, const SceneDev
 #define PTC_SHADE(MODE)                                                                                                    \
     do                                                                                                                     \
     {                                                                                                                      \
-        if (lc.partition) k_shade<MODE, true><<<lc.streamGrid, kStreamThreads, 0, s>>>(sc, fp, st, qin, qout, cn, bounce); \
-        else k_shade<MODE, false><<<lc.streamGrid, kStreamThreads, 0, s>>>(sc, fp, st, qin, qout, cn, bounce);             \
+        if (lc.partition) k_shade<MODE, true><<<lc.streamGrid * kStreamThreads / kShadeThreads, kShadeThreads, 0, s>>>(sc, fp, st, qin, qout, cn, bounce); \
+        else k_shade<MODE, false><<<lc.streamGrid * kStreamThreads / kShadeThreads, kShadeThreads, 0, s>>>(sc, fp, st, qin, qout, cn, bounce); \
     } while (0)
     if (fast && sc.areaJump != 1u) PTC_SHADE(2);
     else if (fast) PTC_SHADE(1);
