@@ -644,7 +644,12 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
     if (!std::getenv("PTC_FULL_STACK"))
     {
         ctx->lc.stackDepth = (int)std::min<uint32_t>(32u, std::max<uint32_t>(4u, maxDepth + 1));
-        if (ctx->wide) ctx->lc.stackDepth = (int)std::max<uint32_t>(3u, wideDepth + 1 + WideLane::kPark);  // the parked triangle groups + one sibling group per level
+        // The wide walk pushes the unvisited siblings of the child it descends into, and the root has none: at most wideDepth - 1 sibling
+        // groups are ever stacked, above the kPark slots of parked triangle groups (one spare level; the CHECKED build tests the bound).
+        // Round 2 sized this wideDepth + 2: the two unused levels (2 KB per CTA) pushed connect's 7 CTAs per SM past the 164 KB shared-memory
+        // carve-out, i.e. halved its L1 (profiles/r02_sweeps.txt T)
+        if (ctx->wide) ctx->lc.stackDepth = (int)std::max<uint32_t>(3u, wideDepth + WideLane::kPark);
+        if (const char *e = std::getenv("PTC_STACK_EXTRA")) ctx->lc.stackDepth = std::max(3, ctx->lc.stackDepth + std::atoi(e));  // experiments
         // a tree too deep for one CTA's shared memory is refused here, with a message, not at the first launch with "invalid argument"
         if (traverse_shared_bytes(ctx->wide, ctx->lc.stackDepth, true) > 227u * 1024u)
             return fail(ctx, PTC_ERR_LIMIT, "BVH of %d levels: the traversal stacks (%zu bytes per CTA) exceed the 227 KB of shared memory", ctx->lc.stackDepth,
