@@ -41,6 +41,7 @@ constexpr int kClassifyItems = 4;                                  // consecutiv
 #define PTC_SHADE_SYNC 1
 #endif
 constexpr int kShadeThreads = PTC_SHADE_THREADS;
+
 constexpr uint32_t kClassTile = kStreamThreads * kClassifyItems;   // 1024
 __device__ __forceinline__ bool entry_is_lit(const PathState &st, uint32_t k) { return (k & (kClassTile - 1u)) < st.tileLit[k / kClassTile]; }
 
@@ -156,6 +157,8 @@ struct StagedRays  // one per warp
     float4 invBest[32];  // reciprocal direction (header.cl:280-282) and the initial distance bound
     uint32_t item[32];
     uint32_t laneItem[32];  // the item each lane is tracing: cold state, read back once at completion instead of riding in a register
+    uint32_t nRays;         // rays this warp staged (every staged ray is traced): touched once per 32 items, so it lives here, not in a register
+    uint32_t pad[3];
 };
 constexpr size_t kStageBytes = sizeof(StagedRays) * (kTraverseThreads / 32);
 
@@ -221,7 +224,7 @@ __global__ void __launch_bounds__(kTraverseThreads, (ANY ? LaneT::kMinCtasAny : 
     uint32_t gMask = 0, gLight = 0;  // connect: lanes of the current path group that are lit, next light to stage for it
     bool lastGroup = false;
     uint32_t nbSum = 0, ntSum = 0;  // COUNT: per-lane sums of the finished rays' counters; else warp totals (uniform, from the votes)
-    uint32_t nRays = 0;             // rays this warp staged (uniform): every staged ray is traced
+    if (lane == 0) stage.nRays = 0;
 #ifdef PTC_LANE_STATS
     unsigned long long ls[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 #endif
@@ -382,7 +385,7 @@ __global__ void __launch_bounds__(kTraverseThreads, (ANY ? LaneT::kMinCtasAny : 
                 }
                 qHead = 0;
                 qCount = (uint32_t)__popc(m);
-                nRays += qCount;
+                if (lane == 0) stage.nRays += qCount;
                 __syncwarp();
             }
             // ---- refill: idle lanes take staged rays
@@ -431,6 +434,8 @@ __global__ void __launch_bounds__(kTraverseThreads, (ANY ? LaneT::kMinCtasAny : 
             if (wantNode) lane_node_step<(FAST != 0)>(L, sc, stk, kTraverseThreads);
         }
         // ---- triangle phase: at least one step if any lane waits for a triangle, then while they are the majority
+        // (the lanes that hold a ray are counted again: keeping nHave alive across the node loop cost extend its only spill)
+        const int thrTri = voteTri * (32 - __popc(__ballot_sync(full, L.idle() || L.finished())));
         while (true)
         {
             const bool wantTri = L.wants_tri();
@@ -442,7 +447,7 @@ __global__ void __launch_bounds__(kTraverseThreads, (ANY ? LaneT::kMinCtasAny : 
             ls[7] += __popc(__ballot_sync(full, !wantTri && L.wants_node()));
 #endif
             if (wantTri) lane_tri_step<ANY>(L, sc, stk, kTraverseThreads, st.hit, &stage.laneItem[lane]);
-            if (8 * nT <= voteTri * nHave) break;
+            if (8 * nT <= thrTri) break;
         }
     }
 #ifdef PTC_LANE_STATS
@@ -450,7 +455,7 @@ __global__ void __launch_bounds__(kTraverseThreads, (ANY ? LaneT::kMinCtasAny : 
         for (int i = 0; i < 8; i++) atomicAdd(&g_laneStats[(ANY ? 8 : 0) + i], ls[i]);
 #endif
     // warp totals live in lane 0 only (the per-lane sums of COUNT are added up by flush_work's reduction)
-    flush_work(cn, ANY ? &cn->shadowRays : &cn->extensionRays, lane == 0 ? nRays : 0u, (COUNT || lane == 0) ? nbSum : 0u, (COUNT || lane == 0) ? ntSum : 0u);
+    flush_work(cn, ANY ? &cn->shadowRays : &cn->extensionRays, lane == 0 ? stage.nRays : 0u, (COUNT || lane == 0) ? nbSum : 0u, (COUNT || lane == 0) ? ntSum : 0u);
 }
 
 // ------------------------------------------------------------------------------------------------ classify
