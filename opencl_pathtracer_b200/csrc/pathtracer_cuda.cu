@@ -648,7 +648,7 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
         // groups are ever stacked, above the kPark slots of parked triangle groups (one spare level; the CHECKED build tests the bound).
         // Round 2 sized this wideDepth + 2: the two unused levels (2 KB per CTA) pushed connect's 7 CTAs per SM past the 164 KB shared-memory
         // carve-out, i.e. halved its L1 (profiles/r02_sweeps.txt T)
-        if (ctx->wide) ctx->lc.stackDepth = (int)std::max<uint32_t>(3u, wideDepth + WideLane::kPark);
+        if (ctx->wide) ctx->lc.stackDepth = (int)std::max<uint32_t>(3u, wideDepth + WideLane::kPark + WideLane::kItemLevels);  // + the item word's level
         if (const char *e = std::getenv("PTC_STACK_EXTRA")) ctx->lc.stackDepth = std::max(3, ctx->lc.stackDepth + std::atoi(e));  // experiments
         // a tree too deep for one CTA's shared memory is refused here, with a message, not at the first launch with "invalid argument"
         if (traverse_shared_bytes(ctx->wide, ctx->lc.stackDepth, true) > 227u * 1024u)

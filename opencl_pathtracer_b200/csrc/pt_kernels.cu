@@ -233,7 +233,7 @@ __global__ void __launch_bounds__(kTraverseThreads, (ANY ? LaneT::kMinCtasAny : 
         // ---- completion: write the result of a finished ray (the counters are fire-and-forget reductions)
         if (L.finished())
         {
-            const uint32_t item = stage.laneItem[lane];
+            const uint32_t item = lane_item(stk, &stage.laneItem[lane]);
             const uint32_t p = ANY ? (item & ((1u << kLightShift) - 1u)) : item;
             PTC_CHECK(cn, kFaultQueueItem, p, st.capacity);
             const uint32_t li = ANY ? (item >> kLightShift) : 0u;
@@ -396,7 +396,7 @@ __global__ void __launch_bounds__(kTraverseThreads, (ANY ? LaneT::kMinCtasAny : 
                 if (L.idle() && e < qCount)
                 {
                     const float4 o = stage.org[e], d = stage.dir[e], ib = stage.invBest[e];
-                    stage.laneItem[lane] = stage.item[e];
+                    lane_set_item(stk, &stage.laneItem[lane], stage.item[e]);
                     Ray r;
                     r.ox = o.x; r.oy = o.y; r.oz = o.z; r.ow = o.w;
                     r.dx = d.x; r.dy = d.y; r.dz = d.z; r.dw = d.w;
@@ -446,7 +446,7 @@ __global__ void __launch_bounds__(kTraverseThreads, (ANY ? LaneT::kMinCtasAny : 
             ls[5]++; ls[6] += nT;
             ls[7] += __popc(__ballot_sync(full, !wantTri && L.wants_node()));
 #endif
-            if (wantTri) lane_tri_step<ANY>(L, sc, stk, kTraverseThreads, st.hit, &stage.laneItem[lane]);
+            if (wantTri) lane_tri_step<ANY>(L, sc, stk, kTraverseThreads, st.hit);
             if (8 * nT <= thrTri) break;
         }
     }

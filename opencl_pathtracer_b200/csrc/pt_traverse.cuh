@@ -168,6 +168,7 @@ struct TraceLane
     typedef uint32_t *StackRef;
     static constexpr bool kStoresHit = false;  // the hit record rides in the lane (hs, ht, htp, hmat) and is written at completion
     static constexpr uint32_t kMatShift = 0;
+    static constexpr int kItemLevels = 0;
     uint32_t oct;  // unused (WideLane's flag word)
     static __device__ __forceinline__ StackRef stack_ref(uint32_t *p) { return p; }
     Ray r;
@@ -264,8 +265,12 @@ __device__ __forceinline__ void lane_node_step(TraceLane &L, const SceneDev &sc,
     L.cur = (hitL || hitR) ? descend : popped;
 }
 
+// the item a lane is tracing: the BVH2 walk keeps it in the warp's staging block (the wide walk in level 0 of its stack)
+__device__ __forceinline__ uint32_t lane_item(const uint32_t *, const uint32_t *slot) { return *slot; }
+__device__ __forceinline__ void lane_set_item(const uint32_t *, uint32_t *slot, uint32_t v) { *slot = v; }
+
 template <bool ANY>
-__device__ __forceinline__ void lane_tri_step(TraceLane &L, const SceneDev &sc, const uint32_t *stk, const int stride, float4 *, const uint32_t *)
+__device__ __forceinline__ void lane_tri_step(TraceLane &L, const SceneDev &sc, const uint32_t *stk, const int stride, float4 *)
 {
     const uint32_t i = (L.cur >> 4) & 0x7ffffffu;
     PTC_CHECK(sc.faultSink, kFaultTriIndex, i, sc.nTriangles);

@@ -75,7 +75,17 @@ struct WideLane
         {
             asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(a + (uint32_t)(level * stride) * 8u), "r"(v.x), "r"(v.y));
         }
+        // level 0 holds the item (path slot | light) the lane is tracing: cold state that is read when a hit is accepted and at
+        // completion — one LDS off the register that addresses the stack, where &stage.laneItem[lane] took six instructions to form
+        __device__ __forceinline__ uint32_t item() const
+        {
+            uint32_t v;
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
+            return v;
+        }
+        __device__ __forceinline__ void set_item(uint32_t v) const { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v)); }
     };
+    static constexpr int kItemLevels = 1;  // stack levels below the parked groups
     static __device__ __forceinline__ StackRef stack_ref(StackT *p)
     {
         StackRef r;
@@ -181,13 +191,13 @@ __device__ __forceinline__ void lane_begin(WideLane &L, const SceneDev &sc, cons
 }
 
 // no inner child left in the current node group: continue with the most recently postponed siblings. Stack level 0 of a
-// lane are the slots of its parked triangle groups, sibling groups live in the sp levels above them.
+// lane holds its item word, the next kPark levels are the slots of its parked triangle groups, sibling groups live in the sp levels above them.
 __device__ __forceinline__ void wide_normalise(WideLane &L, const WideLane::StackRef stk, const int stride)
 {
     const bool pop = L.gy <= 0x00ffffffu && L.sp > 0;
     if (pop)
     {
-        const uint2 e = stk.ld(L.sp + WideLane::kPark - 1, stride);
+        const uint2 e = stk.ld(L.sp + WideLane::kItemLevels + WideLane::kPark - 1, stride);
         L.gx = e.x;
         L.gy = e.y;
     }
@@ -337,6 +347,9 @@ __device__ __forceinline__ uint32_t slab_test_single(const WideLane &L, const ui
     return slotHit;
 }
 
+__device__ __forceinline__ uint32_t lane_item(const WideLane::StackRef stk, const uint32_t *) { return stk.item(); }
+__device__ __forceinline__ void lane_set_item(const WideLane::StackRef stk, uint32_t *, uint32_t v) { stk.set_item(v); }
+
 // One node visit: take the nearest unvisited child of the current group, postpone its siblings, test its 8 children.
 template <bool FAST>
 __device__ __forceinline__ void lane_node_step(WideLane &L, const SceneDev &sc, const WideLane::StackRef stk, const int stride)
@@ -355,13 +368,13 @@ __device__ __forceinline__ void lane_node_step(WideLane &L, const SceneDev &sc, 
     ldg256(np + 64, reinterpret_cast<float4 &>(n4), reinterpret_cast<float4 &>(n5));  // n5 = padding
     if (L.ty != 0u)
     {
-        stk.st(WideLane::kPark == 1 ? 0 : (int)((L.oct >> 8) & 3u), stride, make_uint2(L.tx, L.ty));  // park the untested triangles (wants_node: a slot is free)
+        stk.st(WideLane::kItemLevels + (WideLane::kPark == 1 ? 0 : (int)((L.oct >> 8) & 3u)), stride, make_uint2(L.tx, L.ty));  // park the untested triangles (wants_node: a slot is free)
         L.oct += WideLane::kParkedOne;
     }
     if (rest > 0x00ffffffu)
     {
-        PTC_CHECK(sc.faultSink, kFaultStack, L.sp + WideLane::kPark, sc.stackDepth);
-        stk.st(L.sp + WideLane::kPark, stride, make_uint2(L.gx, rest));
+        PTC_CHECK(sc.faultSink, kFaultStack, L.sp + WideLane::kItemLevels + WideLane::kPark, sc.stackDepth);
+        stk.st(L.sp + WideLane::kItemLevels + WideLane::kPark, stride, make_uint2(L.gx, rest));
     }
     L.sp += rest > 0x00ffffffu ? 1 : 0;
     L.nb += 8;
@@ -395,13 +408,12 @@ __device__ __forceinline__ void lane_node_step(WideLane &L, const SceneDev &sc, 
 // translates it once per ray) and the new bound follows from the hit's own ray parameter (directions are unit length over
 // the four lanes the reference normalises, so parameter and distance coincide).
 template <bool ANY>
-__device__ __forceinline__ void lane_tri_step(WideLane &L, const SceneDev &sc, const WideLane::StackRef stk, const int stride, float4 *__restrict__ hitOut,
-                                              const uint32_t *laneItem)
+__device__ __forceinline__ void lane_tri_step(WideLane &L, const SceneDev &sc, const WideLane::StackRef stk, const int stride, float4 *__restrict__ hitOut)
 {
     if (L.ty == 0u)
     {
         L.oct -= WideLane::kParkedOne;
-        const uint2 e = stk.ld(WideLane::kPark == 1 ? 0 : (int)((L.oct >> 8) & 3u), stride);  // the group parked last
+        const uint2 e = stk.ld(WideLane::kItemLevels + (WideLane::kPark == 1 ? 0 : (int)((L.oct >> 8) & 3u)), stride);  // the group parked last
         L.tx = e.x;
         L.ty = e.y;
     }
@@ -417,7 +429,7 @@ __device__ __forceinline__ void lane_tri_step(WideLane &L, const SceneDev &sc, c
     L.tmax = acc ? bound_as_parameter(htp, L.r) : L.tmax;
     if (!ANY && acc)
     {
-        hitOut[*laneItem] = make_float4(0.f, hs, ht, htp);  // .x = the triangle index, written at completion
+        hitOut[stk.item()] = make_float4(0.f, hs, ht, htp);  // .x = the triangle index, written at completion
         L.oct = (L.oct & ~(15u << WideLane::kMatShift)) | (hmat << WideLane::kMatShift);
     }
     if (ANY)
