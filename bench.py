@@ -274,6 +274,15 @@ def roofline_block(pt, args, scene, W, H, S, mode, main_flags, device, stream_pt
         if dram:
             # ncu's per-launch DRAM bytes were captured on the larger launches of a step (cold caches, serialised): scaled by time
             out["dram_gbs_ncu"] = k.get("dram_gbs")
+            if k.get("dram_gbs"):
+                # what the DRAM itself moved for this kernel, as a fraction of the HBM copy rate: the algorithmic fraction above counts
+                # every node / triangle visit, and the L2 serves most of them (top of the tree, coherent camera rays), so it can pass 1
+                out["dram_frac_ncu"] = k["dram_gbs"] / peaks["hbm_gbs"]
+                out["l2_hit_pct_ncu"] = k.get("l2_hit_pct")
+                if not resident:
+                    out["frac_note"] = ("frac = algorithmic bytes (64 B per BVH2 node visit and triangle test of the reference walk) / time / HBM copy rate; "
+                                        "the L2 (hit rate %.0f %% under ncu) serves repeated visits, so DRAM itself runs at dram_frac_ncu = %.2f of the copy rate "
+                                        "and the kernel is issue bound like the L2-resident scenes (see limiter)" % (k.get("l2_hit_pct") or 0.0, out["dram_frac_ncu"]))
         if k.get("issue_active_pct") is not None:
             out["limiter"] = "instruction issue + SIMT efficiency (ncu %s: issue slots %.0f %% busy, %.1f of 32 lanes per instruction, %s spill instructions)" % (
                 k.get("source", "profiles/"), k["issue_active_pct"], k["lanes_per_inst"], k.get("spill_insts", "?"))

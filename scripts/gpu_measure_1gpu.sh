@@ -29,3 +29,4 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -s 40 -c 4
 python scripts/summarize_launches.py gpurun_out/m1_launches.csv | tee gpurun_out/m1_launches_summary.txt
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_trace|k_shade' -s 3 -c 3 -f -o gpurun_out/m1_ncu_atrium python scripts/profile_step.py 8 fast atrium 1 > gpurun_out/m1_ncu_atrium.log 2>&1; tail -1 gpurun_out/m1_ncu_atrium.log
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_trace|k_shade|k_classify' -s 4 -c 4 -f -o gpurun_out/m1_ncu_cornell python scripts/profile_step.py 8 fast cornell 1 > gpurun_out/m1_ncu_cornell.log 2>&1; tail -1 gpurun_out/m1_ncu_cornell.log
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_trace|k_shade' -s 0 -c 3 -f -o gpurun_out/m1_ncu_terrain python scripts/profile_step.py 1 fast terrain 1 > gpurun_out/m1_ncu_terrain.log 2>&1; tail -1 gpurun_out/m1_ncu_terrain.log
