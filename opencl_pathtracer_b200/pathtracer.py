@@ -6,6 +6,7 @@ construct (= setup), upload(scene) (= initialize memory), render(first, n) + rea
 run loop), read_stats(), close() (= the release at the end of OpenCL_RunKernel).
 """
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -205,8 +206,17 @@ class PathTracerCUDA:
 
     def close(self):
         if getattr(self, "_h", None):
+            # CHECKED build (PTC_LIB_DIR=.../_lib_checked): a context must end with no bounds-check fault, whatever test drove it —
+            # so the whole GPU suite run on that library is a memory-checker pass (PTC_CHECKED_SELFTEST provokes faults on purpose)
+            fault = None
+            if os.path.basename(N.LIB_DIR.rstrip("/")) == "_lib_checked" and not os.environ.get("PTC_CHECKED_SELFTEST"):
+                c = N.Counters()
+                if self._lib.ptc_read_counters(self._h, C.byref(c)) == N.PTC_OK and c.faults:
+                    fault = "CHECKED build: fault mask %#x, first: code %d value %d bound %d" % (c.faults, c.fault_code, c.fault_value, c.fault_bound)
             self._lib.ptc_destroy(self._h)
             self._h = None
+            if fault:
+                raise RuntimeError(fault)
 
     def __enter__(self):
         return self
