@@ -668,7 +668,12 @@ int ptc_upload_scene(ptc_ctx *ctx, const ptc_scene_view *s)
     // PTC_PARTITION=0/1 overrides.
     ctx->lc.partition = ctx->fast && nT <= 4096u;
     if (const char *e = std::getenv("PTC_PARTITION")) ctx->lc.partition = std::atoi(e) != 0;
-    ctx->st.partitioned = ctx->lc.partition ? 1u : 0u;
+    // connect alone gains from the pass on every scene: it stages shadow rays by groups of 32 paths, and in the partitioned queue a
+    // group holds 32 LIT paths (positions tell the class) instead of whatever the bounce's queue holds — connect -3.5 % on the bench
+    // scene, -5 % on the 10 M-triangle scene, for 0.05 ms of k_classify per bounce (profiles/r02_sweeps.txt Y). PTC_PARTITION_CONNECT=0/1.
+    ctx->lc.partitionConnect = ctx->fast && ctx->sc.nLights > 0;
+    if (const char *e = std::getenv("PTC_PARTITION_CONNECT")) ctx->lc.partitionConnect = std::atoi(e) != 0;
+    ctx->st.partitioned = (ctx->lc.partition || ctx->lc.partitionConnect) ? 1u : 0u;
     ctx->sceneLoaded = true;
     ctx->sceneVersion++;  // device pointers and launch configuration may have changed: a captured batch graph is stale
     return PTC_OK;
@@ -712,6 +717,7 @@ int replicate_scene(ptc_ctx *dst, const ptc_ctx *src)
     dst->lc.wide = src->lc.wide;
     dst->lc.stackDepth = src->lc.stackDepth;
     dst->lc.partition = src->lc.partition;
+    dst->lc.partitionConnect = src->lc.partitionConnect;
     dst->st.partitioned = src->st.partitioned;
     dst->lc.traverseGrid = dst->smCount * traverse_ctas_per_sm(dst->fast, dst->wide, dst->lc.stackDepth, false);  // also opts this device's kernels in to large stacks
     dst->lc.connectGrid = dst->smCount * traverse_ctas_per_sm(dst->fast, dst->wide, dst->lc.stackDepth, true);
@@ -845,7 +851,7 @@ int runBatch(ptc_ctx *ctx, uint32_t first, uint32_t nIter, bool accumulate, int 
             StageTimer t(ctx, 1);
             launch_extend(s, ctx->lc, ctx->fast, ctx->sc, ctx->st, qin, cn, b);
         }
-        if (ctx->lc.partition)
+        if (ctx->lc.partition || (ctx->lc.partitionConnect && ctx->sc.nLights))
         {
             StageTimer t(ctx, 3);  // charged to the shade stage, whose input it prepares
             launch_classify(s, ctx->lc, ctx->st, qin, cn, b);

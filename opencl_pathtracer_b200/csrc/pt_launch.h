@@ -15,6 +15,7 @@ struct LaunchCfg
     bool wide;           // FAST mode: traverse the 8-wide compressed BVH (stackDepth then counts 8-byte entries)
     bool partition;      // k_classify partitions every bounce's queue by class; connect and shade take classes from positions (decided per
                          // scene at upload: pays where shade is instruction bound, costs where it is DRAM bound — k_shade in pt_kernels.cu)
+    bool partitionConnect;  // the same pass for the connect stage alone (shade keeps the bounce's own queue): groups of 32 LIT paths per staging
     bool count;          // per-ray work counters + the two 5000-bin histograms (PARITY always; FAST with PTC_FLAG_WORK_COUNTERS)
 };
 
