@@ -52,10 +52,10 @@ struct WideLane
     float tmax;        // the same bound as a ray parameter, padded
     uint32_t gx, gy;   // node group: first child index | bits 31..24 children still to visit (front to back), bits 7..0 imask
     uint32_t tx, ty;   // triangle group: first record (24 * node) | 24 bits of triangles still to test
-    uint32_t oct;      // bits 2..0: 7 - ray octant; kPostponed: a triangle group waits in the lane's slot 0 of the stack
+    uint32_t oct;      // flag word — bits 2..0: 7 - ray octant; 9..8: parked triangle groups; kStrict, kSingle; 15..12: MaterialType of the hit side
     int sp;            // stack entries, -1 = no ray
-    int hitTri;        // wide record index of the accepted hit, -1 = none; (s, t, parameter, material) are recomputed from it once
-                       // per ray (hit_record) instead of riding in four registers through every step
+    int hitTri;        // wide record index of the accepted hit, -1 = none; (s, t, parameter) go to the path's hit record when the hit is
+                       // accepted (kStoresHit) instead of riding in three registers through every step
     uint32_t nb, nt;
     bool found;
 
@@ -138,8 +138,8 @@ struct WideLane
     __device__ __forceinline__ bool wants_tri() const { return sp >= 0 && (ty != 0u || (oct & kParkedMask)); }
     // BVH-order index of the hit (what the shade stage and the reference's ids use), -1 = miss
     __device__ __forceinline__ int hit_index(const SceneDev &sc) const { return hitTri < 0 ? -1 : (int)__ldg(&sc.tri8Index[hitTri]); }
-    // (s, t, ray parameter, MaterialType of the side hit) of the final hit: the accepted test once more — the same operations on
-    // the same operands, hence the same bits the walk saw when it accepted the triangle
+    // (s, t, ray parameter, MaterialType of the side hit) of the final hit by repeating the accepted test — the same operations on the
+    // same operands, hence the same bits (what completion did before kStoresHit; kept for callers that hold only the lane)
     __device__ __forceinline__ void hit_record(const SceneDev &sc, float &hs, float &ht, float &htp, uint32_t &hmat) const
     {
         hs = ht = htp = 0.f;
