@@ -100,10 +100,11 @@ def test_wide_bvh_traversal_matches_brute_force(scene_factory):
     """The traversal of pt_wide.cuh restated in scalar Python (same decode rules: octant ordering, hit masks,
     relative child indices, triangle groups) finds the brute-force closest hit."""
     sc = scene_factory("atrium:8", 64, 48)
-    nodes, order, _ = sc.wide_bvh()
+    nodes, order, depth = sc.wide_bvh()
     tris = sc.triangles()
     verts = np.stack([np.stack([tris[k][a] for a in "xyz"], -1) for k in ("S1", "S2", "S3")], 1).astype(np.float64)
     rng = np.random.default_rng(7)
+    max_stack = 0
     lo, hi = verts.reshape(-1, 3).min(0), verts.reshape(-1, 3).max(0)
     visited_total = 0
     for _ in range(120):
@@ -129,6 +130,7 @@ def test_wide_bvh_traversal_matches_brute_force(scene_factory):
                 rel = bin(g[1] & 0xff & ((1 << slot) - 1)).count("1")
                 if rest > 0x00ffffff:
                     stack.append((g[0], rest))
+                    max_stack = max(max_stack, len(stack))
                 node = g[0] + rel
                 n, blo, bhi = _decode(nodes, node)
                 visited_total += 1
@@ -163,6 +165,9 @@ def test_wide_bvh_traversal_matches_brute_force(scene_factory):
                 break
         assert hit == best or (best >= 0 and hit >= 0 and abs(tmax - best_t) < 1e-9 * max(1.0, best_t)), (hit, best, tmax, best_t)
     assert visited_total > 0
+    # the walk stacks the unvisited siblings of the child it descends into and the root has none: never more than depth - 1 groups
+    # (ptc_upload_scene sizes the shared-memory stack by this bound: item word + parked group + depth - 1 + one spare level)
+    assert 0 < max_stack <= depth - 1, (max_stack, depth)
 
 
 # ---- the packed half-precision slab test of pt_wide.cuh (slab_test_half2), restated operation by operation in numpy
